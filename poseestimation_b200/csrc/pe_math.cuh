@@ -1,0 +1,342 @@
+// Register-resident per-record math for the rotation-mapping hot path (sm_100a).
+//
+// Every function here works on ONE record held in registers by ONE thread: a 3x3 matrix is nine floats in
+// row-major order (m[3*i+j]), exactly the layout `x.view(-1, 3, 3)` gives the reference
+// (/root/reference/rotation_representation.py:199).  No function touches memory; the staging kernels in
+// pe_stage.cuh move records between HBM, shared memory and registers.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string.h>
+#include <math.h>
+
+namespace pe {
+
+// __host__ as well, so tests/hostmath can run the very same formulas on the CPU against the oracle (test
+// infrastructure only: nothing in the package calls the host instantiation).
+#define PE_DEV __host__ __device__ __forceinline__
+
+PE_DEV float rsqrt_fast(float x) {  // MUFU.RSQ, ~2^-22 relative error, flush-to-zero
+#ifdef __CUDA_ARCH__
+    float y;
+    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+#else
+    return 1.0f / sqrtf(x);
+#endif
+}
+PE_DEV int f2i(float x) {
+#ifdef __CUDA_ARCH__
+    return __float_as_int(x);
+#else
+    int i; memcpy(&i, &x, 4); return i;
+#endif
+}
+PE_DEV float i2f(int i) {
+#ifdef __CUDA_ARCH__
+    return __int_as_float(i);
+#else
+    float x; memcpy(&x, &i, 4); return x;
+#endif
+}
+PE_DEV void sincos_f(float a, float* s, float* c) {
+#ifdef __CUDA_ARCH__
+    sincosf(a, s, c);
+#else
+    *s = sinf(a); *c = cosf(a);
+#endif
+}
+// rsqrt with one Newton step: full fp32 accuracy, used where a single rounding matters (elementwise maps).
+PE_DEV float rsqrt_nr(float x) {
+    float y = rsqrt_fast(x);
+    float t = x * y;
+    return y * fmaf(-0.5f * t, y, 1.5f);
+}
+
+// 2^-e for e = exponent of the largest |entry| : an exact power-of-two prescale, so the nine mantissas are
+// untouched and Gram entries stay inside [0, 12].  Exponent is clamped so zero/denormal and huge inputs do
+// not produce a zero or non-finite scale.
+PE_DEV float pow2_prescale(const float* m) {
+    float mx = fmaxf(fmaxf(fmaxf(fabsf(m[0]), fabsf(m[1])), fmaxf(fabsf(m[2]), fabsf(m[3]))),
+                     fmaxf(fmaxf(fabsf(m[4]), fabsf(m[5])), fmaxf(fabsf(m[6]), fmaxf(fabsf(m[7]), fabsf(m[8])))));
+    int e = (f2i(mx) >> 23) & 0xff;
+    e = e < 1 ? 1 : (e > 253 ? 253 : e);
+    return i2f((254 - e) << 23);
+}
+
+// One Hestenes rotation of columns (p, q) of A (3 rows) and V (3 rows).  The angle is the exact Jacobi angle
+// (two MUFU.RSQ, no division); when column q is the longer one a quarter turn is composed in, so that after the
+// rotation |a_p| >= |a_q| ("sorting rotation").  After the last (1,2) rotation of a sweep column 2 is the
+// shortest, which is what the cross-product completion in svd_orth() relies on.
+PE_DEV void hestenes(float& ap0, float& ap1, float& ap2, float& aq0, float& aq1, float& aq2,
+                     float& vp0, float& vp1, float& vp2, float& vq0, float& vq1, float& vq2) {
+    float al = fmaf(ap2, ap2, fmaf(ap1, ap1, ap0 * ap0));
+    float be = fmaf(aq2, aq2, fmaf(aq1, aq1, aq0 * aq0));
+    float ga = fmaf(ap2, aq2, fmaf(ap1, aq1, ap0 * aq0));
+    float dh = 0.5f * (al - be);
+    float ad = fmaxf(fabsf(dh), 1e-18f);
+    float r = rsqrt_fast(fmaf(ad, ad, ga * ga));
+    float c2 = ad * r;                   // cos 2θ  in [0, 1]
+    float s2 = ga * r;                   // sin 2θ  (sign fixed below)
+    float w = fmaf(2.0f, c2, 2.0f);      // 2 + 2 cos 2θ  in [2, 4]
+    float h = rsqrt_fast(w);
+    float c = 0.5f * w * h;              // cos θ
+    float s = s2 * h;                    // sin θ  for dh > 0
+    // dh < 0: the inner angle changes sign, then a quarter turn swaps the roles of p and q.
+    bool neg = dh < 0.0f;
+    float cp = neg ? s : c;              // (-(-s)) = s
+    float sp = neg ? c : s;
+    // p' = cp*p + sp*q ; q' = cp*q - sp*p
+    float t;
+    t = ap0; ap0 = fmaf(cp, t, sp * aq0); aq0 = fmaf(cp, aq0, -sp * t);
+    t = ap1; ap1 = fmaf(cp, t, sp * aq1); aq1 = fmaf(cp, aq1, -sp * t);
+    t = ap2; ap2 = fmaf(cp, t, sp * aq2); aq2 = fmaf(cp, aq2, -sp * t);
+    t = vp0; vp0 = fmaf(cp, t, sp * vq0); vq0 = fmaf(cp, vq0, -sp * t);
+    t = vp1; vp1 = fmaf(cp, t, sp * vq1); vq1 = fmaf(cp, vq1, -sp * t);
+    t = vp2; vp2 = fmaf(cp, t, sp * vq2); vq2 = fmaf(cp, vq2, -sp * t);
+}
+
+// Nearest rotation to M in the Frobenius norm:  R = U diag(1, 1, det(U V^T)) V^T  with  M = U S V^T
+// (reference: symmetric_orthogonalization, /root/reference/rotation_representation.py:192-206).
+//
+// Method (not the reference's LAPACK path): one-sided Jacobi on the columns of A = M V, V accumulated from
+// proper rotations only (det V = +1).  At convergence A = U S.  With u0, u1 the two longest normalised columns,
+//     R = u0 v0^T + u1 v1^T + (u0 x u1) v2^T
+// is the det-fixed answer for either sign of det(M): the true u2 is +-(u0 x u1) and the sign is exactly the
+// reference's det(U V^T).  The smallest singular direction is never normalised, so rank-2 inputs are exact,
+// and nothing is squared (no M^T M), so the error is at the conditioning limit eps*s1/(s2 + d*s3).
+//
+// `dsign` receives det(U V^T) = sign(det M) as +-1 (what the reference multiplies the last row of V^T by).
+template <int SWEEPS>
+PE_DEV void svd_orth(const float* m, float* r, float& dsign) {
+    const float sc = pow2_prescale(m);
+    float a00 = m[0] * sc, a01 = m[1] * sc, a02 = m[2] * sc;
+    float a10 = m[3] * sc, a11 = m[4] * sc, a12 = m[5] * sc;
+    float a20 = m[6] * sc, a21 = m[7] * sc, a22 = m[8] * sc;
+    float v00 = 1.f, v01 = 0.f, v02 = 0.f, v10 = 0.f, v11 = 1.f, v12 = 0.f, v20 = 0.f, v21 = 0.f, v22 = 1.f;
+#pragma unroll
+    for (int sw = 0; sw < SWEEPS; ++sw) {
+        hestenes(a00, a10, a20, a01, a11, a21, v00, v10, v20, v01, v11, v21);
+        hestenes(a00, a10, a20, a02, a12, a22, v00, v10, v20, v02, v12, v22);
+        hestenes(a01, a11, a21, a02, a12, a22, v01, v11, v21, v02, v12, v22);
+    }
+    float al0 = fmaf(a20, a20, fmaf(a10, a10, a00 * a00));
+    float al1 = fmaf(a21, a21, fmaf(a11, a11, a01 * a01));
+    float k0 = rsqrt_fast(al0), k1 = rsqrt_fast(al1);
+    float u00 = a00 * k0, u10 = a10 * k0, u20 = a20 * k0;
+    float u01 = a01 * k1, u11 = a11 * k1, u21 = a21 * k1;
+    if (__builtin_expect(!(al1 > 1e-24f * al0) || !(al0 > 0.f), 0)) {
+        // rank <= 1 (or the zero matrix): the reference returns an arbitrary completion; pick a finite one.
+        if (!(al0 > 0.f)) {
+            if (al0 == 0.f) { u00 = 1.f; u10 = 0.f; u20 = 0.f; }  // zero matrix -> identity (V = I too)
+        }
+        if (al0 == al0) {  // not NaN
+            float ax = fabsf(u00), ay = fabsf(u10), az = fabsf(u20);
+            float e0 = (ax <= ay && ax <= az) ? 1.f : 0.f;
+            float e1 = (e0 == 0.f && ay <= az) ? 1.f : 0.f;
+            float e2 = (e0 == 0.f && e1 == 0.f) ? 1.f : 0.f;
+            // u1 = normalise(u0 x e) ... any unit vector orthogonal to u0
+            float c0 = u10 * e2 - u20 * e1, c1 = u20 * e0 - u00 * e2, c2 = u00 * e1 - u10 * e0;
+            float kk = rsqrt_nr(c0 * c0 + c1 * c1 + c2 * c2);
+            u01 = c0 * kk; u11 = c1 * kk; u21 = c2 * kk;
+        }
+    }
+    // third left vector by cross product (this is where det(U V^T) is applied)
+    float u02 = fmaf(u10, u21, -u20 * u11);
+    float u12 = fmaf(u20, u01, -u00 * u21);
+    float u22 = fmaf(u00, u11, -u10 * u01);
+    dsign = (fmaf(a02, u02, fmaf(a12, u12, a22 * u22)) < 0.f) ? -1.f : 1.f;
+    // V's columns carry the accumulated (1 + O(2^-22)) scale of the approximate rsqrt's: normalise once.
+    float n0 = rsqrt_fast(fmaf(v20, v20, fmaf(v10, v10, v00 * v00)));
+    float n1 = rsqrt_fast(fmaf(v21, v21, fmaf(v11, v11, v01 * v01)));
+    float n2 = rsqrt_fast(fmaf(v22, v22, fmaf(v12, v12, v02 * v02)));
+    v00 *= n0; v10 *= n0; v20 *= n0;
+    v01 *= n1; v11 *= n1; v21 *= n1;
+    v02 *= n2; v12 *= n2; v22 *= n2;
+    // R_ik = sum_j u_ij v_kj
+    r[0] = fmaf(u02, v02, fmaf(u01, v01, u00 * v00));
+    r[1] = fmaf(u02, v12, fmaf(u01, v11, u00 * v10));
+    r[2] = fmaf(u02, v22, fmaf(u01, v21, u00 * v20));
+    r[3] = fmaf(u12, v02, fmaf(u11, v01, u10 * v00));
+    r[4] = fmaf(u12, v12, fmaf(u11, v11, u10 * v10));
+    r[5] = fmaf(u12, v22, fmaf(u11, v21, u10 * v20));
+    r[6] = fmaf(u22, v02, fmaf(u21, v01, u20 * v00));
+    r[7] = fmaf(u22, v12, fmaf(u21, v11, u20 * v10));
+    r[8] = fmaf(u22, v22, fmaf(u21, v21, u20 * v20));
+}
+
+constexpr int kSweeps = 4;  // 4 sweeps reach the fp32 conditioning limit on Gaussian inputs
+
+// Pullback of R = svd_orth(M):  given M, R and G = dL/dR, return dL/dM.
+//
+// Polar form of the closed formula in SURVEY.md 7.4 (B = D U^T G V, W_ij = (B_ij - B_ji)/(s'_i + s'_j),
+// dM = U D W V^T): with P = R^T M = V diag(s') V^T (symmetric) and Z = R^T G - G^T R (skew, axial vector z),
+// the skew Y = V W V^T solves  Y P + P Y = Z, which for 3x3 is the symmetric linear system
+//     (tr(P) I - P) y = z,       dM = R [y]_x .
+// The eigenvalues of tr(P) I - P are exactly the s'_i + s'_j, so the only degenerate direction is
+// s2 + d*s3 -> 0.  Guard: det is floored at kDetFloor * (tr/3)^3, which bounds the gradient.
+// This replaces autograd through torch.svd / det / cat / matmul (rotation_representation.py:200-205).
+constexpr float kDetFloor = 1e-7f;
+PE_DEV void svd_orth_pullback(const float* m, const float* r, const float* g, float* dm) {
+    const float sc = pow2_prescale(m);
+    // N = R^T (sc*M)
+    float n[9];
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = 0; j < 3; ++j)
+            n[3 * i + j] = sc * fmaf(r[6 + i], m[6 + j], fmaf(r[3 + i], m[3 + j], r[i] * m[j]));
+    float p01 = 0.5f * (n[1] + n[3]), p02 = 0.5f * (n[2] + n[6]), p12 = 0.5f * (n[5] + n[7]);
+    float h00 = n[4] + n[8], h11 = n[0] + n[8], h22 = n[0] + n[4];
+    float h01 = -p01, h02 = -p02, h12 = -p12;
+    // T = R^T G ; z = axial(T - T^T)
+    float t01 = fmaf(r[6], g[7], fmaf(r[3], g[4], r[0] * g[1]));
+    float t02 = fmaf(r[6], g[8], fmaf(r[3], g[5], r[0] * g[2]));
+    float t10 = fmaf(r[7], g[6], fmaf(r[4], g[3], r[1] * g[0]));
+    float t12 = fmaf(r[7], g[8], fmaf(r[4], g[5], r[1] * g[2]));
+    float t20 = fmaf(r[8], g[6], fmaf(r[5], g[3], r[2] * g[0]));
+    float t21 = fmaf(r[8], g[7], fmaf(r[5], g[4], r[2] * g[1]));
+    float z0 = t21 - t12, z1 = t02 - t20, z2 = t10 - t01;
+    // y = adj(H) z / det(H)
+    float c00 = fmaf(h11, h22, -h12 * h12), c01 = fmaf(h02, h12, -h01 * h22), c02 = fmaf(h01, h12, -h02 * h11);
+    float c11 = fmaf(h00, h22, -h02 * h02), c12 = fmaf(h01, h02, -h00 * h12), c22 = fmaf(h00, h11, -h01 * h01);
+    float det = fmaf(h00, c00, fmaf(h01, c01, h02 * c02));
+    float tr3 = (h00 + h11 + h22) * (1.0f / 3.0f);
+    float fl = kDetFloor * fabsf(tr3 * tr3 * tr3);
+    det = fmaxf(det, fl);
+    float inv = sc / fmaxf(det, 1e-37f);
+    float y0 = inv * fmaf(c00, z0, fmaf(c01, z1, c02 * z2));
+    float y1 = inv * fmaf(c01, z0, fmaf(c11, z1, c12 * z2));
+    float y2 = inv * fmaf(c02, z0, fmaf(c12, z1, c22 * z2));
+    // dM = R [y]_x
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        float r0 = r[3 * i], r1 = r[3 * i + 1], r2 = r[3 * i + 2];
+        dm[3 * i + 0] = fmaf(r1, y2, -r2 * y1);
+        dm[3 * i + 1] = fmaf(r2, y0, -r0 * y2);
+        dm[3 * i + 2] = fmaf(r0, y1, -r1 * y0);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Gram-Schmidt 6D map (reference: compute_rotation_matrix_from_ortho6d, rotation_representation.py:21-36).
+// x = a/|a| ; z = (x X b)/|x X b| ; y = z X x ; the three vectors are the COLUMNS of R.  No epsilon: a zero or
+// collinear input gives NaN, as in the reference.
+PE_DEV void ortho6d(const float* p, float* r) {
+    float ka = rsqrt_nr(fmaf(p[2], p[2], fmaf(p[1], p[1], p[0] * p[0])));
+    float x0 = p[0] * ka, x1 = p[1] * ka, x2 = p[2] * ka;
+    float z0 = fmaf(x1, p[5], -x2 * p[4]), z1 = fmaf(x2, p[3], -x0 * p[5]), z2 = fmaf(x0, p[4], -x1 * p[3]);
+    float kz = rsqrt_nr(fmaf(z2, z2, fmaf(z1, z1, z0 * z0)));
+    z0 *= kz; z1 *= kz; z2 *= kz;
+    float y0 = fmaf(z1, x2, -z2 * x1), y1 = fmaf(z2, x0, -z0 * x2), y2 = fmaf(z0, x1, -z1 * x0);
+    r[0] = x0; r[1] = y0; r[2] = z0;
+    r[3] = x1; r[4] = y1; r[5] = z1;
+    r[6] = x2; r[7] = y2; r[8] = z2;
+}
+
+// Pullback of ortho6d: recomputes the forward from p (24 B) instead of saving intermediates.
+PE_DEV void ortho6d_pullback(const float* p, const float* g, float* dp) {
+    float na2 = fmaf(p[2], p[2], fmaf(p[1], p[1], p[0] * p[0]));
+    float ka = rsqrt_nr(na2);
+    float x0 = p[0] * ka, x1 = p[1] * ka, x2 = p[2] * ka;
+    float w0 = fmaf(x1, p[5], -x2 * p[4]), w1 = fmaf(x2, p[3], -x0 * p[5]), w2 = fmaf(x0, p[4], -x1 * p[3]);
+    float kz = rsqrt_nr(fmaf(w2, w2, fmaf(w1, w1, w0 * w0)));
+    float z0 = w0 * kz, z1 = w1 * kz, z2 = w2 * kz;
+    // upstream per column
+    float gx0 = g[0], gx1 = g[3], gx2 = g[6];
+    float gy0 = g[1], gy1 = g[4], gy2 = g[7];
+    float gz0 = g[2], gz1 = g[5], gz2 = g[8];
+    // y = z X x :  gz += x X gy ;  gx += gy X z
+    gz0 += fmaf(x1, gy2, -x2 * gy1); gz1 += fmaf(x2, gy0, -x0 * gy2); gz2 += fmaf(x0, gy1, -x1 * gy0);
+    gx0 += fmaf(gy1, z2, -gy2 * z1); gx1 += fmaf(gy2, z0, -gy0 * z2); gx2 += fmaf(gy0, z1, -gy1 * z0);
+    // z = w/|w|
+    float dz = fmaf(z2, gz2, fmaf(z1, gz1, z0 * gz0));
+    float gw0 = (gz0 - z0 * dz) * kz, gw1 = (gz1 - z1 * dz) * kz, gw2 = (gz2 - z2 * dz) * kz;
+    // w = x X b :  gx += b X gw ;  gb = gw X x
+    gx0 += fmaf(p[4], gw2, -p[5] * gw1); gx1 += fmaf(p[5], gw0, -p[3] * gw2); gx2 += fmaf(p[3], gw1, -p[4] * gw0);
+    dp[3] = fmaf(gw1, x2, -gw2 * x1); dp[4] = fmaf(gw2, x0, -gw0 * x2); dp[5] = fmaf(gw0, x1, -gw1 * x0);
+    // x = a/|a|
+    float dx = fmaf(x2, gx2, fmaf(x1, gx1, x0 * gx0));
+    dp[0] = (gx0 - x0 * dx) * ka; dp[1] = (gx1 - x1 * dx) * ka; dp[2] = (gx2 - x2 * dx) * ka;
+}
+
+// Quaternion map, order (w, x, y, z), norm floored at 1e-8
+// (reference: compute_rotation_matrix_from_quaternion + normalize_vector, rotation_representation.py:38-50,139-172).
+constexpr float kQuatFloor = 1e-8f;
+PE_DEV void quat_unit(const float* q, float& w, float& x, float& y, float& z, float& kn, bool& floored) {
+    float n2 = fmaf(q[3], q[3], fmaf(q[2], q[2], fmaf(q[1], q[1], q[0] * q[0])));
+    floored = !(n2 > kQuatFloor * kQuatFloor);
+    kn = floored ? (1.0f / kQuatFloor) : rsqrt_nr(n2);
+    w = q[0] * kn; x = q[1] * kn; y = q[2] * kn; z = q[3] * kn;
+}
+PE_DEV void quat_map(const float* q, float* r) {
+    float w, x, y, z, kn; bool fl;
+    quat_unit(q, w, x, y, z, kn, fl);
+    float xx = x * x, yy = y * y, zz = z * z, xy = x * y, xz = x * z, yz = y * z, xw = x * w, yw = y * w, zw = z * w;
+    r[0] = 1.f - 2.f * yy - 2.f * zz; r[1] = 2.f * xy - 2.f * zw;       r[2] = 2.f * xz + 2.f * yw;
+    r[3] = 2.f * xy + 2.f * zw;       r[4] = 1.f - 2.f * xx - 2.f * zz; r[5] = 2.f * yz - 2.f * xw;
+    r[6] = 2.f * xz - 2.f * yw;       r[7] = 2.f * yz + 2.f * xw;       r[8] = 1.f - 2.f * xx - 2.f * yy;
+}
+PE_DEV void quat_pullback(const float* q, const float* g, float* dq) {
+    float w, x, y, z, kn; bool fl;
+    quat_unit(q, w, x, y, z, kn, fl);
+    float gw = 2.f * (z * (g[3] - g[1]) + y * (g[2] - g[6]) + x * (g[7] - g[5]));
+    float gx = 2.f * (y * (g[1] + g[3]) + z * (g[2] + g[6]) + w * (g[7] - g[5]) - 2.f * x * (g[4] + g[8]));
+    float gy = 2.f * (x * (g[1] + g[3]) + z * (g[5] + g[7]) + w * (g[2] - g[6]) - 2.f * y * (g[0] + g[8]));
+    float gz = 2.f * (x * (g[2] + g[6]) + y * (g[5] + g[7]) + w * (g[3] - g[1]) - 2.f * z * (g[0] + g[4]));
+    // through u = q * kn : kn constant when floored, 1/|q| otherwise
+    float d = fl ? 0.f : (w * gw + x * gx + y * gy + z * gz);
+    dq[0] = (gw - w * d) * kn; dq[1] = (gx - x * d) * kn; dq[2] = (gy - y * d) * kn; dq[3] = (gz - z * d) * kn;
+}
+
+// Euler map (reference: compute_rotation_matrix_from_euler, rotation_representation.py:92-115).  Note the index
+// swap: angle "2" comes from e[2] and angle "3" from e[1] (lines 101-104).
+PE_DEV void euler_map(const float* e, float* r) {
+    float s1, c1, s2, c2, s3, c3;
+    sincos_f(e[0], &s1, &c1); sincos_f(e[2], &s2, &c2); sincos_f(e[1], &s3, &c3);
+    r[0] = c2 * c3;                 r[1] = -s2;     r[2] = c2 * s3;
+    r[3] = c1 * s2 * c3 + s1 * s3;  r[4] = c1 * c2; r[5] = c1 * s2 * s3 - s1 * c3;
+    r[6] = s1 * s2 * c3 - c1 * s3;  r[7] = s1 * c2; r[8] = s1 * s2 * s3 + c1 * c3;
+}
+PE_DEV void euler_pullback(const float* e, const float* g, float* de) {
+    float s1, c1, s2, c2, s3, c3;
+    sincos_f(e[0], &s1, &c1); sincos_f(e[2], &s2, &c2); sincos_f(e[1], &s3, &c3);
+    float r3 = c1 * s2 * c3 + s1 * s3, r4 = c1 * c2, r5 = c1 * s2 * s3 - s1 * c3;
+    float r6 = s1 * s2 * c3 - c1 * s3, r7 = s1 * c2, r8 = s1 * s2 * s3 + c1 * c3;
+    // d/d angle1: rows 1 and 2 rotate into each other
+    de[0] = g[6] * r3 + g[7] * r4 + g[8] * r5 - g[3] * r6 - g[4] * r7 - g[5] * r8;
+    // d/d angle2 (= e[2])
+    de[2] = -g[0] * s2 * c3 - g[1] * c2 - g[2] * s2 * s3
+            + g[3] * c1 * c2 * c3 - g[4] * c1 * s2 + g[5] * c1 * c2 * s3
+            + g[6] * s1 * c2 * c3 - g[7] * s1 * s2 + g[8] * s1 * c2 * s3;
+    // d/d angle3 (= e[1])
+    de[1] = -g[0] * c2 * s3 + g[2] * c2 * c3
+            + g[3] * (s1 * c3 - c1 * s2 * s3) + g[5] * (c1 * s2 * c3 + s1 * s3)
+            - g[6] * (s1 * s2 * s3 + c1 * c3) + g[8] * (s1 * s2 * c3 - c1 * s3);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Distances on SO(3).  tr(A B^T) = tr(A^T B) = sum_ij A_ij B_ij, so one inner product serves
+// compute_geodesic_distance_from_two_matrices (rotation_representation.py:209-227, m1 m2^T),
+// angle_error (:230-242, R1^T R2, float64, degrees) and geodesic (point_cloud/main.py:61-73).
+PE_DEV float dot9(const float* a, const float* b) {
+    float s = a[0] * b[0];
+#pragma unroll
+    for (int i = 1; i < 9; ++i) s = fmaf(a[i], b[i], s);
+    return s;
+}
+PE_DEV double dot9_f64(const float* a, const float* b) {
+    double s = 0.0;
+#pragma unroll
+    for (int i = 0; i < 9; ++i) s = fma((double)a[i], (double)b[i], s);
+    return s;
+}
+// per-matrix Frobenius distance |A - B|_F (loss_frobenius, Comparison/main.py:12-16, before the batch mean)
+PE_DEV float frob_dist(const float* a, const float* b) {
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 9; ++i) { float d = a[i] - b[i]; s = fmaf(d, d, s); }
+    return sqrtf(s);
+}
+
+}  // namespace pe

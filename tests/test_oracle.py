@@ -1,0 +1,123 @@
+"""The oracle (oracle/reference_port.py) against outputs of the UNMODIFIED reference (tests/golden/*.npz,
+made by tests/golden/make_golden.py in a container that has /root/reference).  CPU only."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import reference_port as O
+
+T = lambda a: torch.from_numpy(np.asarray(a))
+
+
+def _fwd_bwd(fn, x, g):
+    x = T(x).double().requires_grad_(True)
+    y = fn(x)
+    (dx,) = torch.autograd.grad(y, x, T(g).double())
+    return y.detach().numpy(), dx.numpy()
+
+
+@pytest.mark.parametrize("name,fn,tol", [
+    ("ortho6d", O.compute_rotation_matrix_from_ortho6d, 1e-12),
+    ("quaternion", O.compute_rotation_matrix_from_quaternion, 1e-12),
+    ("euler", O.compute_rotation_matrix_from_euler, 1e-12),
+    ("expmap", O.vec_3d_to_SO3, 1e-12),
+    # the reference's stereographic_unproject round-trips through a float32 buffer (rotation_representation.py:84)
+    ("ortho5d", O.compute_rotation_matrix_from_ortho5d, 5e-6),
+])
+def test_maps_match_reference(golden, name, fn, tol):
+    z = golden(name)
+    r, dx = _fwd_bwd(fn, z["x"], z["g"])
+    assert np.abs(r - z["r"]).max() <= tol
+    scale = np.abs(z["dx"]).max(axis=-1, keepdims=True) + 1e-300
+    assert (np.abs(dx - z["dx"]) / scale).max() <= max(tol, 1e-10) * 10
+
+
+def test_svd_orth_matches_reference(golden):
+    z = golden("svd_orth")
+    r, dx = _fwd_bwd(O.symmetric_orthogonalization, z["x"], z["g"])
+    assert np.abs(r - z["r"]).max() <= 1e-12
+    det = O.svd_orth_det_sign(T(z["x"]).double()).numpy()
+    assert np.array_equal(np.sign(det), np.sign(z["det"]))
+    # autograd through torch.svd is noisy near repeated singular values: compare where it is not
+    s = z["s"]
+    ok = (np.minimum(s[:, 0] - s[:, 1], s[:, 1] - s[:, 2]) / s[:, 0] > 1e-3)
+    rel = np.abs(dx - z["dx"]).reshape(len(s), -1).max(1) / (np.abs(z["dx"]).reshape(len(s), -1).max(1) + 1e-300)
+    assert rel[ok].max() <= 1e-8
+
+
+def test_svd_orth_closed_form_pullback_matches_reference_autograd(golden):
+    z = golden("svd_orth")
+    x, g = T(z["x"]), T(z["g"])
+    dm = O.svd_orth_pullback(x, g).numpy()
+    s = z["s"]
+    d = np.sign(z["det"])
+    cond = O.svd_orth_conditioning(x).numpy()
+    gap = np.minimum(s[:, 0] - s[:, 1], s[:, 1] - s[:, 2]) / s[:, 0]
+    ok = (cond > 1e-3) & (gap > 1e-3)
+    ref = z["dx"].reshape(-1, 3, 3)
+    rel = np.abs(dm - ref).reshape(len(s), -1).max(1) / (np.abs(ref).reshape(len(s), -1).max(1) + 1e-300)
+    assert ok.sum() > 500
+    assert rel[ok].max() <= 1e-7
+    assert d.min() == -1 and d.max() == 1          # both determinant signs are exercised
+
+
+def test_svd_orth_known_answers(golden):
+    z = golden("svd_orth")
+    n = int(z["n_random"])
+    x = T(z["x"]).double()
+    r = O.symmetric_orthogonalization(x).numpy()
+    assert np.allclose(r[n], np.eye(3), atol=1e-14)                      # identity -> identity
+    assert abs(np.linalg.det(r[n + 1]) - 1) < 1e-12                      # diag(1,1,-1) -> proper rotation
+    rots = z["x"][n + 3:n + 3 + 64].reshape(-1, 3, 3)                    # rotations map to themselves
+    assert np.abs(r[n + 3:n + 3 + 64] - rots).max() < 1e-6               # (inputs are fp32-rounded rotations)
+    assert np.allclose(np.linalg.det(r), 1.0, atol=1e-9)
+    assert np.abs(r @ r.transpose(0, 2, 1) - np.eye(3)).max() < 1e-9
+
+
+def test_euler_matches_getR(golden):
+    z = golden("euler_getR")
+    r = O.compute_rotation_matrix_from_euler(T(z["x"]).double()).numpy()
+    assert np.abs(r - z["r"]).max() < 1e-14
+
+
+def test_distances_match_reference(golden):
+    z = golden("distances")
+    r1, r2, direct = T(z["r1"]), T(z["r2"]), T(z["direct"])
+    assert np.abs(O.compute_geodesic_distance_from_two_matrices(r1.double(), r2.double()).numpy() - z["geo_rr"]).max() < 1e-12
+    assert np.abs(O.compute_geodesic_distance_from_two_matrices(direct.double(), r2.double()).numpy()
+                  - z["geo_rr_direct"]).max() < 1e-12
+    ae = O.angle_error(r1, r2)
+    assert ae.dtype == torch.float64
+    assert np.abs(ae.numpy() - z["angle_error"]).max() < 1e-10
+    assert np.abs(O.angle_error(direct, r2).numpy() - z["angle_error_direct"]).max() < 1e-10
+    for red in ("none", "mean", "sum"):
+        got = O.geodesic(r1.double(), r2.double(), red).numpy()
+        assert np.abs(got - z[f"geo_pc_{red}"]).max() < 1e-9
+    a = direct.double().requires_grad_(True)
+    b = r2.double().requires_grad_(True)
+    v = O.loss_frobenius(a, b)
+    ga, gb = torch.autograd.grad(v, (a, b))
+    assert abs(v.item() - float(z["frob"])) < 1e-14
+    assert np.abs(ga.numpy() - z["frob_grad_pred"]).max() < 1e-14
+    assert np.abs(gb.numpy() - z["frob_grad_true"]).max() < 1e-14
+    assert bool(z["angle_error_raises_bad"])
+    with pytest.raises(ValueError):
+        O.angle_error(T(z["bad"]), r2[:4])
+
+
+def test_kabsch_recovers_reference_rotation(golden):
+    z = golden("kabsch_kat")
+    r, t = O.kabsch(T(z["pc1"]), T(z["pc2"]))
+    assert np.abs(r.numpy() - z["gt_rmat"]).max() < 1e-5                 # inputs are fp32 products
+    assert np.abs(t.numpy()).max() < 1e-5
+    # with a translation and an offset far from the origin
+    shift = torch.tensor([10.0, -7.0, 3.0])
+    r2, t2 = O.kabsch(T(z["pc1"]).double() + 5.0, T(z["pc2"]).double() + shift)
+    assert np.abs(r2.numpy() - z["gt_rmat"]).max() < 1e-5
+
+
+def test_sampler_gives_rotations():
+    g = torch.Generator().manual_seed(0)
+    r = O.sample_rotations_axis_angle(64, g).numpy()
+    assert np.abs(r @ r.transpose(0, 2, 1) - np.eye(3)).max() < 1e-12
+    assert np.allclose(np.linalg.det(r), 1.0)
