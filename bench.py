@@ -1,0 +1,350 @@
+#!/usr/bin/env python
+"""Benchmark of the rotation-mapping hot path.  Contract: one JSON line on stdout (rank 0).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--n MATRICES_PER_GPU] [--impl native|reference]
+
+Metric (BASELINE.json): 3x3 SVD orthogonalisations per second, forward + backward.
+A *step* is one pass of the reference's training step over one resident batch (Comparison/main.py:59-62,
+UPNA/main.py:54-58):  loss = loss_frobenius(symmetric_orthogonalization(x), R_true);  loss.backward()
+as two kernels through the C ABI - forward (reads x, R_true; sum of norms) and backward (reads x, R_true; writes
+dL/dx) - plus, for N > 1, one NCCL all-reduce of the loss sum between them.  180 algorithmic bytes per matrix.
+
+  value        whole-job matrices/s with x, R_true resident in HBM (CUDA events, max over ranks)
+  e2e          same step through the public API (rotation_representation.svd_frobenius_loss + autograd) with HOST
+               pinned inputs: H2D of x and R_true and D2H of the loss inside the timed region
+  roofline     dominant kernel (backward): algorithmic bytes / event-timed duration vs MEASURED_PEAKS.json
+  cpu_baseline the oracle port (= the reference's torch code) in fp32 on this box's host cores, bounded sample
+  --impl reference   times that CPU implementation as the headline instead (rank 0 only)
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "svd_orthogonalizations_per_sec_fwd_bwd"
+UNIT = "matrices/s"
+BYTES_FWD, BYTES_BWD = 72, 108            # algorithmic bytes per matrix per launch
+N_DEFAULT = 1 << 24                       # BASELINE config 2: 16M matrices on one B200
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--n", type=int, default=N_DEFAULT, help="matrices per GPU")
+    ap.add_argument("--impl", default="native", choices=["native", "reference"])
+    ap.add_argument("--cpu-sample", type=int, default=1 << 18, help="matrices per CPU-baseline pass")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons while the timed region runs (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-i", str(self.index), "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [t.strip() for t in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def measured_peak_gbs():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except (KeyError, ValueError):
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+def cpu_reference_pass(n: int, threads: int, reps: int):
+    """The reference's CPU implementation of the step (oracle port = the reference's torch calls), fp32.
+    -> (best seconds per pass, matrices per pass)"""
+    import torch
+    from oracle import reference_port as O
+    torch.set_num_threads(threads)
+    g = torch.Generator().manual_seed(0)
+    x = torch.randn(n, 9, generator=g)
+    r_true = O.symmetric_orthogonalization(torch.randn(n, 9, generator=g))
+    best = float("inf")
+    for _ in range(reps):
+        xr = x.clone().requires_grad_(True)
+        t0 = time.perf_counter()
+        loss = O.loss_frobenius(O.symmetric_orthogonalization(xr), r_true)
+        loss.backward()
+        best = min(best, time.perf_counter() - t0)
+    return best, n
+
+
+def run_reference(args):
+    """--impl reference: the CPU implementation is the thing measured.  Rank 0 only."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    import torch
+    cores = os.cpu_count() or 1
+    from oracle import reference_port as O
+    torch.set_num_threads(cores)
+    n = args.cpu_sample
+    g = torch.Generator().manual_seed(0)
+    x = torch.randn(n, 9, generator=g)
+    r_true = O.symmetric_orthogonalization(torch.randn(n, 9, generator=g))
+
+    def step():
+        xr = x.clone().requires_grad_(True)
+        O.loss_frobenius(O.symmetric_orthogonalization(xr), r_true).backward()
+
+    for _ in range(max(args.warmup, 1)):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    dt = (time.perf_counter() - t0) / args.steps
+    val = n / dt
+    sample = f"{n} matrices per step (bounded sample of the {args.n}-matrix workload; CPU throughput is flat in n)"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "svd_orth+frobenius fwd+bwd (reference torch code on host cores)",
+                   "matrices_per_step": n},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
+                         "sample": sample},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+def run_native(args):
+    import torch
+    import torch.distributed as dist
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device - the native arm has no CPU path")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    from poseestimation_b200 import _lib, launch_count
+    import poseestimation_b200.rotation_representation as rr
+    lib, check = _lib.lib, _lib.check
+
+    n = args.n
+    gen = torch.Generator(device=dev).manual_seed(rank)
+    x = torch.randn(n, 9, device=dev, generator=gen)
+    r_true = rr.symmetric_orthogonalization(torch.randn(n, 9, device=dev, generator=gen)).reshape(n, 9).contiguous()
+    dx = torch.empty(n, 9, device=dev)
+    r_out = torch.empty(n, 9, device=dev)
+    g_up = torch.randn(n, 9, device=dev, generator=gen)
+    loss_sum = torch.zeros(3, dtype=torch.float64, device=dev)     # [sum |.|_F, (spare), count] - the all-reduced vector
+    gout = torch.ones(1, dtype=torch.float32, device=dev)
+    inv_n_global = 1.0 / (n * world)
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def k_fwd():
+        check(lib.pe_svd_orth_frobenius_fwd(x.data_ptr(), 9, r_true.data_ptr(), None, loss_sum.data_ptr(), n, stream),
+              "fwd")
+
+    def k_bwd():
+        check(lib.pe_svd_orth_frobenius_bwd(x.data_ptr(), 9, r_true.data_ptr(), gout.data_ptr(), inv_n_global,
+                                            dx.data_ptr(), n, stream), "bwd")
+
+    def step():
+        k_fwd()
+        if world > 1:
+            dist.all_reduce(loss_sum)        # 24 bytes; the backward does not depend on it (1/B_global is known)
+        k_bwd()
+
+    def sync_all():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    sync_all()
+
+    # ---- timed region: K steps, device-timed, with per-kernel events for the roofline -----------------------------
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.25)
+    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(args.steps)]
+    launches0 = launch_count()
+    sync_all()
+    t_begin = torch.cuda.Event(enable_timing=True)
+    t_end = torch.cuda.Event(enable_timing=True)
+    t_begin.record()
+    for i in range(args.steps):
+        ev[i][0].record()
+        k_fwd()
+        ev[i][1].record()
+        if world > 1:
+            dist.all_reduce(loss_sum)
+        k_bwd()
+        ev[i][2].record()
+    t_end.record()
+    sync_all()
+    launches = launch_count() - launches0
+    total_ms = t_begin.elapsed_time(t_end)
+    fwd_ms = statistics.mean(e[0].elapsed_time(e[1]) for e in ev)
+    bwd_ms = statistics.mean(e[1].elapsed_time(e[2]) for e in ev)     # includes the 24-byte all-reduce when N > 1
+    clocks = sampler.stop() if rank == 0 else None
+    loss_value = float(loss_sum[0].item()) * inv_n_global
+
+    t = torch.tensor([total_ms, fwd_ms, bwd_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms, fwd_ms, bwd_ms = (float(v) for v in t.tolist())
+    ms_per_step = total_ms / args.steps
+    value = n * world / (ms_per_step * 1e-3)
+
+    # ---- explanation lines: the unfused pair svd_orth_fwd / svd_orth_bwd (saved R and recompute) -------------------
+    def time_kernel(fn, reps=10):
+        fn(); torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(reps):
+            fn()
+        b.record(); torch.cuda.synchronize()
+        return a.elapsed_time(b) / reps
+
+    also = {}
+    if rank == 0:
+        also["svd_orth_fwd_ms"] = time_kernel(lambda: check(lib.pe_svd_orth_fwd(
+            x.data_ptr(), 9, r_out.data_ptr(), None, n, stream), "f"))
+        also["svd_orth_bwd_savedR_ms"] = time_kernel(lambda: check(lib.pe_svd_orth_bwd(
+            x.data_ptr(), 9, r_out.data_ptr(), g_up.data_ptr(), dx.data_ptr(), n, stream), "b"))
+        also["svd_orth_bwd_recompute_ms"] = time_kernel(lambda: check(lib.pe_svd_orth_bwd(
+            x.data_ptr(), 9, None, g_up.data_ptr(), dx.data_ptr(), n, stream), "b"))
+        also["fused_fwd_ms"], also["fused_bwd_ms"] = fwd_ms, bwd_ms
+        also["loss"] = loss_value
+
+    # ---- e2e: public API, host-resident inputs ---------------------------------------------------------------------
+    e2e = None
+    if not args.no_e2e:
+        hx = torch.randn(n, 9).pin_memory()
+        ht = r_true.cpu().pin_memory()
+        hloss = torch.empty((), dtype=torch.float32).pin_memory()
+
+        def e2e_step():
+            xd = hx.to(dev, non_blocking=True).requires_grad_(True)
+            td = ht.to(dev, non_blocking=True)
+            loss = rr.svd_frobenius_loss(xd, td)
+            loss.backward()
+            hloss.copy_(loss.detach(), non_blocking=True)
+            return xd.grad
+
+        for _ in range(2):
+            e2e_step()
+        sync_all()
+        k = max(3, min(args.steps, 5))
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(k):
+            e2e_step()
+        b.record()
+        sync_all()
+        te = torch.tensor([a.elapsed_time(b) / k], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(te, op=dist.ReduceOp.MAX)
+        e2e = {"value": n * world / (float(te.item()) * 1e-3), "unit": UNIT,
+               "h2d_bytes_per_step": 2 * n * 36, "d2h_bytes_per_step": 4, "ms_per_step": float(te.item()),
+               "api": "rotation_representation.svd_frobenius_loss(x, R_true).backward()"}
+        del hx, ht
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    peak, peak_src = measured_peak_gbs()
+    achieved = BYTES_BWD * n / (bwd_ms * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": "stream_tma_kernel<SvdFrobBwd> (pe_svd_orth_frobenius_bwd)",
+                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                "peak_source": peak_src, "bytes_per_matrix": BYTES_BWD, "ms": bwd_ms,
+                "step_frac": (BYTES_FWD + BYTES_BWD) * n / (ms_per_step * 1e-3) / 1e9 / peak}
+
+    cpu = None
+    if not args.no_cpu_baseline:
+        cores = os.cpu_count() or 1
+        sec, m = cpu_reference_pass(args.cpu_sample, cores, reps=3)
+        cpu = {"value": m / sec, "unit": UNIT, "cores": cores, "kind": "port",
+               "sample": f"{m} matrices x 3 passes (best), fp32, oracle port = the reference's torch calls"}
+
+    print(json.dumps({
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": {"workload": f"svd_orth+frobenius fwd+bwd, {n} random 3x3 fp32 matrices per GPU (BASELINE config 2)",
+                   "matrices_per_gpu": n, "l2": "inputs (2 x %.0f MB) larger than the 126 MB L2" % (n * 36 / 1e6),
+                   "collective": "ncclAllReduce(3 x f64) per step" if world > 1 else "none"},
+        "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
+        "also": also,
+    }))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse_args()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_native(a)

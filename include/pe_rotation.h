@@ -1,0 +1,115 @@
+/* libpe_rotation.so - C ABI of the B200-native rotation-mapping path.
+ *
+ * The reference (henrikgruner/PoseEstimation) has no FFI: its boundary is the Python function names of
+ * rotation_representation.py, loss.py and point_cloud/main.py.  Each entry point below is what a binding for one
+ * of those functions calls; the comment above it names the reference function it replaces (paths relative to
+ * /root/reference).  INTEGRATION.md shows the ctypes stub for each.
+ *
+ * Conventions (all entry points):
+ *   - every pointer is a DEVICE pointer into memory the caller owns (PyTorch's allocator); the library allocates
+ *     nothing and keeps no state between calls;
+ *   - a "matrix" is 9 consecutive floats, row-major: m[3*i + j] = M[i][j]  (x.view(-1, 3, 3));
+ *   - `n` is the number of records (matrices / vectors); n == 0 is a no-op that still zeroes accumulators;
+ *   - `*_stride` is the distance in FLOATS between consecutive input records (9 for a dense (n, 9) array, 12 for
+ *     the out[:, :9] view of a (n, 12) network output); outputs are always dense;
+ *   - `stream` is a cudaStream_t passed as void*; all work is enqueued on it, nothing synchronises;
+ *   - accumulators (`double* sum`, `int* flag`) are zeroed by the call on `stream`, then added to;
+ *   - return value: 0 = success, > 0 = a cudaError_t from the launch, < 0 = PE_ERR_* below;
+ *     pe_last_error() gives a message for the calling thread's last non-zero return;
+ *   - there is no CPU path: without an sm_100 device every compute entry point fails.
+ */
+#ifndef PE_ROTATION_H
+#define PE_ROTATION_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PE_VERSION 100 /* 0.1.0 */
+
+#define PE_ERR_BAD_ARG (-1)   /* null pointer, negative count, stride smaller than the record */
+#define PE_ERR_NO_DEVICE (-2) /* current device is not sm_100 */
+#define PE_ERR_INTERNAL (-3)
+
+int pe_version(void);
+const char* pe_last_error(void);
+/* kernels launched by this process through the library so far (bench.py's gpu_launches) */
+long long pe_launch_count(void);
+
+/* ---- a1  symmetric_orthogonalization(x)                 rotation_representation.py:192-206 ------------------
+ * r[n][9] = U diag(1, 1, det(U V^T)) V^T with m = U S V^T.  det_sign (nullable, n floats) receives the factor
+ * det(U V^T) = +-1 of line 202. */
+int pe_svd_orth_fwd(const float* m, int64_t m_stride, float* r, float* det_sign, int64_t n, void* stream);
+/* autograd through lines 199-205 (torch's svd_backward, det_backward, ...), as one closed-form pullback:
+ * dm = dL/dm given g = dL/dr.  `r` is the forward output; pass NULL to have it recomputed from m. */
+int pe_svd_orth_bwd(const float* m, int64_t m_stride, const float* r, const float* g, float* dm, int64_t n,
+                    void* stream);
+
+/* ---- a2  compute_rotation_matrix_from_ortho6d(poses)    rotation_representation.py:21-36 (= 174-189) -------- */
+int pe_ortho6d_fwd(const float* p, int64_t p_stride, float* r, int64_t n, void* stream);
+int pe_ortho6d_bwd(const float* p, int64_t p_stride, const float* g, float* dp, int64_t n, void* stream);
+
+/* ---- a3  compute_rotation_matrix_from_quaternion(q)     rotation_representation.py:139-172 (+ 38-50) -------- */
+int pe_quat_fwd(const float* q, int64_t q_stride, float* r, int64_t n, void* stream);
+int pe_quat_bwd(const float* q, int64_t q_stride, const float* g, float* dq, int64_t n, void* stream);
+
+/* ---- a4  compute_rotation_matrix_from_euler(euler)      rotation_representation.py:92-115 -------------------- */
+int pe_euler_fwd(const float* e, int64_t e_stride, float* r, int64_t n, void* stream);
+int pe_euler_bwd(const float* e, int64_t e_stride, const float* g, float* de, int64_t n, void* stream);
+
+/* ---- 8(f).1  compute_rotation_matrix_from_ortho5d(a)    rotation_representation.py:72-90, 120-136 ------------ */
+int pe_ortho5d_fwd(const float* a, int64_t a_stride, float* r, int64_t n, void* stream);
+int pe_ortho5d_bwd(const float* a, int64_t a_stride, const float* g, float* da, int64_t n, void* stream);
+
+/* ---- 8(f).1  vec_3d_to_SO3(x) = so3_exp_map(x)          rotation_representation.py:245-320 ------------------- */
+int pe_expmap_fwd(const float* v, int64_t v_stride, float* r, int64_t n, void* stream);
+int pe_expmap_bwd(const float* v, int64_t v_stride, const float* g, float* dv, int64_t n, void* stream);
+
+/* ---- a5  loss_frobenius(R_pred, R_true)                 Comparison/main.py:12-16 (+ 7 copies) ----------------
+ * *sum = sum_b |a_b - b_b|_F (the caller divides by n: the mean of line 16; across ranks the sums all-reduce). */
+int pe_frobenius_fwd(const float* a, const float* b, double* sum, int64_t n, void* stream);
+/* da = gscale * (a - b)/|a - b|_F, db = -da, with gscale = (*gout) * inv_n; 0 where the norm is 0.
+ * gout is a device scalar (the upstream gradient of the 0-d loss); da or db may be NULL. */
+int pe_frobenius_bwd(const float* a, const float* b, const float* gout, float inv_n, float* da, float* db,
+                     int64_t n, void* stream);
+
+/* ---- a6  compute_geodesic_distance_from_two_matrices    rotation_representation.py:209-227  (lo, hi = -1, 1)
+ * ---- a8  geodesic(R1, R2, reduction)                    point_cloud/main.py:61-73   (lo, hi = -1+1e-7, 1-1e-7)
+ * theta_b = acos(clamp((tr(m1_b m2_b^T) - 1)/2, lo, hi)) in radians.  theta (n floats) and sum are each
+ * nullable; sum receives sum_b theta_b. */
+int pe_geodesic_fwd(const float* m1, const float* m2, float lo, float hi, float* theta, double* sum, int64_t n,
+                    void* stream);
+/* g: n upstream gradients (g_is_scalar = 0) or one device scalar broadcast to all records, times gmul
+ * (reduction='mean': g_is_scalar = 1, gmul = 1/n).  d1 or d2 may be NULL.  Gradient is 0 where the clamp is
+ * active, as torch.clamp's is. */
+int pe_geodesic_bwd(const float* m1, const float* m2, float lo, float hi, const float* g, int g_is_scalar,
+                    float gmul, float* d1, float* d2, int64_t n, void* stream);
+
+/* ---- a7  angle_error(R1, R2)                            rotation_representation.py:230-242 -------------------
+ * float64 arithmetic on float32 inputs: deg_b = acos(clamp((tr(r1_b^T r2_b) - 1)/2, -1, 1)) * 180/pi.
+ * deg (n doubles) and sum are each nullable.  *flag becomes non-zero if any cosine lies outside [-1.1, 1.1]:
+ * the binding raises ValueError (line 238). */
+int pe_angle_error_fwd(const float* r1, const float* r2, double* deg, double* sum, int* flag, int64_t n,
+                       void* stream);
+
+/* ---- fused training step: loss_frobenius(symmetric_orthogonalization(x), R_true) -------------------------------
+ * Comparison/main.py:59-62, UPNA/main.py:54-58, 3D-Pose/main.py:60,85-86.
+ * fwd: r (nullable) as pe_svd_orth_fwd, *sum = sum_b |r_true_b - r_b|_F.
+ * bwd: dm = pullback of gscale * (r - r_true)/|r - r_true|_F through the orthogonalisation, recomputing r from
+ *      m, with gscale = (*gout) * inv_n. */
+int pe_svd_orth_frobenius_fwd(const float* m, int64_t m_stride, const float* r_true, float* r, double* sum,
+                              int64_t n, void* stream);
+int pe_svd_orth_frobenius_bwd(const float* m, int64_t m_stride, const float* r_true, const float* gout,
+                              float inv_n, float* dm, int64_t n, void* stream);
+
+/* ---- a9  Kabsch alignment - no reference function (site: point_cloud/main.py:171-181) --------------------------
+ * p, q: (b, npts, 3) dense.  r[b][9] = the rotation minimising sum_k |R p_k + t - q_k|^2, i.e.
+ * pe_svd_orth of sum_k (q_k - qbar)(p_k - pbar)^T;  t (nullable, b x 3) = qbar - R pbar. */
+int pe_kabsch_fwd(const float* p, const float* q, int64_t b, int64_t npts, float* r, float* t, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PE_ROTATION_H */

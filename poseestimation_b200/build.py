@@ -1,0 +1,53 @@
+"""Build ``libpe_rotation.so`` in-tree for sm_100a:  ``python -m poseestimation_b200.build [-v]``.
+
+nvcc cross-compiles without a GPU.  The library is git-ignored (source-only history) but travels to the GPU box with
+the working-tree snapshot.
+"""
+from __future__ import annotations
+
+import os
+import shutil
+import subprocess
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(HERE, "csrc")
+SOURCES = ["pe_api.cu", "pe_kabsch.cu"]
+HEADERS = ["pe_common.h", "pe_math.cuh", "pe_stage.cuh", "pe_stream.cuh", "pe_ops.cuh",
+           os.path.join("..", "..", "include", "pe_rotation.h")]
+OUT = os.path.join(HERE, "libpe_rotation.so")
+ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
+
+
+def nvcc() -> str:
+    exe = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+    if not os.path.exists(exe):
+        raise RuntimeError("nvcc not found")
+    return exe
+
+
+def up_to_date() -> bool:
+    if not os.path.exists(OUT):
+        return False
+    t = os.path.getmtime(OUT)
+    deps = [os.path.join(CSRC, s) for s in SOURCES + HEADERS] + [os.path.abspath(__file__)]
+    return all(os.path.getmtime(d) <= t for d in deps)
+
+
+def build(force: bool = False, verbose: bool = False) -> str:
+    if not force and up_to_date():
+        return OUT
+    cmd = [nvcc(), "-O3", "-std=c++17", *ARCH, "-lineinfo", "-Xcompiler", "-fPIC", "-shared",
+           *[os.path.join(CSRC, s) for s in SOURCES], "-o", OUT]
+    if verbose:
+        cmd[1:1] = ["-Xptxas", "-v"]
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if verbose or res.returncode != 0:
+        sys.stderr.write(res.stdout + res.stderr)
+    if res.returncode != 0:
+        raise RuntimeError("nvcc failed building libpe_rotation.so")
+    return OUT
+
+
+if __name__ == "__main__":
+    print(build(force="-f" in sys.argv or "--force" in sys.argv, verbose="-v" in sys.argv))

@@ -1,0 +1,126 @@
+// extern "C" entry points of libpe_rotation.so (declared in include/pe_rotation.h) for the per-record ops.
+#include "pe_ops.cuh"
+
+using namespace pe;
+
+namespace {
+
+template <class Op>
+Params<Op> make_params(const float* i0, long long stride0, const float* i1, const float* i2, float* o0, float* o1,
+                       long long n, double* sums, int* flag, typename Op::Extra ex) {
+    Params<Op> p;
+    p.in[0] = i0; p.in[1] = i1; p.in[2] = i2;
+    p.out[0] = o0; p.out[1] = o1;
+    p.n = n;
+    p.in0_stride = stride0;
+    p.sums = sums;
+    p.flag = flag;
+    p.ex = ex;
+    return p;
+}
+
+template <class Op>
+int run(const float* i0, long long stride0, const float* i1, const float* i2, float* o0, float* o1, long long n,
+        double* sums, int* flag, typename Op::Extra ex, void* stream) {
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (n < 0) return fail(PE_ERR_BAD_ARG, "negative record count");
+    if (Op::NRED > 0) {
+        if (!sums) return fail(PE_ERR_BAD_ARG, "null accumulator pointer");
+        cudaError_t e = cudaMemsetAsync(sums, 0, sizeof(double) * Op::NRED, st);
+        if (e != cudaSuccess) return fail_cuda(e, "cudaMemsetAsync(sum)");
+    }
+    if (Op::FLAG) {
+        if (!flag) return fail(PE_ERR_BAD_ARG, "null flag pointer");
+        cudaError_t e = cudaMemsetAsync(flag, 0, sizeof(int), st);
+        if (e != cudaSuccess) return fail_cuda(e, "cudaMemsetAsync(flag)");
+    }
+    return stream_launch<Op>(make_params<Op>(i0, stride0, i1, i2, o0, o1, n, sums, flag, ex), st);
+}
+
+}  // namespace
+
+extern "C" {
+
+int pe_version(void) { return PE_VERSION; }
+const char* pe_last_error(void) { return last_error_buf(); }
+long long pe_launch_count(void) { return launch_counter().load(); }
+
+int pe_svd_orth_fwd(const float* m, int64_t m_stride, float* r, float* det_sign, int64_t n, void* stream) {
+    if (det_sign) return run<SvdFwd<true>>(m, m_stride, nullptr, nullptr, r, det_sign, n, nullptr, nullptr, {}, stream);
+    return run<SvdFwd<false>>(m, m_stride, nullptr, nullptr, r, nullptr, n, nullptr, nullptr, {}, stream);
+}
+int pe_svd_orth_bwd(const float* m, int64_t m_stride, const float* r, const float* g, float* dm, int64_t n,
+                    void* stream) {
+    if (r) return run<SvdBwdSaved>(m, m_stride, r, g, dm, nullptr, n, nullptr, nullptr, {}, stream);
+    return run<SvdBwdRecompute>(m, m_stride, g, nullptr, dm, nullptr, n, nullptr, nullptr, {}, stream);
+}
+
+#define PE_MAP_API(fn, Tag)                                                                                      \
+    int pe_##fn##_fwd(const float* x, int64_t stride, float* r, int64_t n, void* stream) {                       \
+        return run<Tag##Fwd>(x, stride, nullptr, nullptr, r, nullptr, n, nullptr, nullptr, {}, stream);          \
+    }                                                                                                            \
+    int pe_##fn##_bwd(const float* x, int64_t stride, const float* g, float* dx, int64_t n, void* stream) {      \
+        return run<Tag##Bwd>(x, stride, g, nullptr, dx, nullptr, n, nullptr, nullptr, {}, stream);               \
+    }
+PE_MAP_API(ortho6d, Ortho6d)
+PE_MAP_API(quat, Quat)
+PE_MAP_API(euler, Euler)
+PE_MAP_API(ortho5d, Ortho5d)
+PE_MAP_API(expmap, Expmap)
+
+int pe_frobenius_fwd(const float* a, const float* b, double* sum, int64_t n, void* stream) {
+    return run<FrobFwd>(a, 9, b, nullptr, nullptr, nullptr, n, sum, nullptr, {}, stream);
+}
+int pe_frobenius_bwd(const float* a, const float* b, const float* gout, float inv_n, float* da, float* db,
+                     int64_t n, void* stream) {
+    if (!gout) return fail(PE_ERR_BAD_ARG, "null upstream-gradient pointer");
+    if (da && db) return run<FrobBwd<true>>(a, 9, b, nullptr, da, db, n, nullptr, nullptr, {gout, inv_n}, stream);
+    if (da) return run<FrobBwd<false>>(a, 9, b, nullptr, da, nullptr, n, nullptr, nullptr, {gout, inv_n}, stream);
+    if (db) return run<FrobBwd<false>>(a, 9, b, nullptr, db, nullptr, n, nullptr, nullptr, {gout, -inv_n}, stream);
+    return fail(PE_ERR_BAD_ARG, "both gradient outputs are null");
+}
+
+int pe_geodesic_fwd(const float* m1, const float* m2, float lo, float hi, float* theta, double* sum, int64_t n,
+                    void* stream) {
+    Clamp c{lo, hi};
+    if (theta && sum) return run<GeoFwd<true, true>>(m1, 9, m2, nullptr, theta, nullptr, n, sum, nullptr, c, stream);
+    if (theta) return run<GeoFwd<true, false>>(m1, 9, m2, nullptr, theta, nullptr, n, nullptr, nullptr, c, stream);
+    if (sum) return run<GeoFwd<false, true>>(m1, 9, m2, nullptr, nullptr, nullptr, n, sum, nullptr, c, stream);
+    return fail(PE_ERR_BAD_ARG, "both outputs are null");
+}
+int pe_geodesic_bwd(const float* m1, const float* m2, float lo, float hi, const float* g, int g_is_scalar,
+                    float gmul, float* d1, float* d2, int64_t n, void* stream) {
+    if (!g) return fail(PE_ERR_BAD_ARG, "null upstream-gradient pointer");
+    GeoGrad ex{lo, hi, gmul, g};
+    const float* gv = g_is_scalar ? nullptr : g;
+#define PE_GEO(MODE, O0, O1)                                                                                   \
+    (g_is_scalar ? run<GeoBwd<MODE, true>>(m1, 9, m2, nullptr, O0, O1, n, nullptr, nullptr, ex, stream)        \
+                 : run<GeoBwd<MODE, false>>(m1, 9, m2, gv, O0, O1, n, nullptr, nullptr, ex, stream))
+    if (d1 && d2) return PE_GEO(2, d1, d2);
+    if (d1) return PE_GEO(0, d1, nullptr);
+    if (d2) return PE_GEO(1, d2, nullptr);
+#undef PE_GEO
+    return fail(PE_ERR_BAD_ARG, "both gradient outputs are null");
+}
+
+int pe_angle_error_fwd(const float* r1, const float* r2, double* deg, double* sum, int* flag, int64_t n,
+                       void* stream) {
+    float* d = reinterpret_cast<float*>(deg);
+    if (deg && sum) return run<AngleFwd<true, true>>(r1, 9, r2, nullptr, d, nullptr, n, sum, flag, {}, stream);
+    if (deg) return run<AngleFwd<true, false>>(r1, 9, r2, nullptr, d, nullptr, n, nullptr, flag, {}, stream);
+    if (sum) return run<AngleFwd<false, true>>(r1, 9, r2, nullptr, nullptr, nullptr, n, sum, flag, {}, stream);
+    return fail(PE_ERR_BAD_ARG, "both outputs are null");
+}
+
+int pe_svd_orth_frobenius_fwd(const float* m, int64_t m_stride, const float* r_true, float* r, double* sum,
+                              int64_t n, void* stream) {
+    if (r) return run<SvdFrobFwd<true>>(m, m_stride, r_true, nullptr, r, nullptr, n, sum, nullptr, {}, stream);
+    return run<SvdFrobFwd<false>>(m, m_stride, r_true, nullptr, nullptr, nullptr, n, sum, nullptr, {}, stream);
+}
+int pe_svd_orth_frobenius_bwd(const float* m, int64_t m_stride, const float* r_true, const float* gout,
+                              float inv_n, float* dm, int64_t n, void* stream) {
+    if (!gout) return fail(PE_ERR_BAD_ARG, "null upstream-gradient pointer");
+    return run<SvdFrobBwd>(m, m_stride, r_true, nullptr, dm, nullptr, n, nullptr, nullptr, {gout, inv_n}, stream);
+}
+
+}  // extern "C"

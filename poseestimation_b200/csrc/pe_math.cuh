@@ -316,7 +316,103 @@ PE_DEV void euler_pullback(const float* e, const float* g, float* de) {
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// Distances on SO(3).  tr(A B^T) = tr(A^T B) = sum_ij A_ij B_ij, so one inner product serves
+// 5D map (reference: compute_rotation_matrix_from_ortho5d + stereographic_unproject(axis=0),
+// rotation_representation.py:72-90, 120-136).  a[2:5] is scaled by (sqrt2+1, sqrt2+1, sqrt2), unprojected from
+// R^3 to the 3-sphere with the new coordinate in FRONT, divided by the norm of its last three coordinates, and
+// appended to a[0:2] to form the 6D input.
+PE_DEV void ortho5d_to_6d(const float* a, float* b, float* w, float& invD, float& k) {
+    const float c0 = 2.41421356237309515f, c2 = 1.41421356237309515f;
+    float s0 = a[2] * c0, s1 = a[3] * c0, s2 = a[4] * c2;
+    float ss = fmaf(s2, s2, fmaf(s1, s1, s0 * s0));
+    invD = 1.0f / (ss + 1.0f);
+    w[0] = (ss - 1.0f) * invD;
+    w[1] = 2.0f * s0 * invD; w[2] = 2.0f * s1 * invD; w[3] = 2.0f * s2 * invD;
+    k = rsqrt_nr(fmaf(w[3], w[3], fmaf(w[2], w[2], w[1] * w[1])));
+    b[0] = a[0]; b[1] = a[1];
+    b[2] = w[0] * k; b[3] = w[1] * k; b[4] = w[2] * k; b[5] = w[3] * k;
+}
+PE_DEV void ortho5d(const float* a, float* r) {
+    float b[6], w[4], invD, k;
+    ortho5d_to_6d(a, b, w, invD, k);
+    ortho6d(b, r);
+}
+PE_DEV void ortho5d_pullback(const float* a, const float* g, float* da) {
+    const float c0 = 2.41421356237309515f, c2 = 1.41421356237309515f;
+    float b[6], w[4], invD, k, db[6];
+    ortho5d_to_6d(a, b, w, invD, k);
+    ortho6d_pullback(b, g, db);
+    da[0] = db[0]; da[1] = db[1];
+    // u = w * k, k = 1/|w[1:]|
+    float dk = fmaf(db[5], w[3], fmaf(db[4], w[2], fmaf(db[3], w[1], db[2] * w[0])));
+    float dn = -dk * k * k * k;  // d|w[1:]| = -dk/|.|^2, then d w_j += dn * w_j/|.|
+    float dw0 = db[2] * k;
+    float dw1 = fmaf(dn, w[1], db[3] * k), dw2 = fmaf(dn, w[2], db[4] * k), dw3 = fmaf(dn, w[3], db[5] * k);
+    // w0 = 1 - 2/D, w_j = 2 s_j/D, D = |s|^2 + 1
+    float s0 = a[2] * c0, s1 = a[3] * c0, s2 = a[4] * c2;
+    float dots = fmaf(dw3, s2, fmaf(dw2, s1, dw1 * s0));
+    float q = 4.0f * invD * invD * (dw0 - dots);
+    da[2] = c0 * fmaf(q, s0, 2.0f * invD * dw1);
+    da[3] = c0 * fmaf(q, s1, 2.0f * invD * dw2);
+    da[4] = c2 * fmaf(q, s2, 2.0f * invD * dw3);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Exponential map (reference: vec_3d_to_SO3 -> so3_exp_map, rotation_representation.py:245-320).
+// theta = sqrt(max(|v|^2, 1e-4)); R = (sin theta/theta) K + ((1-cos theta)/theta^2) K^2 + I, K = hat(v).
+// K^2 = v v^T - |v|^2 I uses the UNclamped |v|^2, as the reference's bmm(K, K) does.
+constexpr float kExpEps = 1e-4f;
+PE_DEV void expmap_factors(const float* v, float& n2, float& th, float& f1, float& f2, float& sn, float& cs) {
+    n2 = fmaf(v[2], v[2], fmaf(v[1], v[1], v[0] * v[0]));
+    float c = fmaxf(n2, kExpEps);
+    float it = rsqrt_nr(c);
+    th = c * it;
+    sincos_f(th, &sn, &cs);
+    float sh, ch;
+    sincos_f(0.5f * th, &sh, &ch);
+    f1 = sn * it;
+    f2 = 2.0f * sh * sh * it * it;  // (1 - cos) / theta^2 without the cancellation
+}
+PE_DEV void expmap(const float* v, float* r) {
+    float n2, th, f1, f2, sn, cs;
+    expmap_factors(v, n2, th, f1, f2, sn, cs);
+    float x = v[0], y = v[1], z = v[2];
+    r[0] = fmaf(f2, x * x - n2, 1.0f); r[1] = fmaf(f2, x * y, -f1 * z);   r[2] = fmaf(f2, x * z, f1 * y);
+    r[3] = fmaf(f2, x * y, f1 * z);    r[4] = fmaf(f2, y * y - n2, 1.0f); r[5] = fmaf(f2, y * z, -f1 * x);
+    r[6] = fmaf(f2, x * z, -f1 * y);   r[7] = fmaf(f2, y * z, f1 * x);    r[8] = fmaf(f2, z * z - n2, 1.0f);
+}
+PE_DEV void expmap_pullback(const float* v, const float* g, float* dv) {
+    float n2, th, f1, f2, sn, cs;
+    expmap_factors(v, n2, th, f1, f2, sn, cs);
+    float x = v[0], y = v[1], z = v[2];
+    float a0 = g[7] - g[5], a1 = g[2] - g[6], a2 = g[3] - g[1];  // sum_ij G_ij dK_ij/dv
+    float tr = g[0] + g[4] + g[8];
+    // (G + G^T) v
+    float h0 = 2.0f * g[0] * x + (g[1] + g[3]) * y + (g[2] + g[6]) * z;
+    float h1 = (g[1] + g[3]) * x + 2.0f * g[4] * y + (g[5] + g[7]) * z;
+    float h2 = (g[2] + g[6]) * x + (g[5] + g[7]) * y + 2.0f * g[8] * z;
+    float df1 = fmaf(x, a0, fmaf(y, a1, z * a2));
+    float df2 = 0.5f * fmaf(x, h0, fmaf(y, h1, z * h2)) - n2 * tr;
+    float d0 = fmaf(f2, fmaf(-2.0f * tr, x, h0), f1 * a0);
+    float d1 = fmaf(f2, fmaf(-2.0f * tr, y, h1), f1 * a1);
+    float d2 = fmaf(f2, fmaf(-2.0f * tr, z, h2), f1 * a2);
+    if (n2 >= kExpEps) {  // torch.clamp passes the gradient only where the input is not below the bound
+        float t2 = th * th, p1, p2;  // p1 = f1'(theta)/theta, p2 = f2'(theta)/theta
+        if (th < 0.25f) {
+            p1 = -(1.0f / 3.0f) + t2 * ((1.0f / 30.0f) - t2 * (1.0f / 840.0f));
+            p2 = -(1.0f / 12.0f) + t2 * ((1.0f / 180.0f) - t2 * (1.0f / 6720.0f));
+        } else {
+            float it2 = 1.0f / t2;
+            p1 = (cs - f1) * it2;              // (theta cos - sin)/theta^3
+            p2 = (f1 - 2.0f * f2) * it2;       // (theta sin - 2(1 - cos))/theta^4
+        }
+        float sct = fmaf(df1, p1, df2 * p2);
+        d0 = fmaf(sct, x, d0); d1 = fmaf(sct, y, d1); d2 = fmaf(sct, z, d2);
+    }
+    dv[0] = d0; dv[1] = d1; dv[2] = d2;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Distances on SO(3). tr(A B^T) = tr(A^T B) = sum_ij A_ij B_ij, so one inner product serves
 // compute_geodesic_distance_from_two_matrices (rotation_representation.py:209-227, m1 m2^T),
 // angle_error (:230-242, R1^T R2, float64, degrees) and geodesic (point_cloud/main.py:61-73).
 PE_DEV float dot9(const float* a, const float* b) {

@@ -1,0 +1,203 @@
+// The per-record ops of the path, written against the streaming engine (pe_stream.cuh).
+// Each Op names the reference function it replaces; the math is in pe_math.cuh.
+#pragma once
+#include "pe_math.cuh"
+#include "pe_stream.cuh"
+
+namespace pe {
+
+// pick the ring depth so that a CTA stays near 54 KB of shared memory (4 CTAs = 1024 threads per SM)
+constexpr int stages_for(int witot, int wotot, int budget = 54 * 1024) {
+    int stage = kTile * 4 * witot, out = 2 * kTile * 4 * wotot;
+    int s = (budget - out - 512) / stage;
+    return s < 2 ? 2 : (s > 6 ? 6 : s);
+}
+
+struct NoExtra {};
+
+#define PE_OP_COMMON(NAME, I0, I1, I2, O0, O1, NR, FL, MB)                                   \
+    static constexpr int WI0 = (I0), WI1 = (I1), WI2 = (I2), WO0 = (O0), WO1 = (O1), NRED = (NR); \
+    static constexpr bool FLAG = (FL);                                                       \
+    static constexpr int STAGES = stages_for(WI0 + WI1 + WI2, WO0 + WO1), MINB = (MB);       \
+    static const char* name() { return NAME; }
+
+// ---- a1 symmetric_orthogonalization (rotation_representation.py:192-206) ------------------------------------
+template <bool DET>
+struct SvdFwd {
+    PE_OP_COMMON("svd_orth_fwd", 9, 0, 0, 9, DET ? 1 : 0, 0, false, 4)
+    using Extra = NoExtra;
+    __device__ static __forceinline__ void run(const float* m, const float*, const float*, float* r, float* d,
+                                               double*, int&, const Extra&) {
+        float ds;
+        svd_orth<kSweeps>(m, r, ds);
+        if constexpr (DET) d[0] = ds;
+    }
+};
+// pullback with the saved forward output: in = (m, r, g)
+struct SvdBwdSaved {
+    PE_OP_COMMON("svd_orth_bwd", 9, 9, 9, 9, 0, 0, false, 3)
+    using Extra = NoExtra;
+    __device__ static __forceinline__ void run(const float* m, const float* r, const float* g, float* dm, float*,
+                                               double*, int&, const Extra&) {
+        svd_orth_pullback(m, r, g, dm);
+    }
+};
+// pullback that recomputes r from m: in = (m, g)
+struct SvdBwdRecompute {
+    PE_OP_COMMON("svd_orth_bwd_recompute", 9, 9, 0, 9, 0, 0, false, 3)
+    using Extra = NoExtra;
+    __device__ static __forceinline__ void run(const float* m, const float* g, const float*, float* dm, float*,
+                                               double*, int&, const Extra&) {
+        float r[9], ds;
+        svd_orth<kSweeps>(m, r, ds);
+        svd_orth_pullback(m, r, g, dm);
+    }
+};
+
+// ---- elementwise maps: forward (x -> 9 words) and pullback ((x, g) -> dx) ---------------------------------------
+#define PE_MAP_OPS(Tag, W, FWD, BWD, LABEL)                                                                   \
+    struct Tag##Fwd {                                                                                         \
+        PE_OP_COMMON(LABEL "_fwd", W, 0, 0, 9, 0, 0, false, 4)                                                \
+        using Extra = NoExtra;                                                                                \
+        __device__ static __forceinline__ void run(const float* x, const float*, const float*, float* r,     \
+                                                   float*, double*, int&, const Extra&) {                    \
+            FWD(x, r);                                                                                        \
+        }                                                                                                     \
+    };                                                                                                        \
+    struct Tag##Bwd {                                                                                         \
+        PE_OP_COMMON(LABEL "_bwd", W, 9, 0, W, 0, 0, false, 4)                                                \
+        using Extra = NoExtra;                                                                                \
+        __device__ static __forceinline__ void run(const float* x, const float* g, const float*, float* dx,  \
+                                                   float*, double*, int&, const Extra&) {                    \
+            BWD(x, g, dx);                                                                                    \
+        }                                                                                                     \
+    };
+PE_MAP_OPS(Ortho6d, 6, ortho6d, ortho6d_pullback, "ortho6d")   // rotation_representation.py:21-36
+PE_MAP_OPS(Quat, 4, quat_map, quat_pullback, "quat")           // rotation_representation.py:139-172
+PE_MAP_OPS(Euler, 3, euler_map, euler_pullback, "euler")       // rotation_representation.py:92-115
+PE_MAP_OPS(Ortho5d, 5, ortho5d, ortho5d_pullback, "ortho5d")   // rotation_representation.py:120-136
+PE_MAP_OPS(Expmap, 3, expmap, expmap_pullback, "expmap")       // rotation_representation.py:245-320
+
+// ---- a5 loss_frobenius (Comparison/main.py:12-16) ---------------------------------------------------------------
+struct FrobFwd {
+    PE_OP_COMMON("frobenius_fwd", 9, 9, 0, 0, 0, 1, false, 4)
+    using Extra = NoExtra;
+    __device__ static __forceinline__ void run(const float* a, const float* b, const float*, float*, float*,
+                                               double* red, int&, const Extra&) {
+        red[0] += (double)frob_dist(a, b);
+    }
+};
+struct GradScale {
+    const float* gout;  // device scalar: upstream gradient of the 0-d loss
+    float mul;          // 1/n (mean) times the sign of the operand
+};
+// G = gscale (a - b)/|a - b|;  BOTH: out0 = G, out1 = -G;  else out0 = G (mul carries the sign for db-only)
+template <bool BOTH>
+struct FrobBwd {
+    PE_OP_COMMON("frobenius_bwd", 9, 9, 0, 9, BOTH ? 9 : 0, 0, false, 4)
+    using Extra = GradScale;
+    __device__ static __forceinline__ void run(const float* a, const float* b, const float*, float* da, float* db,
+                                               double*, int&, const Extra& ex) {
+        float d[9], s = 0.f;
+#pragma unroll
+        for (int i = 0; i < 9; ++i) { d[i] = a[i] - b[i]; s = fmaf(d[i], d[i], s); }
+        float k = s > 0.f ? __ldg(ex.gout) * ex.mul * rsqrt_nr(s) : 0.f;
+#pragma unroll
+        for (int i = 0; i < 9; ++i) {
+            da[i] = k * d[i];
+            if constexpr (BOTH) db[i] = -da[i];
+        }
+    }
+};
+
+// ---- a6 / a8 geodesic distance (rotation_representation.py:209-227, point_cloud/main.py:61-73) ---------------------
+struct Clamp {
+    float lo, hi;
+};
+template <bool THETA, bool SUM>
+struct GeoFwd {
+    PE_OP_COMMON("geodesic_fwd", 9, 9, 0, THETA ? 1 : 0, 0, SUM ? 1 : 0, false, 4)
+    using Extra = Clamp;
+    __device__ static __forceinline__ void run(const float* a, const float* b, const float*, float* th, float*,
+                                               double* red, int&, const Extra& ex) {
+        float c = 0.5f * (dot9(a, b) - 1.0f);
+        float t = acosf(fminf(fmaxf(c, ex.lo), ex.hi));
+        if constexpr (THETA) th[0] = t;
+        if constexpr (SUM) red[0] += (double)t;
+    }
+};
+struct GeoGrad {
+    float lo, hi, gmul;
+    const float* gscalar;
+};
+// MODE 0: out0 = d1 ; 1: out0 = d2 ; 2: out0 = d1, out1 = d2.   GS: upstream gradient is one device scalar.
+template <int MODE, bool GS>
+struct GeoBwd {
+    PE_OP_COMMON("geodesic_bwd", 9, 9, GS ? 0 : 1, 9, MODE == 2 ? 9 : 0, 0, false, 4)
+    using Extra = GeoGrad;
+    __device__ static __forceinline__ void run(const float* a, const float* b, const float* g, float* o0, float* o1,
+                                               double*, int&, const Extra& ex) {
+        float c = 0.5f * (dot9(a, b) - 1.0f);
+        float up = (GS ? __ldg(ex.gscalar) : g[0]) * ex.gmul;
+        // d theta/d c = -1/sqrt(1 - c^2); d c/d a = b/2.  Zero where the clamp is active.
+        float k = (c >= ex.lo && c <= ex.hi) ? -0.5f * up * rsqrt_nr(fmaf(-c, c, 1.0f)) : 0.f;
+#pragma unroll
+        for (int i = 0; i < 9; ++i) {
+            if constexpr (MODE == 0) o0[i] = k * b[i];
+            if constexpr (MODE == 1) o0[i] = k * a[i];
+            if constexpr (MODE == 2) { o0[i] = k * b[i]; o1[i] = k * a[i]; }
+        }
+    }
+};
+
+// ---- a7 angle_error (rotation_representation.py:230-242): float64 arithmetic, degrees, range flag ---------------
+template <bool DEG, bool SUM>
+struct AngleFwd {
+    PE_OP_COMMON("angle_error_fwd", 9, 9, 0, DEG ? 2 : 0, 0, SUM ? 1 : 0, true, 4)
+    using Extra = NoExtra;
+    __device__ static __forceinline__ void run(const float* a, const float* b, const float*, float* out, float*,
+                                               double* red, int& flag, const Extra&) {
+        double c = 0.5 * (dot9_f64(a, b) - 1.0);
+        if (c < -1.1 || c > 1.1) flag |= 1;  // false for NaN, exactly like the reference's two comparisons (:237)
+        double t = acos(fmin(fmax(c, -1.0), 1.0)) * 57.295779513082320876798154814105;
+        if constexpr (DEG) {
+            out[0] = __int_as_float(__double2loint(t));
+            out[1] = __int_as_float(__double2hiint(t));
+        }
+        if constexpr (SUM) red[0] += t;
+    }
+};
+
+// ---- fused: loss_frobenius(symmetric_orthogonalization(x), R_true) ------------------------------------------------
+template <bool WRITE_R>
+struct SvdFrobFwd {
+    PE_OP_COMMON("svd_orth_frobenius_fwd", 9, 9, 0, WRITE_R ? 9 : 0, 0, 1, false, 4)
+    using Extra = NoExtra;
+    __device__ static __forceinline__ void run(const float* m, const float* rt, const float*, float* r, float*,
+                                               double* red, int&, const Extra&) {
+        float rr[9], ds;
+        svd_orth<kSweeps>(m, rr, ds);
+        red[0] += (double)frob_dist(rr, rt);
+        if constexpr (WRITE_R) {
+#pragma unroll
+            for (int i = 0; i < 9; ++i) r[i] = rr[i];
+        }
+    }
+};
+struct SvdFrobBwd {
+    PE_OP_COMMON("svd_orth_frobenius_bwd", 9, 9, 0, 9, 0, 0, false, 3)
+    using Extra = GradScale;
+    __device__ static __forceinline__ void run(const float* m, const float* rt, const float*, float* dm, float*,
+                                               double*, int&, const Extra& ex) {
+        float r[9], g[9], ds, s = 0.f;
+        svd_orth<kSweeps>(m, r, ds);
+#pragma unroll
+        for (int i = 0; i < 9; ++i) { g[i] = r[i] - rt[i]; s = fmaf(g[i], g[i], s); }
+        float k = s > 0.f ? __ldg(ex.gout) * ex.mul * rsqrt_nr(s) : 0.f;
+#pragma unroll
+        for (int i = 0; i < 9; ++i) g[i] *= k;
+        svd_orth_pullback(m, r, g, dm);
+    }
+};
+
+}  // namespace pe

@@ -1,0 +1,311 @@
+// The record-streaming engine: one persistent kernel template that every per-record op of the path runs in.
+//
+// An Op maps up to three input records (WI0, WI1, WI2 words) to up to two output records (WO0, WO1 words) and
+// optionally adds into NRED double accumulators and an int flag, all for ONE record held in registers
+// (pe_math.cuh).  The engine owns everything else:
+//
+//   HBM --TMA bulk copy--> smem ring (STAGES deep) --LDS--> registers --Op::run--> registers --STS--> smem
+//       --TMA bulk store--> HBM
+//
+// * grid = (#SMs x resident CTAs/SM) persistent CTAs; CTA c handles tiles c, c + grid, c + 2*grid, ...
+//   so at any moment the whole grid streams through one contiguous window of HBM.
+// * a tile is T consecutive records; one elected thread issues one bulk copy per input array per tile and the
+//   copies complete on the stage's mbarrier (byte-counted).  STAGES-1 tiles are always in flight per CTA.
+// * outputs are double-buffered in shared memory and leave with bulk stores tracked by bulk async-groups.
+// * the last, partial tile (n % T records) is moved with plain loads/stores inside the same kernel.
+// * inputs that are not 16-byte aligned, or whose row stride is not the record width (the `out[:, :9]` view of
+//   a (B, 12) tensor, /root/reference/3D-Pose/main2.py:94), run the `direct` kernel: still on the GPU, no TMA.
+#pragma once
+#include <mutex>
+
+#include "pe_common.h"
+#include "pe_stage.cuh"
+
+namespace pe {
+
+constexpr int kTile = 256;  // records per tile = threads per CTA
+
+template <class Op>
+struct Params {
+    const float* in[3];
+    float* out[2];
+    long long n;           // records
+    long long in0_stride;  // words between consecutive records of in[0] (direct kernel only)
+    double* sums;          // NRED accumulators (device), added to with one atomic per CTA
+    int* flag;             // OR-ed with the per-record flags
+    typename Op::Extra ex;
+};
+
+template <class Op>
+struct Geometry {
+    __host__ __device__ static constexpr int wi(int k) { return k == 0 ? Op::WI0 : (k == 1 ? Op::WI1 : Op::WI2); }
+    __host__ __device__ static constexpr int wo(int k) { return k == 0 ? Op::WO0 : Op::WO1; }
+    static constexpr int WITOT = Op::WI0 + Op::WI1 + Op::WI2;
+    static constexpr int WOTOT = Op::WO0 + Op::WO1;
+    static constexpr int NOBUF = WOTOT > 0 ? 2 : 0;
+    static constexpr int kBarBytes = 128;
+    static constexpr int kStageBytes = kTile * 4 * WITOT;
+    static constexpr int kOutBytes = kTile * 4 * WOTOT;
+    static constexpr int kSmemBytes = kBarBytes + Op::STAGES * kStageBytes + NOBUF * kOutBytes + 32 * 8 * (Op::NRED > 0 ? Op::NRED : 1);
+};
+
+template <int N>
+struct RegArr {
+    float v[N > 0 ? N : 1];
+};
+
+template <class Op>
+__device__ __forceinline__ void block_reduce_and_publish(double* red, int flag, double* sums, int* flagp,
+                                                         double* scratch) {
+    if constexpr (Op::NRED > 0) {
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+        for (int k = 0; k < Op::NRED; ++k) {
+            double v = warp_sum(red[k]);
+            if (lane == 0) scratch[warp * Op::NRED + k] = v;
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+#pragma unroll
+            for (int k = 0; k < Op::NRED; ++k) {
+                double v = 0.0;
+                for (int w = 0; w < (int)(blockDim.x >> 5); ++w) v += scratch[w * Op::NRED + k];
+                atomicAdd(sums + k, v);
+            }
+        }
+    }
+    if constexpr (Op::FLAG) {
+        int any = __syncthreads_or(flag);
+        if (threadIdx.x == 0 && any) atomicOr(flagp, any);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+template <class Op>
+__global__ void __launch_bounds__(kTile, Op::MINB) stream_tma_kernel(const Params<Op> p) {
+    using G = Geometry<Op>;
+    constexpr int T = kTile, S = Op::STAGES;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw);
+    float* s_in = reinterpret_cast<float*>(smem_raw + G::kBarBytes);
+    float* s_out = s_in + S * T * G::WITOT;
+    double* s_red = reinterpret_cast<double*>(s_out + G::NOBUF * T * G::WOTOT);
+
+    const int tid = threadIdx.x;
+    const long long n = p.n;
+    const long long ntiles = (n + T - 1) / T;
+    const long long nfull = n / T;  // tiles [0, nfull) are complete and move by TMA
+    const long long gstep = gridDim.x;
+    uint64_t policy = 0;
+
+    auto issue = [&](int s, long long tile) {
+        // one elected thread: arm the barrier with the byte count, then one bulk copy per input array
+        mbar_arrive_expect_tx(&bars[s], (uint32_t)G::kStageBytes);
+        float* dst = s_in + s * T * G::WITOT;
+        int off = 0;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            if (G::wi(k) > 0) {
+                bulk_g2s(dst + off, p.in[k] + tile * T * G::wi(k), (uint32_t)(T * 4 * G::wi(k)), &bars[s], policy);
+                off += T * G::wi(k);
+            }
+        }
+    };
+
+    if (tid == 0) {
+        policy = l2_evict_first_policy();
+#pragma unroll
+        for (int s = 0; s < S; ++s) mbar_init(&bars[s], 1);
+        mbar_init_fence();
+    }
+    __syncthreads();
+    if (tid == 0) {
+#pragma unroll
+        for (int s = 0; s < S; ++s) {
+            long long tile = blockIdx.x + s * gstep;
+            if (tile < nfull) issue(s, tile);
+        }
+    }
+
+    double red[Op::NRED > 0 ? Op::NRED : 1];
+#pragma unroll
+    for (int k = 0; k < (Op::NRED > 0 ? Op::NRED : 1); ++k) red[k] = 0.0;
+    int flag = 0;
+
+    long long it = 0;
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gstep, ++it) {
+        const int s = (int)(it % S);
+        const uint32_t parity = (uint32_t)((it / S) & 1);
+        const long long base = tile * T;
+        const bool full = tile < nfull;
+        const int cnt = full ? T : (int)(n - base);
+        float* si = s_in + s * T * G::WITOT;
+
+        if (full) {
+            mbar_wait(&bars[s], parity);
+        } else {
+            // ragged tail: plain coalesced word copies into the same shared-memory layout
+            int off = 0;
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                if (G::wi(k) > 0) {
+                    const float* src = p.in[k] + base * G::wi(k);
+                    for (int w = tid; w < cnt * G::wi(k); w += T) si[off + w] = src[w];
+                    off += T * G::wi(k);
+                }
+            }
+            __syncthreads();
+        }
+
+        RegArr<Op::WI0> i0;
+        RegArr<Op::WI1> i1;
+        RegArr<Op::WI2> i2;
+        RegArr<Op::WO0> o0;
+        RegArr<Op::WO1> o1;
+        if constexpr (Op::WI0 > 0) lds_record<Op::WI0>(si, tid, i0.v);
+        if constexpr (Op::WI1 > 0) lds_record<Op::WI1>(si + T * Op::WI0, tid, i1.v);
+        if constexpr (Op::WI2 > 0) lds_record<Op::WI2>(si + T * (Op::WI0 + Op::WI1), tid, i2.v);
+        if (tid < cnt) Op::run(i0.v, i1.v, i2.v, o0.v, o1.v, red, flag, p.ex);
+
+        float* so = s_out + (G::NOBUF ? (int)(it & 1) : 0) * T * G::WOTOT;
+        if constexpr (G::NOBUF > 0) {
+            if (tid == 0) bulk_wait_read<1>();  // the store issued two tiles ago has finished reading `so`
+        }
+        __syncthreads();  // (A) every thread is done with stage s; `so` is free
+        if (tid == 0) {
+            long long next = tile + S * gstep;
+            if (next < nfull) issue(s, next);
+        }
+        if constexpr (G::NOBUF > 0) {
+            if constexpr (Op::WO0 > 0) sts_record<Op::WO0>(so, tid, o0.v);
+            if constexpr (Op::WO1 > 0) sts_record<Op::WO1>(so + T * Op::WO0, tid, o1.v);
+            if (full) {
+                fence_async_smem();
+                __syncthreads();  // (B)
+                if (tid == 0) {
+                    if constexpr (Op::WO0 > 0) bulk_s2g(p.out[0] + base * Op::WO0, so, (uint32_t)(T * 4 * Op::WO0));
+                    if constexpr (Op::WO1 > 0)
+                        bulk_s2g(p.out[1] + base * Op::WO1, so + T * Op::WO0, (uint32_t)(T * 4 * Op::WO1));
+                    bulk_commit();
+                }
+            } else {
+                __syncthreads();
+                if constexpr (Op::WO0 > 0) {
+                    float* dst = p.out[0] + base * Op::WO0;
+                    for (int w = tid; w < cnt * Op::WO0; w += T) dst[w] = so[w];
+                }
+                if constexpr (Op::WO1 > 0) {
+                    float* dst = p.out[1] + base * Op::WO1;
+                    for (int w = tid; w < cnt * Op::WO1; w += T) dst[w] = so[T * Op::WO0 + w];
+                }
+            }
+        }
+    }
+    if constexpr (G::NOBUF > 0) {
+        if (tid == 0) bulk_wait<0>();  // shared memory must outlive the stores that read it
+    }
+    block_reduce_and_publish<Op>(red, flag, p.sums, p.flag, s_red);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Non-TMA path: arbitrary alignment and arbitrary row stride on in[0].  One record per thread, grid-stride.
+template <class Op>
+__global__ void __launch_bounds__(kTile) stream_direct_kernel(const Params<Op> p) {
+    __shared__ double s_red[32 * (Op::NRED > 0 ? Op::NRED : 1)];
+    double red[Op::NRED > 0 ? Op::NRED : 1];
+#pragma unroll
+    for (int k = 0; k < (Op::NRED > 0 ? Op::NRED : 1); ++k) red[k] = 0.0;
+    int flag = 0;
+    const long long step = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < p.n; i += step) {
+        RegArr<Op::WI0> i0;
+        RegArr<Op::WI1> i1;
+        RegArr<Op::WI2> i2;
+        RegArr<Op::WO0> o0;
+        RegArr<Op::WO1> o1;
+#pragma unroll
+        for (int w = 0; w < Op::WI0; ++w) i0.v[w] = __ldg(p.in[0] + i * p.in0_stride + w);
+#pragma unroll
+        for (int w = 0; w < Op::WI1; ++w) i1.v[w] = __ldg(p.in[1] + i * Op::WI1 + w);
+#pragma unroll
+        for (int w = 0; w < Op::WI2; ++w) i2.v[w] = __ldg(p.in[2] + i * Op::WI2 + w);
+        Op::run(i0.v, i1.v, i2.v, o0.v, o1.v, red, flag, p.ex);
+#pragma unroll
+        for (int w = 0; w < Op::WO0; ++w) p.out[0][i * Op::WO0 + w] = o0.v[w];
+#pragma unroll
+        for (int w = 0; w < Op::WO1; ++w) p.out[1][i * Op::WO1 + w] = o1.v[w];
+    }
+    block_reduce_and_publish<Op>(red, flag, p.sums, p.flag, s_red);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+struct LaunchCfg {
+    int sms = 0;
+    int ctas_per_sm = 0;
+};
+
+template <class Op>
+int stream_config(LaunchCfg* out) {
+    static std::mutex mu;
+    static LaunchCfg cache[64];
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return fail_cuda(e, "cudaGetDevice");
+    if (dev < 0 || dev >= 64) return fail(PE_ERR_BAD_ARG, "device index out of range");
+    std::lock_guard<std::mutex> lk(mu);
+    if (cache[dev].sms == 0) {
+        using G = Geometry<Op>;
+        cudaDeviceProp prop;
+        e = cudaGetDeviceProperties(&prop, dev);
+        if (e != cudaSuccess) return fail_cuda(e, "cudaGetDeviceProperties");
+        if (prop.major < 10) return fail(PE_ERR_NO_DEVICE, "this library is built for sm_100a (B200) only");
+        e = cudaFuncSetAttribute(stream_tma_kernel<Op>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::kSmemBytes);
+        if (e != cudaSuccess) return fail_cuda(e, "cudaFuncSetAttribute(smem)");
+        int per_sm = 0;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, stream_tma_kernel<Op>, kTile, G::kSmemBytes);
+        if (e != cudaSuccess) return fail_cuda(e, "cudaOccupancyMaxActiveBlocksPerMultiprocessor");
+        if (per_sm < 1) return fail(PE_ERR_INTERNAL, "kernel does not fit on an SM");
+        cache[dev].ctas_per_sm = per_sm;
+        cache[dev].sms = prop.multiProcessorCount;
+    }
+    *out = cache[dev];
+    return 0;
+}
+
+inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+// force_direct: test hook (PE_FORCE_DIRECT=1) so that the non-TMA kernel is covered on aligned inputs too
+template <class Op>
+int stream_launch(Params<Op> p, cudaStream_t stream) {
+    using G = Geometry<Op>;
+    if (p.n < 0) return fail(PE_ERR_BAD_ARG, "negative record count");
+    if (p.n == 0) return 0;
+    for (int k = 0; k < 3; ++k)
+        if (G::wi(k) > 0 && p.in[k] == nullptr) return fail(PE_ERR_BAD_ARG, "null input pointer");
+    for (int k = 0; k < 2; ++k)
+        if (G::wo(k) > 0 && p.out[k] == nullptr) return fail(PE_ERR_BAD_ARG, "null output pointer");
+    if (Op::NRED > 0 && p.sums == nullptr) return fail(PE_ERR_BAD_ARG, "null accumulator pointer");
+    if (Op::FLAG && p.flag == nullptr) return fail(PE_ERR_BAD_ARG, "null flag pointer");
+    if (p.in0_stride < G::wi(0)) return fail(PE_ERR_BAD_ARG, "row stride smaller than the record");
+    LaunchCfg cfg;
+    if (int rc = stream_config<Op>(&cfg)) return rc;
+    bool tma = (p.in0_stride == G::wi(0)) && !force_direct();
+    for (int k = 0; k < 3; ++k) tma = tma && (G::wi(k) == 0 || aligned16(p.in[k]));
+    for (int k = 0; k < 2; ++k) tma = tma && (G::wo(k) == 0 || aligned16(p.out[k]));
+    const long long ntiles = (p.n + kTile - 1) / kTile;
+    if (tma) {
+        long long grid = (long long)cfg.sms * cfg.ctas_per_sm;
+        if (grid > ntiles) grid = ntiles;
+        stream_tma_kernel<Op><<<(unsigned)grid, kTile, G::kSmemBytes, stream>>>(p);
+    } else {
+        long long grid = (long long)cfg.sms * 8;
+        if (grid > ntiles) grid = ntiles;
+        stream_direct_kernel<Op><<<(unsigned)grid, kTile, 0, stream>>>(p);
+    }
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail_cuda(e, Op::name());
+    count_launch();
+    return 0;
+}
+
+}  // namespace pe

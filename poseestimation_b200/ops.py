@@ -1,0 +1,478 @@
+"""``torch.library`` custom ops (namespace ``pe_b200``) over the C ABI of ``libpe_rotation.so``.
+
+Each op is CUDA-only (``device_types="cuda"``): a CPU tensor raises ``NotImplementedError`` from the dispatcher, there is
+no CPU or PyTorch fallback.  Every differentiable op has ``register_fake`` (so ``torch.compile`` can trace it) and
+``register_autograd`` whose backward is itself a custom op.
+
+Record convention: the ops take 2-D ``(n, w)`` float32 tensors ("records": w = 9 for a row-major 3x3 matrix) whose
+inner stride is 1; the row stride may exceed ``w`` (``out[:, :9]`` of a ``(B, 12)`` network output,
+/root/reference/3D-Pose/main2.py:94) and is passed to the kernel instead of copying.
+"""
+from __future__ import annotations
+
+import torch
+from torch import Tensor
+
+from ._lib import check, lib
+
+NS = "pe_b200"
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+def _rec(x: Tensor, w: int):
+    """-> (tensor with unit inner stride, row stride in floats)."""
+    if x.dtype != torch.float32:
+        raise TypeError(f"pe_b200 ops compute in float32; got {x.dtype}")
+    if x.dim() != 2 or x.shape[1] != w:
+        raise ValueError(f"expected a (n, {w}) tensor, got {tuple(x.shape)}")
+    if x.shape[0] <= 1:
+        return x.contiguous(), w
+    if x.stride(1) != 1 or x.stride(0) < w:
+        x = x.contiguous()
+    return x, x.stride(0)
+
+
+def _mat(x: Tensor) -> Tensor:
+    """dense (n, 9) float32 view/copy of a (n, 3, 3) or (n, 9) tensor."""
+    if x.dtype != torch.float32:
+        raise TypeError(f"pe_b200 ops compute in float32; got {x.dtype}")
+    if x.dim() == 3 and x.shape[1:] == (3, 3) or x.dim() == 2 and x.shape[1] == 9:
+        return x.contiguous().view(-1, 9)
+    raise ValueError(f"expected (n, 3, 3) matrices, got {tuple(x.shape)}")
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _p(t: Tensor | None) -> int | None:
+    return None if t is None else t.data_ptr()
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# a1  symmetric_orthogonalization                       /root/reference/rotation_representation.py:192-206
+@torch.library.custom_op(f"{NS}::svd_orth", mutates_args=(), device_types="cuda")
+def svd_orth(x: Tensor) -> Tensor:
+    x, stride = _rec(x, 9)
+    n = x.shape[0]
+    r = torch.empty((n, 3, 3), dtype=torch.float32, device=x.device)
+    with torch.cuda.device(x.device):
+        check(lib.pe_svd_orth_fwd(x.data_ptr(), stride, r.data_ptr(), None, n, _stream()), "pe_svd_orth_fwd")
+    return r
+
+
+@svd_orth.register_fake
+def _(x):
+    return x.new_empty((x.shape[0], 3, 3))
+
+
+@torch.library.custom_op(f"{NS}::svd_orth_bwd", mutates_args=(), device_types="cuda")
+def svd_orth_bwd(x: Tensor, r: Tensor, g: Tensor) -> Tensor:
+    """dL/dx from g = dL/dr; r is the saved forward output."""
+    x, stride = _rec(x, 9)
+    n = x.shape[0]
+    r, g = _mat(r), _mat(g)
+    dx = torch.empty((n, 9), dtype=torch.float32, device=x.device)
+    with torch.cuda.device(x.device):
+        check(lib.pe_svd_orth_bwd(x.data_ptr(), stride, r.data_ptr(), g.data_ptr(), dx.data_ptr(), n, _stream()),
+              "pe_svd_orth_bwd")
+    return dx
+
+
+@svd_orth_bwd.register_fake
+def _(x, r, g):
+    return x.new_empty((x.shape[0], 9))
+
+
+@torch.library.custom_op(f"{NS}::svd_orth_bwd_recompute", mutates_args=(), device_types="cuda")
+def svd_orth_bwd_recompute(x: Tensor, g: Tensor) -> Tensor:
+    """Same pullback, recomputing r from x inside the kernel (reads 72 B/matrix instead of 108)."""
+    x, stride = _rec(x, 9)
+    n = x.shape[0]
+    g = _mat(g)
+    dx = torch.empty((n, 9), dtype=torch.float32, device=x.device)
+    with torch.cuda.device(x.device):
+        check(lib.pe_svd_orth_bwd(x.data_ptr(), stride, None, g.data_ptr(), dx.data_ptr(), n, _stream()),
+              "pe_svd_orth_bwd")
+    return dx
+
+
+@svd_orth_bwd_recompute.register_fake
+def _(x, g):
+    return x.new_empty((x.shape[0], 9))
+
+
+def _svd_orth_setup(ctx, inputs, output):
+    ctx.save_for_backward(inputs[0], output)
+
+
+def _svd_orth_backward(ctx, g):
+    x, r = ctx.saved_tensors
+    return svd_orth_bwd(x, r, g)
+
+
+svd_orth.register_autograd(_svd_orth_backward, setup_context=_svd_orth_setup)
+
+
+@torch.library.custom_op(f"{NS}::svd_orth_det", mutates_args=(), device_types="cuda")
+def svd_orth_det(x: Tensor) -> tuple[Tensor, Tensor]:
+    """(r, det): det is the factor det(U V^T) = +-1 of rotation_representation.py:202.  Not differentiable."""
+    x, stride = _rec(x, 9)
+    n = x.shape[0]
+    r = torch.empty((n, 3, 3), dtype=torch.float32, device=x.device)
+    d = torch.empty((n,), dtype=torch.float32, device=x.device)
+    with torch.cuda.device(x.device):
+        check(lib.pe_svd_orth_fwd(x.data_ptr(), stride, r.data_ptr(), d.data_ptr(), n, _stream()), "pe_svd_orth_fwd")
+    return r, d
+
+
+@svd_orth_det.register_fake
+def _(x):
+    return x.new_empty((x.shape[0], 3, 3)), x.new_empty((x.shape[0],))
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# a2-a4 and the 8(f) maps: x (n, w) -> r (n, 3, 3)
+def _make_map(name: str, w: int):
+    fwd_c = getattr(lib, f"pe_{name}_fwd")
+    bwd_c = getattr(lib, f"pe_{name}_bwd")
+
+    @torch.library.custom_op(f"{NS}::{name}", mutates_args=(), device_types="cuda")
+    def fwd(x: Tensor) -> Tensor:
+        x, stride = _rec(x, w)
+        n = x.shape[0]
+        r = torch.empty((n, 3, 3), dtype=torch.float32, device=x.device)
+        with torch.cuda.device(x.device):
+            check(fwd_c(x.data_ptr(), stride, r.data_ptr(), n, _stream()), f"pe_{name}_fwd")
+        return r
+
+    @fwd.register_fake
+    def _(x):
+        return x.new_empty((x.shape[0], 3, 3))
+
+    @torch.library.custom_op(f"{NS}::{name}_bwd", mutates_args=(), device_types="cuda")
+    def bwd(x: Tensor, g: Tensor) -> Tensor:
+        x, stride = _rec(x, w)
+        n = x.shape[0]
+        g = _mat(g)
+        dx = torch.empty((n, w), dtype=torch.float32, device=x.device)
+        with torch.cuda.device(x.device):
+            check(bwd_c(x.data_ptr(), stride, g.data_ptr(), dx.data_ptr(), n, _stream()), f"pe_{name}_bwd")
+        return dx
+
+    @bwd.register_fake
+    def _(x, g):
+        return x.new_empty((x.shape[0], w))
+
+    def setup(ctx, inputs, output):
+        ctx.save_for_backward(inputs[0])
+
+    def backward(ctx, g):
+        (x,) = ctx.saved_tensors
+        return bwd(x, g)
+
+    fwd.register_autograd(backward, setup_context=setup)
+    return fwd, bwd
+
+
+ortho6d, ortho6d_bwd = _make_map("ortho6d", 6)     # rotation_representation.py:21-36
+quat, quat_bwd = _make_map("quat", 4)              # rotation_representation.py:139-172
+euler, euler_bwd = _make_map("euler", 3)           # rotation_representation.py:92-115
+ortho5d, ortho5d_bwd = _make_map("ortho5d", 5)     # rotation_representation.py:120-136
+expmap, expmap_bwd = _make_map("expmap", 3)        # rotation_representation.py:245-320
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# a5  loss_frobenius                                    /root/reference/Comparison/main.py:12-16 (+ 7 copies)
+@torch.library.custom_op(f"{NS}::frobenius_sum", mutates_args=(), device_types="cuda")
+def frobenius_sum(a: Tensor, b: Tensor) -> Tensor:
+    """sum_b |a_b - b_b|_F as a (1,) float64 tensor (the per-rank partial of the loss; not differentiable)."""
+    a, b = _mat(a), _mat(b)
+    if a.shape != b.shape:
+        raise ValueError("shape mismatch")
+    s = torch.empty((1,), dtype=torch.float64, device=a.device)
+    with torch.cuda.device(a.device):
+        check(lib.pe_frobenius_fwd(a.data_ptr(), b.data_ptr(), s.data_ptr(), a.shape[0], _stream()),
+              "pe_frobenius_fwd")
+    return s
+
+
+@frobenius_sum.register_fake
+def _(a, b):
+    return a.new_empty((1,), dtype=torch.float64)
+
+
+@torch.library.custom_op(f"{NS}::frobenius_mean", mutates_args=(), device_types="cuda")
+def frobenius_mean(a: Tensor, b: Tensor) -> Tensor:
+    """mean_b |a_b - b_b|_F, 0-d float32."""
+    n = _mat(a).shape[0]
+    return (frobenius_sum(a, b) / max(n, 1)).to(torch.float32).reshape(()) if n else \
+        torch.full((), float("nan"), dtype=torch.float32, device=a.device)
+
+
+@frobenius_mean.register_fake
+def _(a, b):
+    return a.new_empty(())
+
+
+@torch.library.custom_op(f"{NS}::frobenius_bwd", mutates_args=(), device_types="cuda")
+def frobenius_bwd(a: Tensor, b: Tensor, gout: Tensor, need_a: bool, need_b: bool) -> tuple[Tensor, Tensor]:
+    a, b = _mat(a), _mat(b)
+    n = a.shape[0]
+    gout = gout.to(torch.float32).reshape(1).contiguous()
+    da = torch.empty((n, 3, 3) if need_a else (0,), dtype=torch.float32, device=a.device)
+    db = torch.empty((n, 3, 3) if need_b else (0,), dtype=torch.float32, device=a.device)
+    if n and (need_a or need_b):
+        with torch.cuda.device(a.device):
+            check(lib.pe_frobenius_bwd(a.data_ptr(), b.data_ptr(), gout.data_ptr(), 1.0 / n,
+                                       da.data_ptr() if need_a else None, db.data_ptr() if need_b else None, n,
+                                       _stream()), "pe_frobenius_bwd")
+    return da, db
+
+
+@frobenius_bwd.register_fake
+def _(a, b, gout, need_a, need_b):
+    n = a.shape[0]
+    return (a.new_empty((n, 3, 3) if need_a else (0,)), a.new_empty((n, 3, 3) if need_b else (0,)))
+
+
+def _frob_setup(ctx, inputs, output):
+    ctx.save_for_backward(inputs[0], inputs[1])
+
+
+def _frob_backward(ctx, g):
+    a, b = ctx.saved_tensors
+    na, nb = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
+    da, db = frobenius_bwd(a, b, g, na, nb)
+    return (da.view(a.shape) if na else None), (db.view(b.shape) if nb else None)
+
+
+frobenius_mean.register_autograd(_frob_backward, setup_context=_frob_setup)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# a6 / a8  geodesic distance      rotation_representation.py:209-227 (lo, hi = -1, 1); point_cloud/main.py:61-73
+@torch.library.custom_op(f"{NS}::geodesic_theta", mutates_args=(), device_types="cuda")
+def geodesic_theta(m1: Tensor, m2: Tensor, lo: float, hi: float) -> Tensor:
+    m1, m2 = _mat(m1), _mat(m2)
+    n = m1.shape[0]
+    th = torch.empty((n,), dtype=torch.float32, device=m1.device)
+    with torch.cuda.device(m1.device):
+        check(lib.pe_geodesic_fwd(m1.data_ptr(), m2.data_ptr(), lo, hi, th.data_ptr(), None, n, _stream()),
+              "pe_geodesic_fwd")
+    return th
+
+
+@geodesic_theta.register_fake
+def _(m1, m2, lo, hi):
+    return m1.new_empty((m1.shape[0],))
+
+
+@torch.library.custom_op(f"{NS}::geodesic_sum", mutates_args=(), device_types="cuda")
+def geodesic_sum(m1: Tensor, m2: Tensor, lo: float, hi: float) -> Tensor:
+    """sum_b theta_b as a (1,) float64 tensor, no per-record output (72 B/pair of traffic)."""
+    m1, m2 = _mat(m1), _mat(m2)
+    s = torch.empty((1,), dtype=torch.float64, device=m1.device)
+    with torch.cuda.device(m1.device):
+        check(lib.pe_geodesic_fwd(m1.data_ptr(), m2.data_ptr(), lo, hi, None, s.data_ptr(), m1.shape[0], _stream()),
+              "pe_geodesic_fwd")
+    return s
+
+
+@geodesic_sum.register_fake
+def _(m1, m2, lo, hi):
+    return m1.new_empty((1,), dtype=torch.float64)
+
+
+@torch.library.custom_op(f"{NS}::geodesic_reduce", mutates_args=(), device_types="cuda")
+def geodesic_reduce(m1: Tensor, m2: Tensor, lo: float, hi: float, mean: bool) -> Tensor:
+    """0-d float32 mean or sum of theta, differentiable."""
+    n = _mat(m1).shape[0]
+    s = geodesic_sum(m1, m2, lo, hi)
+    if mean:
+        s = s / n if n else s * float("nan")
+    return s.to(torch.float32).reshape(())
+
+
+@geodesic_reduce.register_fake
+def _(m1, m2, lo, hi, mean):
+    return m1.new_empty(())
+
+
+@torch.library.custom_op(f"{NS}::geodesic_bwd", mutates_args=(), device_types="cuda")
+def geodesic_bwd(m1: Tensor, m2: Tensor, lo: float, hi: float, g: Tensor, gmul: float, need_1: bool,
+                 need_2: bool) -> tuple[Tensor, Tensor]:
+    """g: (n,) per-record upstream gradient, or a 0-d / 1-element tensor broadcast to all records."""
+    m1, m2 = _mat(m1), _mat(m2)
+    n = m1.shape[0]
+    scalar = g.numel() == 1 and n != 1 or g.dim() == 0
+    g = g.to(torch.float32).reshape(-1).contiguous()
+    d1 = torch.empty((n, 3, 3) if need_1 else (0,), dtype=torch.float32, device=m1.device)
+    d2 = torch.empty((n, 3, 3) if need_2 else (0,), dtype=torch.float32, device=m1.device)
+    if n and (need_1 or need_2):
+        with torch.cuda.device(m1.device):
+            check(lib.pe_geodesic_bwd(m1.data_ptr(), m2.data_ptr(), lo, hi, g.data_ptr(), int(scalar), gmul,
+                                      d1.data_ptr() if need_1 else None, d2.data_ptr() if need_2 else None, n,
+                                      _stream()), "pe_geodesic_bwd")
+    return d1, d2
+
+
+@geodesic_bwd.register_fake
+def _(m1, m2, lo, hi, g, gmul, need_1, need_2):
+    n = m1.shape[0]
+    return (m1.new_empty((n, 3, 3) if need_1 else (0,)), m1.new_empty((n, 3, 3) if need_2 else (0,)))
+
+
+def _geo_setup(ctx, inputs, output):
+    ctx.save_for_backward(inputs[0], inputs[1])
+    ctx.lo, ctx.hi = inputs[2], inputs[3]
+    ctx.mean = inputs[4] if len(inputs) > 4 else None
+
+
+def _geo_theta_backward(ctx, g):
+    m1, m2 = ctx.saved_tensors
+    n1, n2 = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
+    d1, d2 = geodesic_bwd(m1, m2, ctx.lo, ctx.hi, g.reshape(-1), 1.0, n1, n2)
+    return (d1.view(m1.shape) if n1 else None), (d2.view(m2.shape) if n2 else None), None, None
+
+
+def _geo_reduce_backward(ctx, g):
+    m1, m2 = ctx.saved_tensors
+    n1, n2 = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
+    n = m1.shape[0]
+    d1, d2 = geodesic_bwd(m1, m2, ctx.lo, ctx.hi, g.reshape(()), (1.0 / n) if (ctx.mean and n) else 1.0, n1, n2)
+    return (d1.view(m1.shape) if n1 else None), (d2.view(m2.shape) if n2 else None), None, None, None
+
+
+geodesic_theta.register_autograd(_geo_theta_backward, setup_context=_geo_setup)
+geodesic_reduce.register_autograd(_geo_reduce_backward, setup_context=_geo_setup)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# a7  angle_error (float64, degrees, range flag)        /root/reference/rotation_representation.py:230-242
+@torch.library.custom_op(f"{NS}::angle_error_deg", mutates_args=(), device_types="cuda")
+def angle_error_deg(r1: Tensor, r2: Tensor) -> tuple[Tensor, Tensor]:
+    """(deg (n,) float64, flag (1,) int32: non-zero if any cosine is outside [-1.1, 1.1])."""
+    r1, r2 = _mat(r1), _mat(r2)
+    n = r1.shape[0]
+    deg = torch.empty((n,), dtype=torch.float64, device=r1.device)
+    flag = torch.empty((1,), dtype=torch.int32, device=r1.device)
+    with torch.cuda.device(r1.device):
+        check(lib.pe_angle_error_fwd(r1.data_ptr(), r2.data_ptr(), deg.data_ptr(), None, flag.data_ptr(), n,
+                                     _stream()), "pe_angle_error_fwd")
+    return deg, flag
+
+
+@angle_error_deg.register_fake
+def _(r1, r2):
+    return r1.new_empty((r1.shape[0],), dtype=torch.float64), r1.new_empty((1,), dtype=torch.int32)
+
+
+@torch.library.custom_op(f"{NS}::angle_error_sum", mutates_args=(), device_types="cuda")
+def angle_error_sum(r1: Tensor, r2: Tensor) -> tuple[Tensor, Tensor]:
+    """(sum of degrees (1,) float64, flag (1,) int32) without writing the per-record angles."""
+    r1, r2 = _mat(r1), _mat(r2)
+    s = torch.empty((1,), dtype=torch.float64, device=r1.device)
+    flag = torch.empty((1,), dtype=torch.int32, device=r1.device)
+    with torch.cuda.device(r1.device):
+        check(lib.pe_angle_error_fwd(r1.data_ptr(), r2.data_ptr(), None, s.data_ptr(), flag.data_ptr(), r1.shape[0],
+                                     _stream()), "pe_angle_error_fwd")
+    return s, flag
+
+
+@angle_error_sum.register_fake
+def _(r1, r2):
+    return r1.new_empty((1,), dtype=torch.float64), r1.new_empty((1,), dtype=torch.int32)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# fused training step: loss_frobenius(symmetric_orthogonalization(x), R_true)
+# (/root/reference/Comparison/main.py:59-62, UPNA/main.py:54-58, 3D-Pose/main.py:60,85-86)
+@torch.library.custom_op(f"{NS}::svd_orth_frobenius_sum", mutates_args=(), device_types="cuda")
+def svd_orth_frobenius_sum(x: Tensor, r_true: Tensor, write_r: bool) -> tuple[Tensor, Tensor]:
+    """(sum_b |r_true_b - svd_orth(x_b)|_F as (1,) float64, r (n, 3, 3) or an empty tensor)."""
+    x, stride = _rec(x, 9)
+    n = x.shape[0]
+    rt = _mat(r_true)
+    if rt.shape[0] != n:
+        raise ValueError("batch mismatch")
+    s = torch.empty((1,), dtype=torch.float64, device=x.device)
+    r = torch.empty((n, 3, 3) if write_r else (0,), dtype=torch.float32, device=x.device)
+    with torch.cuda.device(x.device):
+        check(lib.pe_svd_orth_frobenius_fwd(x.data_ptr(), stride, rt.data_ptr(), r.data_ptr() if write_r else None,
+                                            s.data_ptr(), n, _stream()), "pe_svd_orth_frobenius_fwd")
+    return s, r
+
+
+@svd_orth_frobenius_sum.register_fake
+def _(x, r_true, write_r):
+    n = x.shape[0]
+    return x.new_empty((1,), dtype=torch.float64), x.new_empty((n, 3, 3) if write_r else (0,))
+
+
+@torch.library.custom_op(f"{NS}::svd_orth_frobenius", mutates_args=(), device_types="cuda")
+def svd_orth_frobenius(x: Tensor, r_true: Tensor) -> Tensor:
+    """0-d float32 loss; differentiable w.r.t. x (r_true is a target)."""
+    n = x.shape[0]
+    s, _ = svd_orth_frobenius_sum(x, r_true, False)
+    return (s / n).to(torch.float32).reshape(()) if n else s.to(torch.float32).reshape(()) * float("nan")
+
+
+@svd_orth_frobenius.register_fake
+def _(x, r_true):
+    return x.new_empty(())
+
+
+@torch.library.custom_op(f"{NS}::svd_orth_frobenius_bwd", mutates_args=(), device_types="cuda")
+def svd_orth_frobenius_bwd(x: Tensor, r_true: Tensor, gout: Tensor) -> Tensor:
+    x, stride = _rec(x, 9)
+    n = x.shape[0]
+    rt = _mat(r_true)
+    gout = gout.to(torch.float32).reshape(1).contiguous()
+    dx = torch.empty((n, 9), dtype=torch.float32, device=x.device)
+    if n:
+        with torch.cuda.device(x.device):
+            check(lib.pe_svd_orth_frobenius_bwd(x.data_ptr(), stride, rt.data_ptr(), gout.data_ptr(), 1.0 / n,
+                                                dx.data_ptr(), n, _stream()), "pe_svd_orth_frobenius_bwd")
+    return dx
+
+
+@svd_orth_frobenius_bwd.register_fake
+def _(x, r_true, gout):
+    return x.new_empty((x.shape[0], 9))
+
+
+def _sof_setup(ctx, inputs, output):
+    ctx.save_for_backward(inputs[0], inputs[1])
+
+
+def _sof_backward(ctx, g):
+    x, rt = ctx.saved_tensors
+    return svd_orth_frobenius_bwd(x, rt, g), None
+
+
+svd_orth_frobenius.register_autograd(_sof_backward, setup_context=_sof_setup)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# a9  Kabsch (no reference function; site /root/reference/point_cloud/main.py:171-181)
+@torch.library.custom_op(f"{NS}::kabsch", mutates_args=(), device_types="cuda")
+def kabsch(p: Tensor, q: Tensor) -> tuple[Tensor, Tensor]:
+    """p, q: (B, N, 3) float32.  -> (R (B, 3, 3), t (B, 3)) with R p_k + t ~ q_k.  Not differentiable (yet)."""
+    if p.dtype != torch.float32 or q.dtype != torch.float32:
+        raise TypeError("pe_b200 ops compute in float32")
+    if p.dim() != 3 or p.shape[2] != 3 or p.shape != q.shape:
+        raise ValueError(f"expected two (B, N, 3) clouds, got {tuple(p.shape)} and {tuple(q.shape)}")
+    p, q = p.contiguous(), q.contiguous()
+    b, npts = p.shape[0], p.shape[1]
+    r = torch.empty((b, 3, 3), dtype=torch.float32, device=p.device)
+    t = torch.empty((b, 3), dtype=torch.float32, device=p.device)
+    with torch.cuda.device(p.device):
+        check(lib.pe_kabsch_fwd(p.data_ptr(), q.data_ptr(), b, npts, r.data_ptr(), t.data_ptr(), _stream()),
+              "pe_kabsch_fwd")
+    return r, t
+
+
+@kabsch.register_fake
+def _(p, q):
+    return p.new_empty((p.shape[0], 3, 3)), p.new_empty((p.shape[0], 3))

@@ -1,0 +1,231 @@
+"""Drop-in for the reference's ``rotation_representation`` module (/root/reference/rotation_representation.py).
+
+Same function names, positional signatures, output shapes and dtypes, exceptions - but each mapping / distance is ONE
+hand-written sm_100a kernel per direction (``poseestimation_b200.ops`` -> ``libpe_rotation.so``) instead of 8-30 small
+PyTorch launches.  How a reference script picks this up: put this package's directory ahead of the
+reference's on ``sys.path`` so that ``from rotation_representation import *`` (Comparison/models.py:11,
+UPNA/main.py:23, 3D-Pose/main.py:23, Iterative/utility.py:4) resolves here, and call :func:`install` on modules that
+carry private copies of the functions (3D-Pose/main2.py:34-62, point_cloud/main.py:43-155, ...).
+
+Inputs must be float32 CUDA tensors: there is no CPU path (a CPU tensor raises ``NotImplementedError``), by design.
+Additions that are not in the reference: ``loss_frobenius`` and ``geodesic`` (the reference keeps copies of them in
+its experiment scripts), ``kabsch``, ``svd_frobenius_loss`` (fused map + loss) and ``mean_angle_error``.
+"""
+from __future__ import annotations
+
+import math
+
+import torch
+
+try:  # importable both as poseestimation_b200.rotation_representation and as a top-level rotation_representation
+    from . import ops as _ops
+except ImportError:  # pragma: no cover - top-level import through sys.path
+    import os as _os
+    import sys as _sys
+    _sys.path.insert(0, _os.path.dirname(_os.path.dirname(_os.path.abspath(__file__))))
+    from poseestimation_b200 import ops as _ops
+
+__all__ = [
+    "compute_rotation_matrix_from_ortho6d", "normalize_vector", "cross_product", "stereographic_unproject",
+    "compute_rotation_matrix_from_euler", "compute_rotation_matrix_from_ortho5d",
+    "compute_rotation_matrix_from_quaternion", "symmetric_orthogonalization",
+    "compute_geodesic_distance_from_two_matrices", "angle_error", "so3_exp_map", "hat", "vec_3d_to_SO3",
+    "transform_output", "get_scene_parameters", "parametrization",
+    "loss_frobenius", "geodesic", "kabsch", "svd_frobenius_loss", "mean_angle_error", "install",
+]
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# maps R^d -> SO(3)
+def symmetric_orthogonalization(x):
+    """Nearest rotation to each 3x3 block of ``x`` (rotation_representation.py:192-206).
+
+    ``x`` is anything ``.view(-1, 3, 3)`` accepts there: (B, 9), (B, 3, 3), or the ``out[:, :9]`` slice of a wider
+    network output, which is read in place through its row stride.  Returns (B, 3, 3).
+    """
+    if x.dim() == 2 and x.shape[1] == 9:
+        rec = x                                   # possibly strided rows: no copy
+    else:
+        rec = x.reshape(-1, 9)                    # reference: x.view(-1, 3, 3)
+    return _ops.svd_orth(rec)
+
+
+def compute_rotation_matrix_from_ortho6d(poses):
+    """Gram-Schmidt 6D map, columns (x, y, z) (rotation_representation.py:21-36 = 174-189).  [..., 6] -> [..., 3, 3]."""
+    assert poses.shape[-1] == 6                   # :28
+    lead = poses.shape[:-1]
+    return _ops.ortho6d(poses.reshape(-1, 6)).reshape(*lead, 3, 3)
+
+
+def compute_rotation_matrix_from_quaternion(quaternion):
+    """(B, 4) quaternions (w, x, y, z), norm floored at 1e-8 -> (B, 3, 3) (rotation_representation.py:139-172)."""
+    return _ops.quat(quaternion.reshape(-1, 4))
+
+
+def compute_rotation_matrix_from_euler(euler):
+    """(B, 3) -> (B, 3, 3) with the reference's angle order (rotation_representation.py:92-115)."""
+    return _ops.euler(euler.reshape(-1, 3))
+
+
+def compute_rotation_matrix_from_ortho5d(a):
+    """(B, 5) -> (B, 3, 3) (rotation_representation.py:120-136)."""
+    return _ops.ortho5d(a.reshape(-1, 5))
+
+
+def so3_exp_map(log_rot, eps: float = 0.0001):
+    """Rodrigues formula with |v|^2 clamped at ``eps`` (rotation_representation.py:245-272)."""
+    if log_rot.dim() != 2 or log_rot.shape[1] != 3:
+        raise ValueError("Input tensor shape has to be Nx3.")           # :255-256
+    if abs(eps - 1e-4) > 1e-12:
+        raise ValueError("the native kernel implements the reference's default eps = 1e-4 only")
+    return _ops.expmap(log_rot)
+
+
+def vec_3d_to_SO3(x):
+    """rotation_representation.py:306-315."""
+    assert x.shape == (x.shape[0], 3)             # :311
+    return so3_exp_map(x)
+
+
+# small helpers that sit on the module surface but not on the hot path (used only inside the reference's own maps,
+# which are fused kernels here); kept for callers that import them
+def normalize_vector(v):
+    """v / max(|v|, 1e-8) row-wise (rotation_representation.py:38-50)."""
+    mag = torch.sqrt(v.pow(2).sum(1)).clamp_min(1e-8)
+    return v / mag.view(-1, 1)
+
+
+def cross_product(u, v):
+    """rotation_representation.py:53-69."""
+    return torch.linalg.cross(u, v, dim=1)
+
+
+def stereographic_unproject(a, axis=None):
+    """rotation_representation.py:72-90."""
+    batch, dim = a.shape
+    axis = dim if axis is None else axis
+    s2 = a.pow(2).sum(1, keepdim=True)
+    un = 2 * a / (s2 + 1)
+    return torch.cat((un[:, :axis], (s2 - 1) / (s2 + 1), un[:, axis:]), dim=1)
+
+
+def hat(v):
+    """(N, 3) -> (N, 3, 3) skew matrices (rotation_representation.py:275-303)."""
+    n, dim = v.shape
+    if dim != 3:
+        raise ValueError("Input vectors have to be 3-dimensional.")
+    x, y, z = v.unbind(1)
+    o = torch.zeros_like(x)
+    return torch.stack((o, -z, y, z, o, -x, -y, x, o), dim=1).view(n, 3, 3)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# distances and losses on SO(3)
+def compute_geodesic_distance_from_two_matrices(m1, m2):
+    """acos(clamp((tr(m1 m2^T) - 1)/2, -1, 1)), radians, (B,) float32 (rotation_representation.py:209-227)."""
+    return _ops.geodesic_theta(m1, m2, -1.0, 1.0)
+
+
+def geodesic(R1, R2, reduction="mean"):
+    """point_cloud/main.py:61-73: clamp at +-(1 - 1e-7); ``none`` | ``mean`` | ``sum``."""
+    eps = 1e-7
+    if reduction == "none":
+        return _ops.geodesic_theta(R1, R2, -1 + eps, 1 - eps)
+    if reduction == "mean":
+        return _ops.geodesic_reduce(R1, R2, -1 + eps, 1 - eps, True)
+    if reduction == "sum":
+        return _ops.geodesic_reduce(R1, R2, -1 + eps, 1 - eps, False)
+    return None                                   # the reference falls off the end of the function
+
+
+def angle_error(R1, R2):
+    """Angle between rotations in DEGREES, computed in float64, (B,) float64 (rotation_representation.py:230-242).
+
+    Raises ``ValueError`` if any cosine falls outside [-1.1, 1.1] (:237-239) - this reads one int back from the
+    device, the same synchronisation the reference's ``torch.any`` incurs.
+    """
+    deg, flag = _ops.angle_error_deg(R1, R2)
+    if int(flag.item()) & 1:
+        raise ValueError("angle out of range, input probably not proper rotation matrices")
+    return deg
+
+
+def mean_angle_error(R1, R2, check: bool = True):
+    """``angle_error(R1, R2).mean()`` without materialising the per-matrix angles: 0-d float64 on the device.
+
+    With ``check=False`` nothing synchronises (the caller's ``.item()`` is the only sync)."""
+    s, flag = _ops.angle_error_sum(R1, R2)
+    if check and int(flag.item()) & 1:
+        raise ValueError("angle out of range, input probably not proper rotation matrices")
+    n = R1.reshape(-1, 9).shape[0]
+    return (s / n).reshape(())
+
+
+def loss_frobenius(R_pred, R_true):
+    """mean_b |R_true - R_pred|_F (un-squared), 0-d float32 (Comparison/main.py:12-16 and its 7 copies)."""
+    return _ops.frobenius_mean(R_pred, R_true)
+
+
+def svd_frobenius_loss(x, R_true):
+    """``loss_frobenius(symmetric_orthogonalization(x), R_true)`` as one kernel per direction (108 B/matrix)."""
+    rec = x if (x.dim() == 2 and x.shape[1] == 9) else x.reshape(-1, 9)
+    return _ops.svd_orth_frobenius(rec, R_true)
+
+
+def kabsch(P, Q):
+    """Rotation and translation aligning cloud P onto Q: (B, N, 3) x2 -> ((B, 3, 3), (B, 3)), R p + t ~ q.
+
+    Not in the reference; the cloud pair is the (pc1, pc_out) of point_cloud/main.py:171-181."""
+    return _ops.kabsch(P, Q)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+transform_output = {'SVD': (9, symmetric_orthogonalization), '6D': (6, compute_rotation_matrix_from_ortho6d),
+                    '3D': (3, vec_3d_to_SO3)}     # rotation_representation.py:323-324
+
+
+def get_scene_parameters():
+    """(fx, fy, vx, vy) of the 320 px / 36 mm / 50 mm camera (rotation_representation.py:327-343)."""
+    sw, img_res, flen = 36, 320, 50
+    ppm = sw / img_res
+    fx = fy = flen / ppm
+    vx = vy = img_res / 2
+    return fx, fy, vx, vy
+
+
+def parametrization(output, T_init, fx, fy, vx, vy, rot_rep):
+    """CosyPose pose update (rotation_representation.py:346-373; the reference body uses undefined names and cannot
+    run - this follows its formulas and the working twin Iterative/utility.py:90-128).  The rotation goes through the
+    native map; the 4x4 assembly is a SURVEY 8(f) "next" row and still plain torch."""
+    vector_length, representation_func = transform_output[rot_rep]
+    R = representation_func(output[:, 0:vector_length])
+    v = output[:, vector_length:vector_length + 3]
+    xk, yk, zk = T_init[:, 0, 3], T_init[:, 1, 3], T_init[:, 2, 3]
+    zk1 = v[:, 2] * zk
+    yk1 = (v[:, 1] / fy + yk / zk) * zk1
+    xk1 = (v[:, 0] / fx + xk / zk) * zk1
+    T_out = torch.zeros((output.shape[0], 4, 4), dtype=output.dtype, device=output.device)
+    T_out[:, :3, :3] = R @ T_init[:, :3, :3]
+    T_out[:, :3, 3] = torch.stack((xk1, yk1, zk1), dim=1)
+    T_out[:, 3, 3] = 1
+    return T_out
+
+
+_DROP_IN = ("compute_rotation_matrix_from_ortho6d", "compute_rotation_matrix_from_euler",
+            "compute_rotation_matrix_from_ortho5d", "compute_rotation_matrix_from_quaternion",
+            "symmetric_orthogonalization", "compute_geodesic_distance_from_two_matrices", "angle_error",
+            "vec_3d_to_SO3", "so3_exp_map", "loss_frobenius", "geodesic")
+
+
+def install(namespace) -> list:
+    """Rebind the reference's private copies of the hot-path functions in ``namespace`` (a module or its globals
+    dict) to the native ones; returns the names that were rebound.  For scripts that shadow the import with their
+    own definitions: 3D-Pose/main2.py:34-70, 3D-Pose/test.py:32-73, point_cloud/main.py:43-155, UPNA/main.py:27-31,
+    Iterative/loss.py:4-7, Comparison/main.py:12-31."""
+    g = namespace if isinstance(namespace, dict) else vars(namespace)
+    done = []
+    for name in _DROP_IN:
+        if name in g:
+            g[name] = globals()[name]
+            done.append(name)
+    return done

@@ -1,0 +1,22 @@
+// TEST INFRASTRUCTURE: the per-record formulas of poseestimation_b200/csrc/pe_math.cuh compiled for the HOST with
+// g++, so that the CPU test-suite can check the exact arithmetic the kernels run against the oracle without a GPU.
+// Nothing in the package loads this library.
+#include "../../poseestimation_b200/csrc/pe_math.cuh"
+
+#define LOOP for (long i = 0; i < n; ++i)
+extern "C" {
+void hm_svd_orth(const float* m, float* r, float* d, long n) { LOOP pe::svd_orth<pe::kSweeps>(m + 9 * i, r + 9 * i, d[i]); }
+void hm_svd_orth_bwd(const float* m, const float* r, const float* g, float* dm, long n) {
+    LOOP pe::svd_orth_pullback(m + 9 * i, r + 9 * i, g + 9 * i, dm + 9 * i);
+}
+void hm_ortho6d(const float* x, float* r, long n) { LOOP pe::ortho6d(x + 6 * i, r + 9 * i); }
+void hm_ortho6d_bwd(const float* x, const float* g, float* dx, long n) { LOOP pe::ortho6d_pullback(x + 6 * i, g + 9 * i, dx + 6 * i); }
+void hm_quat(const float* x, float* r, long n) { LOOP pe::quat_map(x + 4 * i, r + 9 * i); }
+void hm_quat_bwd(const float* x, const float* g, float* dx, long n) { LOOP pe::quat_pullback(x + 4 * i, g + 9 * i, dx + 4 * i); }
+void hm_euler(const float* x, float* r, long n) { LOOP pe::euler_map(x + 3 * i, r + 9 * i); }
+void hm_euler_bwd(const float* x, const float* g, float* dx, long n) { LOOP pe::euler_pullback(x + 3 * i, g + 9 * i, dx + 3 * i); }
+void hm_ortho5d(const float* x, float* r, long n) { LOOP pe::ortho5d(x + 5 * i, r + 9 * i); }
+void hm_ortho5d_bwd(const float* x, const float* g, float* dx, long n) { LOOP pe::ortho5d_pullback(x + 5 * i, g + 9 * i, dx + 5 * i); }
+void hm_expmap(const float* x, float* r, long n) { LOOP pe::expmap(x + 3 * i, r + 9 * i); }
+void hm_expmap_bwd(const float* x, const float* g, float* dx, long n) { LOOP pe::expmap_pullback(x + 3 * i, g + 9 * i, dx + 3 * i); }
+}

@@ -1,0 +1,112 @@
+"""The C-ABI library loads and exports every symbol include/pe_rotation.h declares; the ctypes table matches the
+header.  No compute calls (no GPU needed) except the argument-validation paths, which return before any CUDA call."""
+import ctypes
+import os
+import re
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HEADER = os.path.join(ROOT, "include", "pe_rotation.h")
+
+
+def _declared():
+    src = open(HEADER).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    out = {}
+    for m in re.finditer(r"\b(int|long long|const char\s*\*)\s+(pe_\w+)\s*\(([^)]*)\)\s*;", src):
+        args = [a.strip() for a in m.group(3).split(",") if a.strip() and a.strip() != "void"]
+        out[m.group(2)] = args
+    return out
+
+
+@pytest.fixture(scope="module")
+def built():
+    from poseestimation_b200 import build
+    return build.build()
+
+
+def test_header_declares_the_expected_surface():
+    d = _declared()
+    for name in ("pe_version", "pe_last_error", "pe_launch_count", "pe_svd_orth_fwd", "pe_svd_orth_bwd",
+                 "pe_ortho6d_fwd", "pe_quat_fwd", "pe_euler_fwd", "pe_frobenius_fwd", "pe_geodesic_fwd",
+                 "pe_angle_error_fwd", "pe_svd_orth_frobenius_fwd", "pe_svd_orth_frobenius_bwd", "pe_kabsch_fwd"):
+        assert name in d
+    assert len(d) >= 23
+
+
+def test_library_exports_every_declared_symbol(built):
+    lib = ctypes.CDLL(built)
+    for name in _declared():
+        assert hasattr(lib, name), f"{name} declared in pe_rotation.h but not exported"
+
+
+def test_ctypes_table_matches_header(built):
+    from poseestimation_b200 import _lib
+    d = _declared()
+    compute = {k: v for k, v in d.items() if k not in ("pe_version", "pe_last_error", "pe_launch_count")}
+    assert set(compute) == set(_lib.SIGNATURES)
+    for name, args in compute.items():
+        sig = _lib.SIGNATURES[name]
+        assert len(sig) == len(args), name
+        for c_decl, ct in zip(args, sig):
+            if "*" in c_decl:
+                assert ct is ctypes.c_void_p, (name, c_decl)
+            elif c_decl.startswith("int64_t"):
+                assert ct is ctypes.c_int64, (name, c_decl)
+            elif c_decl.startswith("float"):
+                assert ct is ctypes.c_float, (name, c_decl)
+            elif c_decl.startswith("int"):
+                assert ct is ctypes.c_int, (name, c_decl)
+            else:
+                raise AssertionError(f"unhandled C type {c_decl!r}")
+
+
+def test_version_and_error_convention(built):
+    from poseestimation_b200 import _lib
+    assert _lib.version() == 100
+    # negative count is rejected before any CUDA call
+    rc = _lib.lib.pe_svd_orth_fwd(None, 9, None, None, -1, None)
+    assert rc == -1
+    assert b"negative" in _lib.lib.pe_last_error()
+    with pytest.raises(RuntimeError, match="bad call -1"):
+        _lib.check(rc, "pe_svd_orth_fwd")
+    assert _lib.lib.pe_kabsch_fwd(None, None, 4, 0, None, None, None) == -1
+
+
+def test_no_cpu_fallback():
+    """CPU tensors must not be computed by some other path: the dispatcher has no CPU kernel for these ops."""
+    import torch
+    import poseestimation_b200.rotation_representation as rr
+    with pytest.raises(NotImplementedError):
+        rr.symmetric_orthogonalization(torch.randn(4, 9))
+    with pytest.raises(NotImplementedError):
+        rr.loss_frobenius(torch.randn(4, 3, 3), torch.randn(4, 3, 3))
+    with pytest.raises(NotImplementedError):
+        rr.kabsch(torch.randn(2, 8, 3), torch.randn(2, 8, 3))
+
+
+def test_product_does_not_import_the_oracle():
+    pkg = os.path.join(ROOT, "poseestimation_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                text = open(os.path.join(dirpath, f)).read()
+                assert "import oracle" not in text and "from oracle" not in text, f
+                assert "reference_port" not in text, f
+
+
+def test_fake_kernels_give_shapes():
+    """register_fake: shape/dtype inference without a device (what torch.compile traces)."""
+    import torch
+    from torch._subclasses.fake_tensor import FakeTensorMode
+    from poseestimation_b200 import ops
+    with FakeTensorMode():
+        x = torch.empty(5, 9, device="cuda")
+        assert ops.svd_orth(x).shape == (5, 3, 3)
+        assert ops.ortho6d(torch.empty(5, 6, device="cuda")).shape == (5, 3, 3)
+        assert ops.frobenius_mean(torch.empty(5, 3, 3, device="cuda"), torch.empty(5, 3, 3, device="cuda")).shape == ()
+        deg, flag = ops.angle_error_deg(torch.empty(5, 3, 3, device="cuda"), torch.empty(5, 3, 3, device="cuda"))
+        assert deg.dtype == torch.float64 and deg.shape == (5,) and flag.dtype == torch.int32
+        r, t = ops.kabsch(torch.empty(2, 16, 3, device="cuda"), torch.empty(2, 16, 3, device="cuda"))
+        assert r.shape == (2, 3, 3) and t.shape == (2, 3)

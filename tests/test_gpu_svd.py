@@ -1,0 +1,184 @@
+"""GPU parity for symmetric orthogonalisation (forward, analytic backward, fused loss step) - BASELINE configs 1, 2."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import reference_port as O
+
+pytestmark = pytest.mark.gpu
+
+T = lambda a: torch.from_numpy(np.asarray(a))
+
+
+@pytest.fixture(scope="module")
+def rr():
+    import poseestimation_b200.rotation_representation as m
+    return m
+
+
+@pytest.fixture(scope="module")
+def ops():
+    from poseestimation_b200 import ops as o
+    return o
+
+
+def _relrows(a, b):
+    a, b = np.asarray(a, np.float64).reshape(len(a), -1), np.asarray(b, np.float64).reshape(len(b), -1)
+    return np.abs(a - b).max(1) / (np.abs(b).max(1) + 1e-30)
+
+
+def test_svd_orth_matches_reference_golden(rr, ops, golden):
+    z = golden("svd_orth")
+    n = int(z["n_random"])
+    x = T(z["x"]).cuda().requires_grad_(True)
+    r = rr.symmetric_orthogonalization(x)
+    r.backward(T(z["g"]).cuda())
+    got = r.detach().cpu().numpy()
+    s = z["s"]
+    d = np.sign(z["det"])
+    cond = np.minimum(s[:, 1] + d * s[:, 2], s[:, 0] + d * s[:, 2]) / s[:, 0]
+    err = np.abs(got - z["r"]).reshape(len(s), -1).max(1)
+    # random part: the reference's own fp32 result is the yardstick for what fp32 can do on the same input
+    ref32 = np.abs(z["r_fp32"].astype(np.float64) - z["r"]).reshape(len(s), -1).max(1)
+    assert err[:n][cond[:n] > 0.05].max() <= 1e-5
+    assert (err[:n] * cond[:n]).max() <= 1e-6
+    assert np.median(err[:n]) <= 2 * np.median(ref32[:n]) + 1e-7
+    # known answers: identity, diag(1,1,-1) -> det +1, rotations map to themselves
+    assert np.abs(got[n] - np.eye(3)).max() <= 1e-6
+    assert abs(np.linalg.det(got[n + 1].astype(np.float64)) - 1) <= 1e-5
+    assert np.abs(got[n + 3:n + 67] - z["x"][n + 3:n + 67].reshape(-1, 3, 3)).max() <= 2e-6
+    # determinant sign: exact agreement with the reference wherever det(M) is not at rounding level
+    _, ds = ops.svd_orth_det(T(z["x"]).cuda())
+    m64 = z["x"].reshape(-1, 3, 3).astype(np.float64)
+    clear = np.abs(np.linalg.det(m64)) > 1e-6 * np.abs(m64).max((1, 2)) ** 3
+    assert np.array_equal(np.sign(ds.cpu().numpy())[clear], d[clear])
+    # gradient vs the reference's autograd, away from degenerate spectra
+    gap = np.minimum(s[:, 0] - s[:, 1], s[:, 1] - s[:, 2]) / s[:, 0]
+    ok = (cond > 0.1) & (gap > 1e-3)
+    ok[n:] = False
+    assert ok.sum() > 300
+    assert _relrows(x.grad.cpu().numpy(), z["dx"])[ok].max() <= 1e-4
+
+
+@pytest.mark.parametrize("n", [1, 2, 255, 256, 257, 4096, (1 << 20) + 3])
+def test_svd_orth_fwd_bwd_vs_oracle(rr, ops, n):
+    g = torch.Generator().manual_seed(n)
+    x, up = torch.randn(n, 9, generator=g), torch.randn(n, 3, 3, generator=g)
+    xd = x.cuda().requires_grad_(True)
+    r = rr.symmetric_orthogonalization(xd)
+    r.backward(up.cuda())
+    ref = O.symmetric_orthogonalization(x.double()).numpy()
+    cond = O.svd_orth_conditioning(x).numpy()
+    err = np.abs(r.detach().cpu().numpy() - ref).reshape(n, -1).max(1)
+    assert (err * cond).max() <= 1e-6
+    assert err[cond > 0.05].max(initial=0) <= 1e-5
+    _, ds = ops.svd_orth_det(x.cuda())
+    assert np.array_equal(np.sign(ds.cpu().numpy()), np.sign(O.svd_orth_det_sign(x.double()).numpy()))
+    dref = O.svd_orth_pullback(x, up).numpy()
+    rel = _relrows(xd.grad.cpu().numpy(), dref)
+    assert rel[cond > 0.1].max(initial=0) <= 1e-4
+    assert (rel * cond).max() <= 5e-5
+    # recompute variant of the backward gives the same gradient
+    d2 = ops.svd_orth_bwd_recompute(x.cuda(), up.cuda())
+    assert _relrows(d2.cpu().numpy(), dref)[cond > 0.1].max(initial=0) <= 1e-4
+
+
+def test_svd_orth_near_rotation_inputs(rr):
+    """What a trained network emits: R + 0.1 * noise (second distribution)."""
+    g = torch.Generator().manual_seed(3)
+    n = 1 << 16
+    rot = O.sample_rotations_axis_angle(n, g).float()
+    x = (rot + 0.1 * torch.randn(n, 3, 3, generator=g)).reshape(n, 9)
+    r = rr.symmetric_orthogonalization(x.cuda()).cpu().numpy()
+    ref = O.symmetric_orthogonalization(x.double()).numpy()
+    assert np.abs(r - ref).max() <= 1e-5            # well conditioned: the plain 1e-5 bound holds for every matrix
+
+
+def test_strided_rows_are_read_in_place(rr):
+    """out[:, :9] of a (B, 12) network output (3D-Pose/main2.py:94, Iterative/utility.py:105)."""
+    torch.manual_seed(2)
+    out = torch.randn(3001, 12).cuda().requires_grad_(True)
+    r = rr.symmetric_orthogonalization(out[:, :9])
+    ref = O.symmetric_orthogonalization(out.detach().cpu()[:, :9].double())
+    cond = O.svd_orth_conditioning(out.detach().cpu()[:, :9].contiguous()).numpy()
+    assert (np.abs(r.detach().cpu().numpy() - ref.numpy()).reshape(3001, -1).max(1) * cond).max() <= 1e-6
+    r.sum().backward()
+    assert out.grad.shape == (3001, 12) and float(out.grad[:, 9:].abs().max()) == 0.0
+    # 3-D input too
+    r3 = rr.symmetric_orthogonalization(out.detach()[:, :9].reshape(-1, 3, 3))
+    assert torch.equal(r3, r.detach())
+
+
+def test_full_size_properties(rr):
+    """BASELINE config 2 size (2^24): size-independent properties instead of an elementwise oracle."""
+    n = 1 << 24
+    torch.manual_seed(0)
+    x = torch.randn(n, 9, device="cuda")
+    r = rr.symmetric_orthogonalization(x)
+    rtr = torch.bmm(r.transpose(1, 2), r) - torch.eye(3, device="cuda")
+    assert float(rtr.abs().max()) <= 5e-6                      # orthogonal
+    det = torch.linalg.det(r.double())
+    assert float((det - 1).abs().max()) <= 1e-5                # proper
+    r2 = rr.symmetric_orthogonalization(r.reshape(n, 9))
+    assert float((r2 - r).abs().max()) <= 5e-6                 # idempotent on rotations
+    # equivariance: svd_orth(Q M) = Q svd_orth(M) for a rotation Q (holds to conditioning-limited accuracy)
+    q = r[:1].expand(1 << 20, 3, 3)
+    m = x[1:(1 << 20) + 1].reshape(-1, 3, 3)
+    lhs = rr.symmetric_orthogonalization(torch.bmm(q, m).reshape(-1, 9))
+    rhs = torch.bmm(q, r[1:(1 << 20) + 1])
+    assert float((lhs - rhs).abs().median()) <= 1e-6
+    # the tr(R^T M) objective is maximal: no worse than the float64 oracle on a slice
+    sl = slice(0, 1 << 16)
+    ref = O.symmetric_orthogonalization(x[sl].cpu().double())
+    obj = (r[sl].cpu().double() * x[sl].cpu().double().reshape(-1, 3, 3)).sum((1, 2))
+    obj_ref = (ref * x[sl].cpu().double().reshape(-1, 3, 3)).sum((1, 2))
+    assert float((obj_ref - obj).max()) <= 1e-5
+
+
+def test_config1_svd_plus_frobenius(rr):
+    """BASELINE config 1: 4096 random matrices, forward + Frobenius loss, vs the reference formulas on the CPU."""
+    torch.manual_seed(0)
+    x = torch.randn(4096, 9)
+    r_true = O.symmetric_orthogonalization(torch.randn(4096, 9).double()).float()
+    xr = x.double().requires_grad_(True)
+    loss_ref = O.loss_frobenius(O.symmetric_orthogonalization(xr), r_true.double())
+    loss_ref.backward()
+    xd = x.cuda().requires_grad_(True)
+    loss = rr.loss_frobenius(rr.symmetric_orthogonalization(xd), r_true.cuda())
+    loss.backward()
+    assert loss.dtype == torch.float32 and loss.dim() == 0
+    assert abs(loss.item() - loss_ref.item()) <= 1e-6
+    cond = O.svd_orth_conditioning(x).numpy()
+    rel = _relrows(xd.grad.cpu().numpy(), xr.grad.numpy())
+    assert rel[cond > 0.1].max() <= 1e-4
+    # fused op: same loss, same gradient
+    xf = x.cuda().requires_grad_(True)
+    lf = rr.svd_frobenius_loss(xf, r_true.cuda())
+    lf.backward()
+    assert abs(lf.item() - loss_ref.item()) <= 1e-6
+    assert _relrows(xf.grad.cpu().numpy(), xr.grad.numpy())[cond > 0.1].max() <= 1e-4
+
+
+def test_degenerate_inputs_are_finite_rotations(rr):
+    cases = torch.tensor([
+        [0.0] * 9, [1, 0, 0, 0, 1, 0, 0, 0, 1], [-1, 0, 0, 0, -1, 0, 0, 0, -1], [1, 0, 0, 0, 1, 0, 0, 0, -1],
+        [3, 0, 0, 0, 0, 0, 0, 0, 0], [2, 0, 0, 0, 1, 0, 0, 0, 0], [1, 1, 1, 1, 1, 1, 1, 1, 1],
+        [1e-30 * k for k in range(1, 10)], [1e30, 2e30, 3e30, 4e30, 5e30, 6e30, 7e30, 8e30, 1e31]], dtype=torch.float32)
+    x = cases.cuda().requires_grad_(True)
+    r = rr.symmetric_orthogonalization(x)
+    r.sum().backward()
+    rd = r.detach().cpu().double()
+    assert torch.isfinite(rd).all() and torch.isfinite(x.grad).all()
+    assert (rd @ rd.transpose(1, 2) - torch.eye(3, dtype=torch.float64)).abs().max() <= 1e-5
+    assert (torch.linalg.det(rd) - 1).abs().max() <= 1e-5
+
+
+def test_opcheck(ops):
+    x = torch.randn(33, 9, device="cuda", requires_grad=True)
+    torch.library.opcheck(ops.svd_orth, (x,), test_utils=("test_schema", "test_faketensor", "test_autograd_registration"))
+    a = torch.randn(33, 3, 3, device="cuda", requires_grad=True)
+    b = torch.randn(33, 3, 3, device="cuda")
+    torch.library.opcheck(ops.frobenius_mean, (a, b),
+                          test_utils=("test_schema", "test_faketensor", "test_autograd_registration"))
+    torch.library.opcheck(ops.ortho6d, (torch.randn(33, 6, device="cuda", requires_grad=True),),
+                          test_utils=("test_schema", "test_faketensor", "test_autograd_registration"))

@@ -1,0 +1,128 @@
+"""The kernels' per-record formulas (csrc/pe_math.cuh, compiled for the host) against the oracle in float64.
+CPU only: this is the arithmetic the GPU runs, minus MUFU.RSQ's last bits (the host uses 1/sqrtf)."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import reference_port as O
+import hostmath
+
+T = lambda a: torch.from_numpy(np.asarray(a))
+
+
+@pytest.fixture(scope="module")
+def hm():
+    return hostmath.load()
+
+
+def _autograd(fn, x, g):
+    x = T(x).double().requires_grad_(True)
+    y = fn(x)
+    (dx,) = torch.autograd.grad(y, x, T(g).double().reshape(y.shape))
+    return y.detach().numpy().reshape(len(g), 9), dx.numpy()
+
+
+def _rel(a, b):
+    a, b = a.reshape(len(a), -1), b.reshape(len(b), -1)
+    return np.abs(a - b).max(1) / (np.abs(b).max(1) + 1e-30)
+
+
+MAPS = [
+    ("ortho6d", 6, O.compute_rotation_matrix_from_ortho6d, "randn"),
+    ("quat", 4, O.compute_rotation_matrix_from_quaternion, "randn"),
+    ("euler", 3, O.compute_rotation_matrix_from_euler, "angle"),
+    ("ortho5d", 5, O.compute_rotation_matrix_from_ortho5d, "randn"),
+    ("expmap", 3, O.vec_3d_to_SO3, "randn"),
+]
+
+
+@pytest.mark.parametrize("name,w,fn,dist", MAPS)
+def test_map_and_pullback_vs_oracle(hm, name, w, fn, dist):
+    rng = np.random.default_rng(7)
+    n = 20000
+    x = rng.standard_normal((n, w)).astype(np.float32)
+    if dist == "angle":
+        x = rng.uniform(-np.pi, np.pi, (n, w)).astype(np.float32)
+    g = rng.standard_normal((n, 9)).astype(np.float32)
+    r = hostmath.call(hm, f"hm_{name}", x, (n, 9))
+    dx = hostmath.call(hm, f"hm_{name}_bwd", x, g, (n, w))
+    r_ref, dx_ref = _autograd(fn, x, g)
+    assert np.abs(r - r_ref).max() <= 1e-5          # north_star: outputs <= 1e-5 in fp32
+    # gradients: 1e-4 relative, away from the map's own singularities (tiny |a|, collinear 6D input).  A record whose
+    # gradient nearly cancels is measured against a tenth of the typical gradient rather than its own tiny one.
+    scale = np.abs(dx_ref).max(1)
+    err = np.abs(dx - dx_ref).max(1) / np.maximum(scale, 0.1 * np.median(scale))
+    ok = scale < 50 * np.median(scale)
+    assert ok.mean() > 0.95
+    assert np.quantile(err, 0.999) <= 1e-5
+    assert err[ok].max() <= 5e-4             # the few near-collinear 6D/5D inputs lose digits in any fp32 method
+
+
+def test_expmap_small_angles(hm):
+    rng = np.random.default_rng(3)
+    n = 4000
+    x = (rng.standard_normal((n, 3)) * np.logspace(-6, 0, n)[:, None]).astype(np.float32)
+    g = rng.standard_normal((n, 9)).astype(np.float32)
+    r = hostmath.call(hm, "hm_expmap", x, (n, 9))
+    dx = hostmath.call(hm, "hm_expmap_bwd", x, g, (n, 3))
+    r_ref, dx_ref = _autograd(O.vec_3d_to_SO3, x, g)
+    assert np.abs(r - r_ref).max() <= 1e-6
+    assert _rel(dx, dx_ref).max() <= 1e-4
+
+
+def test_svd_orth_vs_oracle(hm):
+    torch.manual_seed(0)
+    n = 1 << 16
+    x = torch.randn(n, 9)
+    ref = O.symmetric_orthogonalization(x.double()).numpy().reshape(n, 9)
+    cond = O.svd_orth_conditioning(x).numpy()
+    dref = O.svd_orth_det_sign(x.double()).numpy()
+    r, d = hostmath.call(hm, "hm_svd_orth", x.numpy(), (n, 9), (n,))
+    err = np.abs(r - ref).max(1)
+    # the error of ANY fp32 method scales like eps/cond; torch's own fp32 path reaches 1.9e-6
+    assert (err * cond).max() <= 1e-6
+    assert err[cond > 0.1].max() <= 1e-5
+    assert np.array_equal(np.sign(d), np.sign(dref))            # determinant sign: exact agreement
+    rr = r.reshape(n, 3, 3).astype(np.float64)
+    assert np.abs(rr @ rr.transpose(0, 2, 1) - np.eye(3)).max() <= 2e-6
+    assert np.abs(np.linalg.det(rr) - 1).max() <= 2e-6
+
+
+def test_svd_orth_pullback_vs_oracle(hm):
+    torch.manual_seed(1)
+    n = 1 << 15
+    x, g = torch.randn(n, 9), torch.randn(n, 9)
+    r, _ = hostmath.call(hm, "hm_svd_orth", x.numpy(), (n, 9), (n,))
+    dm = hostmath.call(hm, "hm_svd_orth_bwd", x.numpy(), r, g.numpy(), (n, 9))
+    ref = O.svd_orth_pullback(x, g).numpy().reshape(n, 9)
+    cond = O.svd_orth_conditioning(x).numpy()
+    rel = _rel(dm, ref)
+    assert rel[cond > 0.1].max() <= 1e-4                        # north_star: 1e-4 away from degenerate spectra
+    assert (rel * cond).max() <= 2e-5
+    assert np.isfinite(dm).all()
+
+
+def test_svd_orth_edge_cases(hm):
+    eye = np.eye(3, dtype=np.float32).reshape(1, 9)
+    cases = np.concatenate([
+        eye, -eye, np.zeros((1, 9), np.float32),
+        np.diag([1, 1, -1]).astype(np.float32).reshape(1, 9),
+        np.diag([3, 0, 0]).astype(np.float32).reshape(1, 9),              # rank 1
+        np.diag([2, 1, 0]).astype(np.float32).reshape(1, 9),              # rank 2
+        (1e-30 * np.arange(1, 10, dtype=np.float32)).reshape(1, 9),       # tiny
+        (1e30 * np.array([[1, 2, 3, 4, 5, 6, 7, 8, 10]], np.float32)),    # huge
+    ])
+    r, d = hostmath.call(hm, "hm_svd_orth", cases, (len(cases), 9), (len(cases),))
+    rr = r.reshape(-1, 3, 3).astype(np.float64)
+    assert np.isfinite(rr).all()
+    assert np.abs(rr @ rr.transpose(0, 2, 1) - np.eye(3)).max() <= 1e-5
+    assert np.abs(np.linalg.det(rr) - 1).max() <= 1e-5
+    assert np.allclose(rr[0], np.eye(3), atol=1e-6)
+    # rank-2 input is still uniquely determined: compare with the oracle
+    ref = O.symmetric_orthogonalization(T(cases[5:6]).double()).numpy()
+    assert np.abs(rr[5] - ref[0]).max() <= 1e-6
+    # the two fixed matrices of 3D-Pose/loss.py:28-34 are rotations: a rotation maps to itself
+    c, s = np.cos(0.3), np.sin(0.3)
+    rot = np.array([[c, -s, 0, s, c, 0, 0, 0, 1]], np.float32)
+    r2, _ = hostmath.call(hm, "hm_svd_orth", rot, (1, 9), (1,))
+    assert np.abs(r2 - rot).max() <= 1e-6
