@@ -204,7 +204,7 @@ PE_DEV void svd_orth_pullback(const float* m, const float* r, const float* g, fl
     float tr3 = (h00 + h11 + h22) * (1.0f / 3.0f);
     float fl = kDetFloor * fabsf(tr3 * tr3 * tr3);
     det = fmaxf(det, fl);
-    float inv = sc / fmaxf(det, 1e-37f);
+    float inv = det > 1e-30f ? sc / det : 0.f;  // det = 0 only for the zero matrix: define its gradient as 0
     float y0 = inv * fmaf(c00, z0, fmaf(c01, z1, c02 * z2));
     float y1 = inv * fmaf(c01, z0, fmaf(c11, z1, c12 * z2));
     float y2 = inv * fmaf(c02, z0, fmaf(c12, z1, c22 * z2));

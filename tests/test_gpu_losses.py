@@ -136,4 +136,5 @@ def test_kabsch_full_size_round_trip(rr):
     r, t = rr.kabsch(p, q)
     assert float((r - rot).abs().max()) <= 2e-5
     assert float(t.abs().max()) <= 2e-5
-    assert float(rr.mean_angle_error(r, rot).item()) <= 1e-3
+    # float64 acos of a trace built from fp32 entries has a ~0.03 degree floor near zero angle (sqrt(2 * 3e-7) rad)
+    assert float(rr.mean_angle_error(r, rot).item()) <= 0.05

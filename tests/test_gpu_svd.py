@@ -23,8 +23,11 @@ def ops():
 
 
 def _relrows(a, b):
+    """per-record gradient error relative to the record's own gradient, or to a tenth of the typical gradient when
+    the record's gradient nearly cancels (relative error of a near-zero vector is meaningless)."""
     a, b = np.asarray(a, np.float64).reshape(len(a), -1), np.asarray(b, np.float64).reshape(len(b), -1)
-    return np.abs(a - b).max(1) / (np.abs(b).max(1) + 1e-30)
+    scale = np.abs(b).max(1)
+    return np.abs(a - b).max(1) / (np.maximum(scale, 0.1 * np.median(scale)) + 1e-30)
 
 
 def test_svd_orth_matches_reference_golden(rr, ops, golden):
@@ -57,7 +60,8 @@ def test_svd_orth_matches_reference_golden(rr, ops, golden):
     ok = (cond > 0.1) & (gap > 1e-3)
     ok[n:] = False
     assert ok.sum() > 300
-    assert _relrows(x.grad.cpu().numpy(), z["dx"])[ok].max() <= 1e-4
+    # (the appended known-answer cases are degenerate: the reference's autograd returns NaN for some of them)
+    assert _relrows(x.grad.cpu().numpy()[ok], z["dx"][ok]).max() <= 1e-4
 
 
 @pytest.mark.parametrize("n", [1, 2, 255, 256, 257, 4096, (1 << 20) + 3])
