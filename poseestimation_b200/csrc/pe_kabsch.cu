@@ -88,7 +88,7 @@ __global__ void __launch_bounds__(kKWarps * 32, 1) kabsch_kernel(const KabschPar
     auto flush = [&]() {
         if (lane < parked) {
             float r[9], ds;
-            svd_orth<kSweeps>(keep, r, ds);
+            svd_orth_fast(keep, r, ds);
             float* dst = prm.r + kpair * 9;
 #pragma unroll
             for (int i = 0; i < 9; ++i) dst[i] = r[i];

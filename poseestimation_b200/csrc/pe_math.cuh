@@ -167,6 +167,131 @@ PE_DEV void svd_orth(const float* m, float* r, float& dsign) {
 
 constexpr int kSweeps = 4;  // 4 sweeps reach the fp32 conditioning limit on Gaussian inputs
 
+// ---------------------------------------------------------------------------------------------------------
+// Production variant of svd_orth (same result, ~35 % fewer issue slots):
+//  * V is NOT accumulated.  At convergence A = M V = U S, so the right vectors follow from the left ones:
+//    v_j ~ M^T u_j.  v0 = normalise(M^T u0); v1 = normalise(M^T u1 - (.,v0) v0) (the Gram-Schmidt step removes
+//    exactly the eps*s0/s1-amplified part of u1's error); v2 = v0 x v1.  R = u0 v0^T + u1 v1^T + (u0 x u1)(v0 x v1)^T.
+//  * 10 rotations in the order (0,1)(0,2)(1,2)(0,2)(0,1)(1,2)(0,2)(0,1)(0,2)(1,2) instead of 4 cyclic sweeps (12):
+//    found by exhaustive search over pair sequences; same err*cond as 12 on 2^19 Gaussian matrices.
+//  * rows 0 and 1 of every column live in one 64-bit register pair and are rotated with packed FMUL2/FFMA2
+//    (sm_100 fp32x2): half the issue slots for the rotation application.
+struct F2 {
+    float x, y;
+};
+PE_DEV F2 f2_fma(F2 a, F2 b, F2 c) {
+#ifdef __CUDA_ARCH__
+    float2 r = __ffma2_rn(make_float2(a.x, a.y), make_float2(b.x, b.y), make_float2(c.x, c.y));
+    return F2{r.x, r.y};
+#else
+    return F2{fmaf(a.x, b.x, c.x), fmaf(a.y, b.y, c.y)};
+#endif
+}
+PE_DEV F2 f2_mul(F2 a, F2 b) {
+#ifdef __CUDA_ARCH__
+    float2 r = __fmul2_rn(make_float2(a.x, a.y), make_float2(b.x, b.y));
+    return F2{r.x, r.y};
+#else
+    return F2{a.x * b.x, a.y * b.y};
+#endif
+}
+// one sorting Hestenes rotation of columns p, q held as (rows 0-1 packed, row 2 scalar)
+PE_DEV void hestenes_a(F2& p01, float& p2, F2& q01, float& q2) {
+    float al = fmaf(p2, p2, fmaf(p01.y, p01.y, p01.x * p01.x));
+    float be = fmaf(q2, q2, fmaf(q01.y, q01.y, q01.x * q01.x));
+    float ga = fmaf(p2, q2, fmaf(p01.y, q01.y, p01.x * q01.x));
+    float dh = 0.5f * (al - be);
+    float ad = fmaxf(fabsf(dh), 1e-18f);
+    float r = rsqrt_fast(fmaf(ad, ad, ga * ga));
+    float c2 = ad * r, s2 = ga * r;
+    float w = fmaf(2.0f, c2, 2.0f);
+    float h = rsqrt_fast(w);
+    float c = 0.5f * w * h, s = s2 * h;
+    bool neg = dh < 0.0f;
+    float cp = neg ? s : c, sp = neg ? c : s;
+    F2 C{cp, cp}, S{sp, sp}, N{-sp, -sp};
+    F2 pn = f2_fma(C, p01, f2_mul(S, q01));
+    F2 qn = f2_fma(C, q01, f2_mul(N, p01));
+    float t = p2;
+    p2 = fmaf(cp, t, sp * q2);
+    q2 = fmaf(cp, q2, -sp * t);
+    p01 = pn; q01 = qn;
+}
+// a unit vector orthogonal to the unit vector u (any one; used only for rank-deficient inputs)
+PE_DEV void any_orthogonal(float u0, float u1, float u2, float& o0, float& o1, float& o2) {
+    float ax = fabsf(u0), ay = fabsf(u1), az = fabsf(u2);
+    float e0 = (ax <= ay && ax <= az) ? 1.f : 0.f;
+    float e1 = (e0 == 0.f && ay <= az) ? 1.f : 0.f;
+    float e2 = (e0 == 0.f && e1 == 0.f) ? 1.f : 0.f;
+    float c0 = u1 * e2 - u2 * e1, c1 = u2 * e0 - u0 * e2, c2 = u0 * e1 - u1 * e0;
+    float kk = rsqrt_nr(c0 * c0 + c1 * c1 + c2 * c2);
+    o0 = c0 * kk; o1 = c1 * kk; o2 = c2 * kk;
+}
+PE_DEV void svd_orth_fast(const float* m, float* r, float& dsign) {
+    const float sc = pow2_prescale(m);
+    // column j: rows 0,1 packed, row 2 scalar
+    F2 c0{m[0] * sc, m[3] * sc}, c1{m[1] * sc, m[4] * sc}, c2{m[2] * sc, m[5] * sc};
+    float z0 = m[6] * sc, z1 = m[7] * sc, z2 = m[8] * sc;
+    hestenes_a(c0, z0, c1, z1);
+    hestenes_a(c0, z0, c2, z2);
+    hestenes_a(c1, z1, c2, z2);
+    hestenes_a(c0, z0, c2, z2);
+    hestenes_a(c0, z0, c1, z1);
+    hestenes_a(c1, z1, c2, z2);
+    hestenes_a(c0, z0, c2, z2);
+    hestenes_a(c0, z0, c1, z1);
+    hestenes_a(c0, z0, c2, z2);
+    hestenes_a(c1, z1, c2, z2);
+    float al0 = fmaf(z0, z0, fmaf(c0.y, c0.y, c0.x * c0.x));
+    float al1 = fmaf(z1, z1, fmaf(c1.y, c1.y, c1.x * c1.x));
+    float k0 = rsqrt_fast(al0), k1 = rsqrt_fast(al1);
+    float u00 = c0.x * k0, u10 = c0.y * k0, u20 = z0 * k0;
+    float u01 = c1.x * k1, u11 = c1.y * k1, u21 = z1 * k1;
+    if (__builtin_expect(!(al1 > 1e-24f * al0) || !(al0 > 0.f), 0)) {  // rank <= 1, or the zero matrix
+        if (al0 == 0.f) { u00 = 1.f; u10 = 0.f; u20 = 0.f; }
+        if (al0 == al0) any_orthogonal(u00, u10, u20, u01, u11, u21);
+    }
+    float u02 = fmaf(u10, u21, -u20 * u11);
+    float u12 = fmaf(u20, u01, -u00 * u21);
+    float u22 = fmaf(u00, u11, -u10 * u01);
+    dsign = (fmaf(c2.x, u02, fmaf(c2.y, u12, z2 * u22)) < 0.f) ? -1.f : 1.f;
+    // right vectors from the left ones: w_j = (sc M)^T u_j
+    float m0 = m[0] * sc, m1 = m[1] * sc, m2 = m[2] * sc, m3 = m[3] * sc, m4 = m[4] * sc, m5 = m[5] * sc,
+          m6 = m[6] * sc, m7 = m[7] * sc, m8 = m[8] * sc;
+    float w00 = fmaf(m6, u20, fmaf(m3, u10, m0 * u00));
+    float w10 = fmaf(m7, u20, fmaf(m4, u10, m1 * u00));
+    float w20 = fmaf(m8, u20, fmaf(m5, u10, m2 * u00));
+    float w01 = fmaf(m6, u21, fmaf(m3, u11, m0 * u01));
+    float w11 = fmaf(m7, u21, fmaf(m4, u11, m1 * u01));
+    float w21 = fmaf(m8, u21, fmaf(m5, u11, m2 * u01));
+    float n0 = fmaf(w20, w20, fmaf(w10, w10, w00 * w00));
+    float j0 = rsqrt_fast(n0);
+    float v00 = w00 * j0, v10 = w10 * j0, v20 = w20 * j0;
+    if (__builtin_expect(!(n0 > 0.f), 0)) {
+        if (n0 == 0.f) { v00 = 1.f; v10 = 0.f; v20 = 0.f; }
+    }
+    float pr = fmaf(w21, v20, fmaf(w11, v10, w01 * v00));
+    w01 = fmaf(-pr, v00, w01); w11 = fmaf(-pr, v10, w11); w21 = fmaf(-pr, v20, w21);
+    float n1 = fmaf(w21, w21, fmaf(w11, w11, w01 * w01));
+    float j1 = rsqrt_fast(n1);
+    float v01 = w01 * j1, v11 = w11 * j1, v21 = w21 * j1;
+    if (__builtin_expect(!(n1 > 1e-30f), 0)) {
+        if (n1 == n1) any_orthogonal(v00, v10, v20, v01, v11, v21);
+    }
+    float v02 = fmaf(v10, v21, -v20 * v11);
+    float v12 = fmaf(v20, v01, -v00 * v21);
+    float v22 = fmaf(v00, v11, -v10 * v01);
+    r[0] = fmaf(u02, v02, fmaf(u01, v01, u00 * v00));
+    r[1] = fmaf(u02, v12, fmaf(u01, v11, u00 * v10));
+    r[2] = fmaf(u02, v22, fmaf(u01, v21, u00 * v20));
+    r[3] = fmaf(u12, v02, fmaf(u11, v01, u10 * v00));
+    r[4] = fmaf(u12, v12, fmaf(u11, v11, u10 * v10));
+    r[5] = fmaf(u12, v22, fmaf(u11, v21, u10 * v20));
+    r[6] = fmaf(u22, v02, fmaf(u21, v01, u20 * v00));
+    r[7] = fmaf(u22, v12, fmaf(u21, v11, u20 * v10));
+    r[8] = fmaf(u22, v22, fmaf(u21, v21, u20 * v20));
+}
+
 // Pullback of R = svd_orth(M):  given M, R and G = dL/dR, return dL/dM.
 //
 // Polar form of the closed formula in SURVEY.md 7.4 (B = D U^T G V, W_ij = (B_ij - B_ji)/(s'_i + s'_j),

@@ -29,7 +29,7 @@ struct SvdFwd {
     __device__ static __forceinline__ void run(const float* m, const float*, const float*, float* r, float* d,
                                                double*, int&, const Extra&) {
         float ds;
-        svd_orth<kSweeps>(m, r, ds);
+        svd_orth_fast(m, r, ds);
         if constexpr (DET) d[0] = ds;
     }
 };
@@ -49,7 +49,7 @@ struct SvdBwdRecompute {
     __device__ static __forceinline__ void run(const float* m, const float* g, const float*, float* dm, float*,
                                                double*, int&, const Extra&) {
         float r[9], ds;
-        svd_orth<kSweeps>(m, r, ds);
+        svd_orth_fast(m, r, ds);
         svd_orth_pullback(m, r, g, dm);
     }
 };
@@ -176,7 +176,7 @@ struct SvdFrobFwd {
     __device__ static __forceinline__ void run(const float* m, const float* rt, const float*, float* r, float*,
                                                double* red, int&, const Extra&) {
         float rr[9], ds;
-        svd_orth<kSweeps>(m, rr, ds);
+        svd_orth_fast(m, rr, ds);
         red[0] += (double)frob_dist(rr, rt);
         if constexpr (WRITE_R) {
 #pragma unroll
@@ -190,7 +190,7 @@ struct SvdFrobBwd {
     __device__ static __forceinline__ void run(const float* m, const float* rt, const float*, float* dm, float*,
                                                double*, int&, const Extra& ex) {
         float r[9], g[9], ds, s = 0.f;
-        svd_orth<kSweeps>(m, r, ds);
+        svd_orth_fast(m, r, ds);
 #pragma unroll
         for (int i = 0; i < 9; ++i) { g[i] = r[i] - rt[i]; s = fmaf(g[i], g[i], s); }
         float k = s > 0.f ? __ldg(ex.gout) * ex.mul * rsqrt_nr(s) : 0.f;

@@ -5,7 +5,9 @@
 
 #define LOOP for (long i = 0; i < n; ++i)
 extern "C" {
-void hm_svd_orth(const float* m, float* r, float* d, long n) { LOOP pe::svd_orth<pe::kSweeps>(m + 9 * i, r + 9 * i, d[i]); }
+void hm_svd_orth(const float* m, float* r, float* d, long n) { LOOP pe::svd_orth_fast(m + 9 * i, r + 9 * i, d[i]); }
+// the 4-sweep, V-accumulating variant the production one was derived from (kept for A/B tests)
+void hm_svd_orth_4sweep(const float* m, float* r, float* d, long n) { LOOP pe::svd_orth<pe::kSweeps>(m + 9 * i, r + 9 * i, d[i]); }
 void hm_svd_orth_bwd(const float* m, const float* r, const float* g, float* dm, long n) {
     LOOP pe::svd_orth_pullback(m + 9 * i, r + 9 * i, g + 9 * i, dm + 9 * i);
 }
