@@ -1,0 +1,217 @@
+// Lane abstraction for the SVD math: the same formulas instantiate for T = float (one matrix per thread) and
+// T = F2 (TWO matrices per thread, one in each half of a 64-bit register pair).  On sm_100 the F2 arithmetic maps
+// to the packed fp32x2 instructions FMUL2 / FFMA2 / FADD2: one issue slot does the work for both matrices.  The SVD
+// kernels are issue-bound, not HBM-bound, so this is the lever that matters.
+#pragma once
+#include "pe_math.cuh"
+
+namespace pe {
+
+struct B2 {
+    bool x, y;
+};
+
+// ---- float ---------------------------------------------------------------------------------------------------
+PE_DEV float t_set(float, float v) { return v; }  // first argument only selects the overload
+PE_DEV float t_mul(float a, float b) { return a * b; }
+PE_DEV float t_fma(float a, float b, float c) { return fmaf(a, b, c); }
+PE_DEV float t_add(float a, float b) { return a + b; }
+PE_DEV float t_sub(float a, float b) { return a - b; }
+PE_DEV float t_neg(float a) { return -a; }
+PE_DEV float t_abs(float a) { return fabsf(a); }
+PE_DEV float t_max(float a, float b) { return fmaxf(a, b); }
+PE_DEV float t_rsq(float a) { return rsqrt_fast(a); }
+PE_DEV float t_sqrt(float a) { return sqrtf(a); }
+PE_DEV bool t_ltz(float a) { return a < 0.f; }
+PE_DEV float t_sel(bool m, float a, float b) { return m ? a : b; }
+PE_DEV float t_prescale(const float* m) { return pow2_prescale(m); }
+
+// ---- F2 ------------------------------------------------------------------------------------------------------
+PE_DEV F2 t_set(F2, float v) { return F2{v, v}; }
+PE_DEV F2 t_mul(F2 a, F2 b) { return f2_mul(a, b); }
+PE_DEV F2 t_fma(F2 a, F2 b, F2 c) { return f2_fma(a, b, c); }
+PE_DEV F2 t_add(F2 a, F2 b) {
+#ifdef __CUDA_ARCH__
+    float2 r = __fadd2_rn(make_float2(a.x, a.y), make_float2(b.x, b.y));
+    return F2{r.x, r.y};
+#else
+    return F2{a.x + b.x, a.y + b.y};
+#endif
+}
+PE_DEV F2 t_neg(F2 a) { return F2{-a.x, -a.y}; }
+PE_DEV F2 t_sub(F2 a, F2 b) { return t_add(a, t_neg(b)); }
+PE_DEV F2 t_abs(F2 a) { return F2{fabsf(a.x), fabsf(a.y)}; }
+PE_DEV F2 t_max(F2 a, F2 b) { return F2{fmaxf(a.x, b.x), fmaxf(a.y, b.y)}; }
+PE_DEV F2 t_rsq(F2 a) { return F2{rsqrt_fast(a.x), rsqrt_fast(a.y)}; }
+PE_DEV F2 t_sqrt(F2 a) { return F2{sqrtf(a.x), sqrtf(a.y)}; }
+PE_DEV B2 t_ltz(F2 a) { return B2{a.x < 0.f, a.y < 0.f}; }
+PE_DEV F2 t_sel(B2 m, F2 a, F2 b) { return F2{m.x ? a.x : b.x, m.y ? a.y : b.y}; }
+PE_DEV F2 t_prescale(const F2* m) {
+    float a[9], b[9];
+#pragma unroll
+    for (int i = 0; i < 9; ++i) { a[i] = m[i].x; b[i] = m[i].y; }
+    return F2{pow2_prescale(a), pow2_prescale(b)};
+}
+PE_DEV float lane_get(float v, int) { return v; }
+PE_DEV float lane_get(F2 v, int k) { return k ? v.y : v.x; }
+PE_DEV void lane_put(float& v, int, float s) { v = s; }
+PE_DEV void lane_put(F2& v, int k, float s) { if (k) v.y = s; else v.x = s; }
+template <class T> struct LaneCount { static constexpr int value = 1; };
+template <> struct LaneCount<F2> { static constexpr int value = 2; };
+
+// ---- the Jacobi rotation, one (or two) matrices, columns as three separate rows ----------------------------------
+template <class T>
+PE_DEV void hestenes_t(T& p0, T& p1, T& p2, T& q0, T& q1, T& q2) {
+    const T z = p0;  // overload selector
+    T al = t_fma(p2, p2, t_fma(p1, p1, t_mul(p0, p0)));
+    T be = t_fma(q2, q2, t_fma(q1, q1, t_mul(q0, q0)));
+    T ga = t_fma(p2, q2, t_fma(p1, q1, t_mul(p0, q0)));
+    T dh = t_mul(t_set(z, 0.5f), t_sub(al, be));
+    T ad = t_max(t_abs(dh), t_set(z, 1e-18f));
+    T r = t_rsq(t_fma(ad, ad, t_mul(ga, ga)));
+    T c2 = t_mul(ad, r), s2 = t_mul(ga, r);
+    T w = t_fma(t_set(z, 2.0f), c2, t_set(z, 2.0f));
+    T h = t_rsq(w);
+    T c = t_mul(t_mul(t_set(z, 0.5f), w), h), s = t_mul(s2, h);
+    auto neg = t_ltz(dh);
+    T cp = t_sel(neg, s, c), sp = t_sel(neg, c, s), ns = t_neg(sp);
+    T t;
+    t = p0; p0 = t_fma(cp, t, t_mul(sp, q0)); q0 = t_fma(cp, q0, t_mul(ns, t));
+    t = p1; p1 = t_fma(cp, t, t_mul(sp, q1)); q1 = t_fma(cp, q1, t_mul(ns, t));
+    t = p2; p2 = t_fma(cp, t, t_mul(sp, q2)); q2 = t_fma(cp, q2, t_mul(ns, t));
+}
+
+// Same algorithm as svd_orth_fast (pe_math.cuh), lane-generic.  Degenerate lanes (rank <= 1, zero, NaN) are
+// detected and redone with the scalar routine, which owns the special cases.
+template <class T>
+PE_DEV void svd_orth_t(const T* m, T* r, T& dsign) {
+    const T z = m[0];
+    const T sc = t_prescale(m);
+    T a[9];
+#pragma unroll
+    for (int i = 0; i < 9; ++i) a[i] = t_mul(m[i], sc);
+    // column j = (c[j], c[3+j], c[6+j])
+    T c00 = a[0], c01 = a[1], c02 = a[2], c10 = a[3], c11 = a[4], c12 = a[5], c20 = a[6], c21 = a[7], c22 = a[8];
+    hestenes_t(c00, c10, c20, c01, c11, c21);
+    hestenes_t(c00, c10, c20, c02, c12, c22);
+    hestenes_t(c01, c11, c21, c02, c12, c22);
+    hestenes_t(c00, c10, c20, c02, c12, c22);
+    hestenes_t(c00, c10, c20, c01, c11, c21);
+    hestenes_t(c01, c11, c21, c02, c12, c22);
+    hestenes_t(c00, c10, c20, c02, c12, c22);
+    hestenes_t(c00, c10, c20, c01, c11, c21);
+    hestenes_t(c00, c10, c20, c02, c12, c22);
+    hestenes_t(c01, c11, c21, c02, c12, c22);
+    T al0 = t_fma(c20, c20, t_fma(c10, c10, t_mul(c00, c00)));
+    T al1 = t_fma(c21, c21, t_fma(c11, c11, t_mul(c01, c01)));
+    T k0 = t_rsq(al0), k1 = t_rsq(al1);
+    T u00 = t_mul(c00, k0), u10 = t_mul(c10, k0), u20 = t_mul(c20, k0);
+    T u01 = t_mul(c01, k1), u11 = t_mul(c11, k1), u21 = t_mul(c21, k1);
+    T u02 = t_fma(u10, u21, t_neg(t_mul(u20, u11)));
+    T u12 = t_fma(u20, u01, t_neg(t_mul(u00, u21)));
+    T u22 = t_fma(u00, u11, t_neg(t_mul(u10, u01)));
+    T dd = t_fma(c02, u02, t_fma(c12, u12, t_mul(c22, u22)));
+    dsign = t_sel(t_ltz(dd), t_set(z, -1.f), t_set(z, 1.f));
+    // right vectors from the left ones: w_j = (sc M)^T u_j, Gram-Schmidt, cross product
+    T w00 = t_fma(a[6], u20, t_fma(a[3], u10, t_mul(a[0], u00)));
+    T w10 = t_fma(a[7], u20, t_fma(a[4], u10, t_mul(a[1], u00)));
+    T w20 = t_fma(a[8], u20, t_fma(a[5], u10, t_mul(a[2], u00)));
+    T w01 = t_fma(a[6], u21, t_fma(a[3], u11, t_mul(a[0], u01)));
+    T w11 = t_fma(a[7], u21, t_fma(a[4], u11, t_mul(a[1], u01)));
+    T w21 = t_fma(a[8], u21, t_fma(a[5], u11, t_mul(a[2], u01)));
+    T n0 = t_fma(w20, w20, t_fma(w10, w10, t_mul(w00, w00)));
+    T j0 = t_rsq(n0);
+    T v00 = t_mul(w00, j0), v10 = t_mul(w10, j0), v20 = t_mul(w20, j0);
+    T pr = t_neg(t_fma(w21, v20, t_fma(w11, v10, t_mul(w01, v00))));
+    w01 = t_fma(pr, v00, w01); w11 = t_fma(pr, v10, w11); w21 = t_fma(pr, v20, w21);
+    T n1 = t_fma(w21, w21, t_fma(w11, w11, t_mul(w01, w01)));
+    T j1 = t_rsq(n1);
+    T v01 = t_mul(w01, j1), v11 = t_mul(w11, j1), v21 = t_mul(w21, j1);
+    T v02 = t_fma(v10, v21, t_neg(t_mul(v20, v11)));
+    T v12 = t_fma(v20, v01, t_neg(t_mul(v00, v21)));
+    T v22 = t_fma(v00, v11, t_neg(t_mul(v10, v01)));
+    r[0] = t_fma(u02, v02, t_fma(u01, v01, t_mul(u00, v00)));
+    r[1] = t_fma(u02, v12, t_fma(u01, v11, t_mul(u00, v10)));
+    r[2] = t_fma(u02, v22, t_fma(u01, v21, t_mul(u00, v20)));
+    r[3] = t_fma(u12, v02, t_fma(u11, v01, t_mul(u10, v00)));
+    r[4] = t_fma(u12, v12, t_fma(u11, v11, t_mul(u10, v10)));
+    r[5] = t_fma(u12, v22, t_fma(u11, v21, t_mul(u10, v20)));
+    r[6] = t_fma(u22, v02, t_fma(u21, v01, t_mul(u20, v00)));
+    r[7] = t_fma(u22, v12, t_fma(u21, v11, t_mul(u20, v10)));
+    r[8] = t_fma(u22, v22, t_fma(u21, v21, t_mul(u20, v20)));
+    // degenerate lanes: hand them to the scalar routine (rare: rank <= 1, all-zero, non-finite)
+#pragma unroll
+    for (int k = 0; k < LaneCount<T>::value; ++k) {
+        float A0 = lane_get(al0, k), A1 = lane_get(al1, k), N0 = lane_get(n0, k), N1 = lane_get(n1, k);
+        if (__builtin_expect(!(A1 > 1e-24f * A0) || !(A0 > 0.f) || !(N0 > 0.f) || !(N1 > 1e-30f), 0)) {
+            float ms[9], rs[9], ds;
+#pragma unroll
+            for (int i = 0; i < 9; ++i) ms[i] = lane_get(m[i], k);
+            svd_orth_fast(ms, rs, ds);
+#pragma unroll
+            for (int i = 0; i < 9; ++i) lane_put(r[i], k, rs[i]);
+            lane_put(dsign, k, ds);
+        }
+    }
+}
+
+// Pullback of R = svd_orth(M), lane-generic (formulas and guards: svd_orth_pullback in pe_math.cuh).
+template <class T>
+PE_DEV void svd_orth_pullback_t(const T* m, const T* r, const T* g, T* dm) {
+    const T z = m[0];
+    const T sc = t_prescale(m);
+    T n[9];
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = 0; j < 3; ++j)
+            n[3 * i + j] = t_mul(sc, t_fma(r[6 + i], m[6 + j], t_fma(r[3 + i], m[3 + j], t_mul(r[i], m[j]))));
+    const T half = t_set(z, 0.5f);
+    T h01 = t_neg(t_mul(half, t_add(n[1], n[3]))), h02 = t_neg(t_mul(half, t_add(n[2], n[6]))),
+      h12 = t_neg(t_mul(half, t_add(n[5], n[7])));
+    T h00 = t_add(n[4], n[8]), h11 = t_add(n[0], n[8]), h22 = t_add(n[0], n[4]);
+    T t01 = t_fma(r[6], g[7], t_fma(r[3], g[4], t_mul(r[0], g[1])));
+    T t02 = t_fma(r[6], g[8], t_fma(r[3], g[5], t_mul(r[0], g[2])));
+    T t10 = t_fma(r[7], g[6], t_fma(r[4], g[3], t_mul(r[1], g[0])));
+    T t12 = t_fma(r[7], g[8], t_fma(r[4], g[5], t_mul(r[1], g[2])));
+    T t20 = t_fma(r[8], g[6], t_fma(r[5], g[3], t_mul(r[2], g[0])));
+    T t21 = t_fma(r[8], g[7], t_fma(r[5], g[4], t_mul(r[2], g[1])));
+    T z0 = t_sub(t21, t12), z1 = t_sub(t02, t20), z2 = t_sub(t10, t01);
+    T c00 = t_fma(h11, h22, t_neg(t_mul(h12, h12))), c01 = t_fma(h02, h12, t_neg(t_mul(h01, h22))),
+      c02 = t_fma(h01, h12, t_neg(t_mul(h02, h11)));
+    T c11 = t_fma(h00, h22, t_neg(t_mul(h02, h02))), c12 = t_fma(h01, h02, t_neg(t_mul(h00, h12))),
+      c22 = t_fma(h00, h11, t_neg(t_mul(h01, h01)));
+    T det = t_fma(h00, c00, t_fma(h01, c01, t_mul(h02, c02)));
+    T tr3 = t_mul(t_add(t_add(h00, h11), h22), t_set(z, 1.0f / 3.0f));
+    T fl = t_mul(t_set(z, kDetFloor), t_abs(t_mul(t_mul(tr3, tr3), tr3)));
+    det = t_max(det, fl);
+    T inv = z;
+#pragma unroll
+    for (int k = 0; k < LaneCount<T>::value; ++k) {
+        float d = lane_get(det, k);
+        lane_put(inv, k, d > 1e-30f ? lane_get(sc, k) / d : 0.f);
+    }
+    T y0 = t_mul(inv, t_fma(c00, z0, t_fma(c01, z1, t_mul(c02, z2))));
+    T y1 = t_mul(inv, t_fma(c01, z0, t_fma(c11, z1, t_mul(c12, z2))));
+    T y2 = t_mul(inv, t_fma(c02, z0, t_fma(c12, z1, t_mul(c22, z2))));
+    T ny0 = t_neg(y0), ny1 = t_neg(y1), ny2 = t_neg(y2);
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        T r0 = r[3 * i], r1 = r[3 * i + 1], r2 = r[3 * i + 2];
+        dm[3 * i + 0] = t_fma(r1, y2, t_mul(r2, ny1));
+        dm[3 * i + 1] = t_fma(r2, y0, t_mul(r0, ny2));
+        dm[3 * i + 2] = t_fma(r0, y1, t_mul(r1, ny0));
+    }
+}
+
+// d = a - b and |d|_F^2, lane-generic
+template <class T>
+PE_DEV T diff9_sq(const T* a, const T* b, T* d) {
+    d[0] = t_sub(a[0], b[0]);
+    T s = t_mul(d[0], d[0]);
+#pragma unroll
+    for (int i = 1; i < 9; ++i) { d[i] = t_sub(a[i], b[i]); s = t_fma(d[i], d[i], s); }
+    return s;
+}
+
+}  // namespace pe

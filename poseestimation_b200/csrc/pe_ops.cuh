@@ -1,7 +1,7 @@
 // The per-record ops of the path, written against the streaming engine (pe_stream.cuh).
 // Each Op names the reference function it replaces; the math is in pe_math.cuh.
 #pragma once
-#include "pe_math.cuh"
+#include "pe_lanes.cuh"
 #include "pe_stream.cuh"
 
 namespace pe {
@@ -15,43 +15,58 @@ constexpr int stages_for(int witot, int wotot, int budget = 54 * 1024) {
 
 struct NoExtra {};
 
-#define PE_OP_COMMON(NAME, I0, I1, I2, O0, O1, NR, FL, MB)                                   \
+#define PE_OP_COMMON_R(NAME, I0, I1, I2, O0, O1, NR, FL, MB, R)                              \
     static constexpr int WI0 = (I0), WI1 = (I1), WI2 = (I2), WO0 = (O0), WO1 = (O1), NRED = (NR); \
     static constexpr bool FLAG = (FL);                                                       \
-    static constexpr int STAGES = stages_for(WI0 + WI1 + WI2, WO0 + WO1), MINB = (MB);       \
+    static constexpr int RPT = (R);                                                          \
+    static constexpr int STAGES = stages_for((R) * (WI0 + WI1 + WI2), (R) * (WO0 + WO1), (R) * 54 * 1024); \
+    static constexpr int MINB = (MB);                                                        \
     static const char* name() { return NAME; }
+// one record per thread
+#define PE_OP_COMMON(NAME, I0, I1, I2, O0, O1, NR, FL, MB) PE_OP_COMMON_R(NAME, I0, I1, I2, O0, O1, NR, FL, MB, 1)
+// two records per thread, packed fp32x2 arithmetic (the SVD ops: issue-bound)
+#define PE_OP_COMMON2(NAME, I0, I1, I2, O0, O1, NR, FL, MB) PE_OP_COMMON_R(NAME, I0, I1, I2, O0, O1, NR, FL, MB, 2)
 
 // ---- a1 symmetric_orthogonalization (rotation_representation.py:192-206) ------------------------------------
+// Every SVD op has a lane-generic body: `run` (T = float) serves the direct kernel, `run2` (T = F2) the TMA kernel.
 template <bool DET>
 struct SvdFwd {
-    PE_OP_COMMON("svd_orth_fwd", 9, 0, 0, 9, DET ? 1 : 0, 0, false, 4)
+    PE_OP_COMMON2("svd_orth_fwd", 9, 0, 0, 9, DET ? 1 : 0, 0, false, 2)
     using Extra = NoExtra;
-    __device__ static __forceinline__ void run(const float* m, const float*, const float*, float* r, float* d,
-                                               double*, int&, const Extra&) {
-        float ds;
-        svd_orth_fast(m, r, ds);
+    template <class T>
+    __device__ static __forceinline__ void body(const T* m, T* r, T* d) {
+        T ds;
+        svd_orth_t(m, r, ds);
         if constexpr (DET) d[0] = ds;
     }
+    __device__ static __forceinline__ void run(const float* m, const float*, const float*, float* r, float* d,
+                                               double*, int&, const Extra&) { body(m, r, d); }
+    __device__ static __forceinline__ void run2(const F2* m, const F2*, const F2*, F2* r, F2* d, double*, int&,
+                                                bool, bool, const Extra&) { body(m, r, d); }
 };
 // pullback with the saved forward output: in = (m, r, g)
 struct SvdBwdSaved {
-    PE_OP_COMMON("svd_orth_bwd", 9, 9, 9, 9, 0, 0, false, 3)
+    PE_OP_COMMON2("svd_orth_bwd", 9, 9, 9, 9, 0, 0, false, 2)
     using Extra = NoExtra;
     __device__ static __forceinline__ void run(const float* m, const float* r, const float* g, float* dm, float*,
-                                               double*, int&, const Extra&) {
-        svd_orth_pullback(m, r, g, dm);
-    }
+                                               double*, int&, const Extra&) { svd_orth_pullback_t(m, r, g, dm); }
+    __device__ static __forceinline__ void run2(const F2* m, const F2* r, const F2* g, F2* dm, F2*, double*, int&,
+                                                bool, bool, const Extra&) { svd_orth_pullback_t(m, r, g, dm); }
 };
 // pullback that recomputes r from m: in = (m, g)
 struct SvdBwdRecompute {
-    PE_OP_COMMON("svd_orth_bwd_recompute", 9, 9, 0, 9, 0, 0, false, 3)
+    PE_OP_COMMON2("svd_orth_bwd_recompute", 9, 9, 0, 9, 0, 0, false, 2)
     using Extra = NoExtra;
-    __device__ static __forceinline__ void run(const float* m, const float* g, const float*, float* dm, float*,
-                                               double*, int&, const Extra&) {
-        float r[9], ds;
-        svd_orth_fast(m, r, ds);
-        svd_orth_pullback(m, r, g, dm);
+    template <class T>
+    __device__ static __forceinline__ void body(const T* m, const T* g, T* dm) {
+        T r[9], ds;
+        svd_orth_t(m, r, ds);
+        svd_orth_pullback_t(m, r, g, dm);
     }
+    __device__ static __forceinline__ void run(const float* m, const float* g, const float*, float* dm, float*,
+                                               double*, int&, const Extra&) { body(m, g, dm); }
+    __device__ static __forceinline__ void run2(const F2* m, const F2* g, const F2*, F2* dm, F2*, double*, int&,
+                                                bool, bool, const Extra&) { body(m, g, dm); }
 };
 
 // ---- elementwise maps: forward (x -> 9 words) and pullback ((x, g) -> dx) ---------------------------------------
@@ -171,32 +186,54 @@ struct AngleFwd {
 // ---- fused: loss_frobenius(symmetric_orthogonalization(x), R_true) ------------------------------------------------
 template <bool WRITE_R>
 struct SvdFrobFwd {
-    PE_OP_COMMON("svd_orth_frobenius_fwd", 9, 9, 0, WRITE_R ? 9 : 0, 0, 1, false, 4)
+    PE_OP_COMMON2("svd_orth_frobenius_fwd", 9, 9, 0, WRITE_R ? 9 : 0, 0, 1, false, 2)
     using Extra = NoExtra;
-    __device__ static __forceinline__ void run(const float* m, const float* rt, const float*, float* r, float*,
-                                               double* red, int&, const Extra&) {
-        float rr[9], ds;
-        svd_orth_fast(m, rr, ds);
-        red[0] += (double)frob_dist(rr, rt);
+    template <class T>
+    __device__ static __forceinline__ T body(const T* m, const T* rt, T* r) {
+        T rr[9], d[9], ds;
+        svd_orth_t(m, rr, ds);
+        T s = diff9_sq(rr, rt, d);
         if constexpr (WRITE_R) {
 #pragma unroll
             for (int i = 0; i < 9; ++i) r[i] = rr[i];
         }
+        return t_sqrt(s);
+    }
+    __device__ static __forceinline__ void run(const float* m, const float* rt, const float*, float* r, float*,
+                                               double* red, int&, const Extra&) {
+        red[0] += (double)body(m, rt, r);
+    }
+    __device__ static __forceinline__ void run2(const F2* m, const F2* rt, const F2*, F2* r, F2*, double* red, int&,
+                                                bool v0, bool v1, const Extra&) {
+        F2 f = body(m, rt, r);
+        red[0] += (double)((v0 ? f.x : 0.f) + (v1 ? f.y : 0.f));
     }
 };
 struct SvdFrobBwd {
-    PE_OP_COMMON("svd_orth_frobenius_bwd", 9, 9, 0, 9, 0, 0, false, 3)
+    PE_OP_COMMON2("svd_orth_frobenius_bwd", 9, 9, 0, 9, 0, 0, false, 2)
     using Extra = GradScale;
+    template <class T>
+    __device__ static __forceinline__ void body(const T* m, const T* rt, T* dm, float gs) {
+        T r[9], g[9], ds;
+        svd_orth_t(m, r, ds);
+        T s = diff9_sq(r, rt, g);
+        T k = s;
+#pragma unroll
+        for (int l = 0; l < LaneCount<T>::value; ++l) {
+            float sl = lane_get(s, l);
+            lane_put(k, l, sl > 0.f ? gs * rsqrt_nr(sl) : 0.f);
+        }
+#pragma unroll
+        for (int i = 0; i < 9; ++i) g[i] = t_mul(g[i], k);
+        svd_orth_pullback_t(m, r, g, dm);
+    }
     __device__ static __forceinline__ void run(const float* m, const float* rt, const float*, float* dm, float*,
                                                double*, int&, const Extra& ex) {
-        float r[9], g[9], ds, s = 0.f;
-        svd_orth_fast(m, r, ds);
-#pragma unroll
-        for (int i = 0; i < 9; ++i) { g[i] = r[i] - rt[i]; s = fmaf(g[i], g[i], s); }
-        float k = s > 0.f ? __ldg(ex.gout) * ex.mul * rsqrt_nr(s) : 0.f;
-#pragma unroll
-        for (int i = 0; i < 9; ++i) g[i] *= k;
-        svd_orth_pullback(m, r, g, dm);
+        body(m, rt, dm, __ldg(ex.gout) * ex.mul);
+    }
+    __device__ static __forceinline__ void run2(const F2* m, const F2* rt, const F2*, F2* dm, F2*, double*, int&,
+                                                bool, bool, const Extra& ex) {
+        body(m, rt, dm, __ldg(ex.gout) * ex.mul);
     }
 };
 

@@ -19,6 +19,7 @@
 #include <mutex>
 
 #include "pe_common.h"
+#include "pe_math.cuh"
 #include "pe_stage.cuh"
 
 namespace pe {
@@ -43,9 +44,10 @@ struct Geometry {
     static constexpr int WITOT = Op::WI0 + Op::WI1 + Op::WI2;
     static constexpr int WOTOT = Op::WO0 + Op::WO1;
     static constexpr int NOBUF = WOTOT > 0 ? 2 : 0;
+    static constexpr int TR = kTile * Op::RPT;  // records per tile (RPT records per thread)
     static constexpr int kBarBytes = 128;
-    static constexpr int kStageBytes = kTile * 4 * WITOT;
-    static constexpr int kOutBytes = kTile * 4 * WOTOT;
+    static constexpr int kStageBytes = TR * 4 * WITOT;
+    static constexpr int kOutBytes = TR * 4 * WOTOT;
     static constexpr int kSmemBytes = kBarBytes + Op::STAGES * kStageBytes + NOBUF * kOutBytes + 32 * 8 * (Op::NRED > 0 ? Op::NRED : 1);
 };
 
@@ -53,6 +55,20 @@ template <int N>
 struct RegArr {
     float v[N > 0 ? N : 1];
 };
+
+template <int N>
+struct PairArr {
+    F2 v[N > 0 ? N : 1];
+};
+// records t and t + stride of a tile -> the two halves of F2 registers
+template <int W>
+__device__ __forceinline__ void lds_pair(const float* s, int t, int stride, F2* r) {
+    float a[W], b[W];
+    lds_record<W>(s, t, a);
+    lds_record<W>(s, t + stride, b);
+#pragma unroll
+    for (int i = 0; i < W; ++i) r[i] = F2{a[i], b[i]};
+}
 
 template <class Op>
 __device__ __forceinline__ void block_reduce_and_publish(double* red, int flag, double* sums, int* flagp,
@@ -84,30 +100,30 @@ __device__ __forceinline__ void block_reduce_and_publish(double* red, int flag, 
 template <class Op>
 __global__ void __launch_bounds__(kTile, Op::MINB) stream_tma_kernel(const Params<Op> p) {
     using G = Geometry<Op>;
-    constexpr int T = kTile, S = Op::STAGES;
+    constexpr int T = kTile, TR = G::TR, S = Op::STAGES;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw);
     float* s_in = reinterpret_cast<float*>(smem_raw + G::kBarBytes);
-    float* s_out = s_in + S * T * G::WITOT;
-    double* s_red = reinterpret_cast<double*>(s_out + G::NOBUF * T * G::WOTOT);
+    float* s_out = s_in + S * TR * G::WITOT;
+    double* s_red = reinterpret_cast<double*>(s_out + G::NOBUF * TR * G::WOTOT);
 
     const int tid = threadIdx.x;
     const long long n = p.n;
-    const long long ntiles = (n + T - 1) / T;
-    const long long nfull = n / T;  // tiles [0, nfull) are complete and move by TMA
+    const long long ntiles = (n + TR - 1) / TR;
+    const long long nfull = n / TR;  // tiles [0, nfull) are complete and move by TMA
     const long long gstep = gridDim.x;
     uint64_t policy = 0;
 
     auto issue = [&](int s, long long tile) {
         // one elected thread: arm the barrier with the byte count, then one bulk copy per input array
         mbar_arrive_expect_tx(&bars[s], (uint32_t)G::kStageBytes);
-        float* dst = s_in + s * T * G::WITOT;
+        float* dst = s_in + s * TR * G::WITOT;
         int off = 0;
 #pragma unroll
         for (int k = 0; k < 3; ++k) {
             if (G::wi(k) > 0) {
-                bulk_g2s(dst + off, p.in[k] + tile * T * G::wi(k), (uint32_t)(T * 4 * G::wi(k)), &bars[s], policy);
-                off += T * G::wi(k);
+                bulk_g2s(dst + off, p.in[k] + tile * TR * G::wi(k), (uint32_t)(TR * 4 * G::wi(k)), &bars[s], policy);
+                off += TR * G::wi(k);
             }
         }
     };
@@ -136,10 +152,10 @@ __global__ void __launch_bounds__(kTile, Op::MINB) stream_tma_kernel(const Param
     for (long long tile = blockIdx.x; tile < ntiles; tile += gstep, ++it) {
         const int s = (int)(it % S);
         const uint32_t parity = (uint32_t)((it / S) & 1);
-        const long long base = tile * T;
+        const long long base = tile * TR;
         const bool full = tile < nfull;
-        const int cnt = full ? T : (int)(n - base);
-        float* si = s_in + s * T * G::WITOT;
+        const int cnt = full ? TR : (int)(n - base);
+        float* si = s_in + s * TR * G::WITOT;
 
         if (full) {
             mbar_wait(&bars[s], parity);
@@ -151,23 +167,42 @@ __global__ void __launch_bounds__(kTile, Op::MINB) stream_tma_kernel(const Param
                 if (G::wi(k) > 0) {
                     const float* src = p.in[k] + base * G::wi(k);
                     for (int w = tid; w < cnt * G::wi(k); w += T) si[off + w] = src[w];
-                    off += T * G::wi(k);
+                    off += TR * G::wi(k);
                 }
             }
             __syncthreads();
         }
 
-        RegArr<Op::WI0> i0;
-        RegArr<Op::WI1> i1;
-        RegArr<Op::WI2> i2;
-        RegArr<Op::WO0> o0;
-        RegArr<Op::WO1> o1;
-        if constexpr (Op::WI0 > 0) lds_record<Op::WI0>(si, tid, i0.v);
-        if constexpr (Op::WI1 > 0) lds_record<Op::WI1>(si + T * Op::WI0, tid, i1.v);
-        if constexpr (Op::WI2 > 0) lds_record<Op::WI2>(si + T * (Op::WI0 + Op::WI1), tid, i2.v);
-        if (tid < cnt) Op::run(i0.v, i1.v, i2.v, o0.v, o1.v, red, flag, p.ex);
+        float* so = s_out + (G::NOBUF ? (int)(it & 1) : 0) * TR * G::WOTOT;
+        const float* si1 = si + TR * Op::WI0;
+        const float* si2 = si + TR * (Op::WI0 + Op::WI1);
+        RegArr<Op::WO0 * Op::RPT> o0;
+        RegArr<Op::WO1 * Op::RPT> o1;
+        if constexpr (Op::RPT == 1) {
+            RegArr<Op::WI0> i0;
+            RegArr<Op::WI1> i1;
+            RegArr<Op::WI2> i2;
+            if constexpr (Op::WI0 > 0) lds_record<Op::WI0>(si, tid, i0.v);
+            if constexpr (Op::WI1 > 0) lds_record<Op::WI1>(si1, tid, i1.v);
+            if constexpr (Op::WI2 > 0) lds_record<Op::WI2>(si2, tid, i2.v);
+            if (tid < cnt) Op::run(i0.v, i1.v, i2.v, o0.v, o1.v, red, flag, p.ex);
+        } else {
+            // two records per thread (tid and tid + T), one in each half of a packed fp32x2 register pair
+            PairArr<Op::WI0> i0;
+            PairArr<Op::WI1> i1;
+            PairArr<Op::WI2> i2;
+            PairArr<Op::WO0> q0;
+            PairArr<Op::WO1> q1;
+            if constexpr (Op::WI0 > 0) lds_pair<Op::WI0>(si, tid, T, i0.v);
+            if constexpr (Op::WI1 > 0) lds_pair<Op::WI1>(si1, tid, T, i1.v);
+            if constexpr (Op::WI2 > 0) lds_pair<Op::WI2>(si2, tid, T, i2.v);
+            Op::run2(i0.v, i1.v, i2.v, q0.v, q1.v, red, flag, tid < cnt, tid + T < cnt, p.ex);
+#pragma unroll
+            for (int w = 0; w < Op::WO0; ++w) { o0.v[w] = q0.v[w].x; o0.v[Op::WO0 + w] = q0.v[w].y; }
+#pragma unroll
+            for (int w = 0; w < Op::WO1; ++w) { o1.v[w] = q1.v[w].x; o1.v[Op::WO1 + w] = q1.v[w].y; }
+        }
 
-        float* so = s_out + (G::NOBUF ? (int)(it & 1) : 0) * T * G::WOTOT;
         if constexpr (G::NOBUF > 0) {
             if (tid == 0) bulk_wait_read<1>();  // the store issued two tiles ago has finished reading `so`
         }
@@ -177,15 +212,18 @@ __global__ void __launch_bounds__(kTile, Op::MINB) stream_tma_kernel(const Param
             if (next < nfull) issue(s, next);
         }
         if constexpr (G::NOBUF > 0) {
-            if constexpr (Op::WO0 > 0) sts_record<Op::WO0>(so, tid, o0.v);
-            if constexpr (Op::WO1 > 0) sts_record<Op::WO1>(so + T * Op::WO0, tid, o1.v);
+#pragma unroll
+            for (int rr = 0; rr < Op::RPT; ++rr) {
+                if constexpr (Op::WO0 > 0) sts_record<Op::WO0>(so, tid + rr * T, o0.v + rr * Op::WO0);
+                if constexpr (Op::WO1 > 0) sts_record<Op::WO1>(so + TR * Op::WO0, tid + rr * T, o1.v + rr * Op::WO1);
+            }
             if (full) {
                 fence_async_smem();
                 __syncthreads();  // (B)
                 if (tid == 0) {
-                    if constexpr (Op::WO0 > 0) bulk_s2g(p.out[0] + base * Op::WO0, so, (uint32_t)(T * 4 * Op::WO0));
+                    if constexpr (Op::WO0 > 0) bulk_s2g(p.out[0] + base * Op::WO0, so, (uint32_t)(TR * 4 * Op::WO0));
                     if constexpr (Op::WO1 > 0)
-                        bulk_s2g(p.out[1] + base * Op::WO1, so + T * Op::WO0, (uint32_t)(T * 4 * Op::WO1));
+                        bulk_s2g(p.out[1] + base * Op::WO1, so + TR * Op::WO0, (uint32_t)(TR * 4 * Op::WO1));
                     bulk_commit();
                 }
             } else {
@@ -196,7 +234,7 @@ __global__ void __launch_bounds__(kTile, Op::MINB) stream_tma_kernel(const Param
                 }
                 if constexpr (Op::WO1 > 0) {
                     float* dst = p.out[1] + base * Op::WO1;
-                    for (int w = tid; w < cnt * Op::WO1; w += T) dst[w] = so[T * Op::WO0 + w];
+                    for (int w = tid; w < cnt * Op::WO1; w += T) dst[w] = so[TR * Op::WO0 + w];
                 }
             }
         }
@@ -292,7 +330,7 @@ int stream_launch(Params<Op> p, cudaStream_t stream) {
     bool tma = (p.in0_stride == G::wi(0)) && !force_direct();
     for (int k = 0; k < 3; ++k) tma = tma && (G::wi(k) == 0 || aligned16(p.in[k]));
     for (int k = 0; k < 2; ++k) tma = tma && (G::wo(k) == 0 || aligned16(p.out[k]));
-    const long long ntiles = (p.n + kTile - 1) / kTile;
+    const long long ntiles = (p.n + G::TR - 1) / G::TR;
     if (tma) {
         long long grid = (long long)cfg.sms * cfg.ctas_per_sm;
         if (grid > ntiles) grid = ntiles;

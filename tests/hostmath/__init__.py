@@ -7,13 +7,13 @@ import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 SRC = os.path.join(HERE, "hostmath.cpp")
-HDR = os.path.join(HERE, "..", "..", "poseestimation_b200", "csrc", "pe_math.cuh")
+HDRS = [os.path.join(HERE, "..", "..", "poseestimation_b200", "csrc", h) for h in ("pe_math.cuh", "pe_lanes.cuh")]
 OUT = os.path.join(HERE, "_hostmath.so")
 CUDA_INC = os.environ.get("CUDA_HOME", "/usr/local/cuda") + "/include"
 
 
 def load():
-    if not os.path.exists(OUT) or os.path.getmtime(OUT) < max(os.path.getmtime(SRC), os.path.getmtime(HDR)):
+    if not os.path.exists(OUT) or os.path.getmtime(OUT) < max(os.path.getmtime(f) for f in [SRC] + HDRS):
         # -ffp-contract=off: only the explicit fmaf() calls fuse, as in the device code's explicit FMAs
         subprocess.run(["g++", "-O2", "-ffp-contract=off", "-shared", "-fPIC", "-I", CUDA_INC, "-x", "c++", SRC,
                         "-o", OUT], check=True)

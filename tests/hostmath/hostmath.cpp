@@ -1,7 +1,7 @@
 // TEST INFRASTRUCTURE: the per-record formulas of poseestimation_b200/csrc/pe_math.cuh compiled for the HOST with
 // g++, so that the CPU test-suite can check the exact arithmetic the kernels run against the oracle without a GPU.
 // Nothing in the package loads this library.
-#include "../../poseestimation_b200/csrc/pe_math.cuh"
+#include "../../poseestimation_b200/csrc/pe_lanes.cuh"
 
 #define LOOP for (long i = 0; i < n; ++i)
 extern "C" {
@@ -21,4 +21,28 @@ void hm_ortho5d(const float* x, float* r, long n) { LOOP pe::ortho5d(x + 5 * i, 
 void hm_ortho5d_bwd(const float* x, const float* g, float* dx, long n) { LOOP pe::ortho5d_pullback(x + 5 * i, g + 9 * i, dx + 5 * i); }
 void hm_expmap(const float* x, float* r, long n) { LOOP pe::expmap(x + 3 * i, r + 9 * i); }
 void hm_expmap_bwd(const float* x, const float* g, float* dx, long n) { LOOP pe::expmap_pullback(x + 3 * i, g + 9 * i, dx + 3 * i); }
+// the two-matrices-per-thread (packed fp32x2) instantiation: record i rides with record i + n/2 (n even)
+void hm_svd_orth_x2(const float* m, float* r, float* d, long n) {
+    long h = n / 2;
+    for (long i = 0; i < h; ++i) {
+        pe::F2 mm[9], rr[9], ds;
+        for (int k = 0; k < 9; ++k) mm[k] = pe::F2{m[9 * i + k], m[9 * (i + h) + k]};
+        pe::svd_orth_t(mm, rr, ds);
+        for (int k = 0; k < 9; ++k) { r[9 * i + k] = rr[k].x; r[9 * (i + h) + k] = rr[k].y; }
+        d[i] = ds.x; d[i + h] = ds.y;
+    }
+}
+void hm_svd_orth_bwd_x2(const float* m, const float* r, const float* g, float* dm, long n) {
+    long h = n / 2;
+    for (long i = 0; i < h; ++i) {
+        pe::F2 mm[9], rr[9], gg[9], dd[9];
+        for (int k = 0; k < 9; ++k) {
+            mm[k] = pe::F2{m[9 * i + k], m[9 * (i + h) + k]};
+            rr[k] = pe::F2{r[9 * i + k], r[9 * (i + h) + k]};
+            gg[k] = pe::F2{g[9 * i + k], g[9 * (i + h) + k]};
+        }
+        pe::svd_orth_pullback_t(mm, rr, gg, dd);
+        for (int k = 0; k < 9; ++k) { dm[9 * i + k] = dd[k].x; dm[9 * (i + h) + k] = dd[k].y; }
+    }
+}
 }

@@ -126,3 +126,25 @@ def test_svd_orth_edge_cases(hm):
     rot = np.array([[c, -s, 0, s, c, 0, 0, 0, 1]], np.float32)
     r2, _ = hostmath.call(hm, "hm_svd_orth", rot, (1, 9), (1,))
     assert np.abs(r2 - rot).max() <= 1e-6
+
+
+def test_packed_two_lane_instantiation_matches_scalar(hm):
+    """svd_orth_t<F2> / svd_orth_pullback_t<F2> (what the kernels run, two matrices per thread) vs the scalar code."""
+    torch.manual_seed(4)
+    n = 1 << 14
+    x, g = torch.randn(n, 9), torch.randn(n, 9)
+    x[5] = 0                                                   # degenerate lanes take the scalar fix-up path
+    x[n // 2 + 7] = torch.tensor([3.0, 0, 0, 0, 0, 0, 0, 0, 0])
+    r1, d1 = hostmath.call(hm, "hm_svd_orth", x.numpy(), (n, 9), (n,))
+    r2, d2 = hostmath.call(hm, "hm_svd_orth_x2", x.numpy(), (n, 9), (n,))
+    assert np.array_equal(d1, d2)
+    assert np.abs(r1 - r2).max() <= 2e-6
+    ref = O.symmetric_orthogonalization(x.double()).numpy().reshape(n, 9)
+    cond = O.svd_orth_conditioning(x).numpy()
+    ok = np.isfinite(cond) & (cond > 0)
+    assert (np.abs(r2 - ref).max(1) * cond)[ok].max() <= 1e-6
+    b1 = hostmath.call(hm, "hm_svd_orth_bwd", x.numpy(), r1, g.numpy(), (n, 9))
+    b2 = hostmath.call(hm, "hm_svd_orth_bwd_x2", x.numpy(), r1, g.numpy(), (n, 9))
+    assert np.isfinite(b2).all()
+    scale = np.abs(b1).max(1)
+    assert (np.abs(b1 - b2).max(1) / np.maximum(scale, 0.1 * np.median(scale))).max() <= 1e-5
