@@ -83,15 +83,20 @@ PE_DEV void hestenes_t(T& p0, T& p1, T& p2, T& q0, T& q1, T& q2) {
 
 // Same algorithm as svd_orth_fast (pe_math.cuh), lane-generic.  Degenerate lanes (rank <= 1, zero, NaN) are
 // detected and redone with the scalar routine, which owns the special cases.
-template <class T>
-PE_DEV void svd_orth_t(const T* m, T* r, T& dsign) {
-    const T z = m[0];
-    const T sc = t_prescale(m);
+//
+// `fetch(T* dst)` delivers the nine entries of M.  It is called twice (three times for a degenerate lane): once for
+// the Jacobi iteration and once more, afterwards, for the recovery of V - so M does not sit in registers while the
+// rotations run (the kernels re-read it from shared memory; see PairSrc in pe_stream.cuh).
+template <class T, class Fetch>
+PE_DEV void svd_orth_f(const Fetch& fetch, T* r, T& dsign) {
     T a[9];
-#pragma unroll
-    for (int i = 0; i < 9; ++i) a[i] = t_mul(m[i], sc);
+    fetch(a);
+    const T z = a[0];
+    const T sc = t_prescale(a);
     // column j = (c[j], c[3+j], c[6+j])
-    T c00 = a[0], c01 = a[1], c02 = a[2], c10 = a[3], c11 = a[4], c12 = a[5], c20 = a[6], c21 = a[7], c22 = a[8];
+    T c00 = t_mul(a[0], sc), c01 = t_mul(a[1], sc), c02 = t_mul(a[2], sc), c10 = t_mul(a[3], sc),
+      c11 = t_mul(a[4], sc), c12 = t_mul(a[5], sc), c20 = t_mul(a[6], sc), c21 = t_mul(a[7], sc),
+      c22 = t_mul(a[8], sc);
     hestenes_t(c00, c10, c20, c01, c11, c21);
     hestenes_t(c00, c10, c20, c02, c12, c22);
     hestenes_t(c01, c11, c21, c02, c12, c22);
@@ -113,6 +118,9 @@ PE_DEV void svd_orth_t(const T* m, T* r, T& dsign) {
     T dd = t_fma(c02, u02, t_fma(c12, u12, t_mul(c22, u22)));
     dsign = t_sel(t_ltz(dd), t_set(z, -1.f), t_set(z, 1.f));
     // right vectors from the left ones: w_j = (sc M)^T u_j, Gram-Schmidt, cross product
+    fetch(a);
+#pragma unroll
+    for (int i = 0; i < 9; ++i) a[i] = t_mul(a[i], sc);
     T w00 = t_fma(a[6], u20, t_fma(a[3], u10, t_mul(a[0], u00)));
     T w10 = t_fma(a[7], u20, t_fma(a[4], u10, t_mul(a[1], u00)));
     T w20 = t_fma(a[8], u20, t_fma(a[5], u10, t_mul(a[2], u00)));
@@ -145,14 +153,23 @@ PE_DEV void svd_orth_t(const T* m, T* r, T& dsign) {
         float A0 = lane_get(al0, k), A1 = lane_get(al1, k), N0 = lane_get(n0, k), N1 = lane_get(n1, k);
         if (__builtin_expect(!(A1 > 1e-24f * A0) || !(A0 > 0.f) || !(N0 > 0.f) || !(N1 > 1e-30f), 0)) {
             float ms[9], rs[9], ds;
+            fetch(a);
 #pragma unroll
-            for (int i = 0; i < 9; ++i) ms[i] = lane_get(m[i], k);
+            for (int i = 0; i < 9; ++i) ms[i] = lane_get(a[i], k);
             svd_orth_fast(ms, rs, ds);
 #pragma unroll
             for (int i = 0; i < 9; ++i) lane_put(r[i], k, rs[i]);
             lane_put(dsign, k, ds);
         }
     }
+}
+
+template <class T>
+PE_DEV void svd_orth_t(const T* m, T* r, T& dsign) {
+    svd_orth_f<T>([m](T* dst) {
+#pragma unroll
+        for (int i = 0; i < 9; ++i) dst[i] = m[i];
+    }, r, dsign);
 }
 
 // Pullback of R = svd_orth(M), lane-generic (formulas and guards: svd_orth_pullback in pe_math.cuh).

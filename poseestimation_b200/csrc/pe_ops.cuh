@@ -19,7 +19,9 @@ struct NoExtra {};
     static constexpr int WI0 = (I0), WI1 = (I1), WI2 = (I2), WO0 = (O0), WO1 = (O1), NRED = (NR); \
     static constexpr bool FLAG = (FL);                                                       \
     static constexpr int RPT = (R);                                                          \
-    static constexpr int STAGES = stages_for((R) * (WI0 + WI1 + WI2), (R) * (WO0 + WO1), (R) * 54 * 1024); \
+    static constexpr bool kInPlace = (R) == 2 && WO0 == WI0 && WO1 == 0;                     \
+    static constexpr int STAGES = stages_for((R) * (WI0 + WI1 + WI2), kInPlace ? 0 : (R) * (WO0 + WO1), \
+                                             (R) == 2 ? 75 * 1024 : 54 * 1024);              \
     static constexpr int MINB = (MB);                                                        \
     static const char* name() { return NAME; }
 // one record per thread
@@ -28,21 +30,35 @@ struct NoExtra {};
 #define PE_OP_COMMON2(NAME, I0, I1, I2, O0, O1, NR, FL, MB) PE_OP_COMMON_R(NAME, I0, I1, I2, O0, O1, NR, FL, MB, 2)
 
 // ---- a1 symmetric_orthogonalization (rotation_representation.py:192-206) ------------------------------------
-// Every SVD op has a lane-generic body: `run` (T = float) serves the direct kernel, `run2` (T = F2) the TMA kernel.
+// Every SVD op has a lane-generic body over lazy sources: `run` (T = float, registers) serves the direct kernel,
+// `run2` (T = F2, shared-memory sources read on demand) the TMA kernel.
+template <int W>
+struct RegSrc {  // scalar twin of PairSrc: the record is already in registers
+    const float* v;
+    __device__ __forceinline__ void load(float* dst) const {
+#pragma unroll
+        for (int i = 0; i < W; ++i) dst[i] = v[i];
+    }
+};
+template <class T, class Src>
+__device__ __forceinline__ void svd_from(const Src& src, T* r, T& ds) {
+    svd_orth_f<T>([&src](T* dst) { src.load(dst); }, r, ds);
+}
+
 template <bool DET>
 struct SvdFwd {
-    PE_OP_COMMON2("svd_orth_fwd", 9, 0, 0, 9, DET ? 1 : 0, 0, false, 2)
+    PE_OP_COMMON2("svd_orth_fwd", 9, 0, 0, 9, DET ? 1 : 0, 0, false, 3)
     using Extra = NoExtra;
-    template <class T>
-    __device__ static __forceinline__ void body(const T* m, T* r, T* d) {
+    template <class T, class S0>
+    __device__ static __forceinline__ void body(const S0& m, T* r, T* d) {
         T ds;
-        svd_orth_t(m, r, ds);
+        svd_from<T>(m, r, ds);
         if constexpr (DET) d[0] = ds;
     }
     __device__ static __forceinline__ void run(const float* m, const float*, const float*, float* r, float* d,
-                                               double*, int&, const Extra&) { body(m, r, d); }
-    __device__ static __forceinline__ void run2(const F2* m, const F2*, const F2*, F2* r, F2* d, double*, int&,
-                                                bool, bool, const Extra&) { body(m, r, d); }
+                                               double*, int&, const Extra&) { body<float>(RegSrc<9>{m}, r, d); }
+    __device__ static __forceinline__ void run2(const PairSrc<9>& m, const PairSrc<0>&, const PairSrc<0>&, F2* r, F2* d,
+                                                double*, int&, bool, bool, const Extra&) { body<F2>(m, r, d); }
 };
 // pullback with the saved forward output: in = (m, r, g)
 struct SvdBwdSaved {
@@ -50,23 +66,30 @@ struct SvdBwdSaved {
     using Extra = NoExtra;
     __device__ static __forceinline__ void run(const float* m, const float* r, const float* g, float* dm, float*,
                                                double*, int&, const Extra&) { svd_orth_pullback_t(m, r, g, dm); }
-    __device__ static __forceinline__ void run2(const F2* m, const F2* r, const F2* g, F2* dm, F2*, double*, int&,
-                                                bool, bool, const Extra&) { svd_orth_pullback_t(m, r, g, dm); }
+    __device__ static __forceinline__ void run2(const PairSrc<9>& ms, const PairSrc<9>& rs, const PairSrc<9>& gs, F2* dm,
+                                                F2*, double*, int&, bool, bool, const Extra&) {
+        F2 m[9], r[9], g[9];
+        ms.load(m); rs.load(r); gs.load(g);
+        svd_orth_pullback_t(m, r, g, dm);
+    }
 };
 // pullback that recomputes r from m: in = (m, g)
 struct SvdBwdRecompute {
-    PE_OP_COMMON2("svd_orth_bwd_recompute", 9, 9, 0, 9, 0, 0, false, 2)
+    PE_OP_COMMON2("svd_orth_bwd_recompute", 9, 9, 0, 9, 0, 0, false, 3)
     using Extra = NoExtra;
-    template <class T>
-    __device__ static __forceinline__ void body(const T* m, const T* g, T* dm) {
-        T r[9], ds;
-        svd_orth_t(m, r, ds);
+    template <class T, class S0, class S1>
+    __device__ static __forceinline__ void body(const S0& ms, const S1& gs, T* dm) {
+        T r[9], m[9], g[9], ds;
+        svd_from<T>(ms, r, ds);
+        ms.load(m); gs.load(g);
         svd_orth_pullback_t(m, r, g, dm);
     }
     __device__ static __forceinline__ void run(const float* m, const float* g, const float*, float* dm, float*,
-                                               double*, int&, const Extra&) { body(m, g, dm); }
-    __device__ static __forceinline__ void run2(const F2* m, const F2* g, const F2*, F2* dm, F2*, double*, int&,
-                                                bool, bool, const Extra&) { body(m, g, dm); }
+                                               double*, int&, const Extra&) {
+        body<float>(RegSrc<9>{m}, RegSrc<9>{g}, dm);
+    }
+    __device__ static __forceinline__ void run2(const PairSrc<9>& m, const PairSrc<9>& g, const PairSrc<0>&, F2* dm, F2*,
+                                                double*, int&, bool, bool, const Extra&) { body<F2>(m, g, dm); }
 };
 
 // ---- elementwise maps: forward (x -> 9 words) and pullback ((x, g) -> dx) ---------------------------------------
@@ -186,12 +209,13 @@ struct AngleFwd {
 // ---- fused: loss_frobenius(symmetric_orthogonalization(x), R_true) ------------------------------------------------
 template <bool WRITE_R>
 struct SvdFrobFwd {
-    PE_OP_COMMON2("svd_orth_frobenius_fwd", 9, 9, 0, WRITE_R ? 9 : 0, 0, 1, false, 2)
+    PE_OP_COMMON2("svd_orth_frobenius_fwd", 9, 9, 0, WRITE_R ? 9 : 0, 0, 1, false, 3)
     using Extra = NoExtra;
-    template <class T>
-    __device__ static __forceinline__ T body(const T* m, const T* rt, T* r) {
-        T rr[9], d[9], ds;
-        svd_orth_t(m, rr, ds);
+    template <class T, class S0, class S1>
+    __device__ static __forceinline__ T body(const S0& ms, const S1& rts, T* r) {
+        T rr[9], rt[9], d[9], ds;
+        svd_from<T>(ms, rr, ds);
+        rts.load(rt);
         T s = diff9_sq(rr, rt, d);
         if constexpr (WRITE_R) {
 #pragma unroll
@@ -201,22 +225,23 @@ struct SvdFrobFwd {
     }
     __device__ static __forceinline__ void run(const float* m, const float* rt, const float*, float* r, float*,
                                                double* red, int&, const Extra&) {
-        red[0] += (double)body(m, rt, r);
+        red[0] += (double)body<float>(RegSrc<9>{m}, RegSrc<9>{rt}, r);
     }
-    __device__ static __forceinline__ void run2(const F2* m, const F2* rt, const F2*, F2* r, F2*, double* red, int&,
-                                                bool v0, bool v1, const Extra&) {
-        F2 f = body(m, rt, r);
+    __device__ static __forceinline__ void run2(const PairSrc<9>& m, const PairSrc<9>& rt, const PairSrc<0>&, F2* r, F2*,
+                                                double* red, int&, bool v0, bool v1, const Extra&) {
+        F2 f = body<F2>(m, rt, r);
         red[0] += (double)((v0 ? f.x : 0.f) + (v1 ? f.y : 0.f));
     }
 };
 struct SvdFrobBwd {
-    PE_OP_COMMON2("svd_orth_frobenius_bwd", 9, 9, 0, 9, 0, 0, false, 2)
+    PE_OP_COMMON2("svd_orth_frobenius_bwd", 9, 9, 0, 9, 0, 0, false, 3)
     using Extra = GradScale;
-    template <class T>
-    __device__ static __forceinline__ void body(const T* m, const T* rt, T* dm, float gs) {
-        T r[9], g[9], ds;
-        svd_orth_t(m, r, ds);
-        T s = diff9_sq(r, rt, g);
+    template <class T, class S0, class S1>
+    __device__ static __forceinline__ void body(const S0& ms, const S1& rts, T* dm, float gs) {
+        T r[9], g[9], m[9], ds;
+        svd_from<T>(ms, r, ds);
+        rts.load(m);  // R_true, reusing the registers that will hold M next
+        T s = diff9_sq(r, m, g);
         T k = s;
 #pragma unroll
         for (int l = 0; l < LaneCount<T>::value; ++l) {
@@ -225,15 +250,16 @@ struct SvdFrobBwd {
         }
 #pragma unroll
         for (int i = 0; i < 9; ++i) g[i] = t_mul(g[i], k);
+        ms.load(m);
         svd_orth_pullback_t(m, r, g, dm);
     }
     __device__ static __forceinline__ void run(const float* m, const float* rt, const float*, float* dm, float*,
                                                double*, int&, const Extra& ex) {
-        body(m, rt, dm, __ldg(ex.gout) * ex.mul);
+        body<float>(RegSrc<9>{m}, RegSrc<9>{rt}, dm, __ldg(ex.gout) * ex.mul);
     }
-    __device__ static __forceinline__ void run2(const F2* m, const F2* rt, const F2*, F2* dm, F2*, double*, int&,
-                                                bool, bool, const Extra& ex) {
-        body(m, rt, dm, __ldg(ex.gout) * ex.mul);
+    __device__ static __forceinline__ void run2(const PairSrc<9>& m, const PairSrc<9>& rt, const PairSrc<0>&, F2* dm, F2*,
+                                                double*, int&, bool, bool, const Extra& ex) {
+        body<F2>(m, rt, dm, __ldg(ex.gout) * ex.mul);
     }
 };
 

@@ -43,7 +43,9 @@ struct Geometry {
     __host__ __device__ static constexpr int wo(int k) { return k == 0 ? Op::WO0 : Op::WO1; }
     static constexpr int WITOT = Op::WI0 + Op::WI1 + Op::WI2;
     static constexpr int WOTOT = Op::WO0 + Op::WO1;
-    static constexpr int NOBUF = WOTOT > 0 ? 2 : 0;
+    // in-place output: the op's single output record has the width of in[0] and replaces it inside the stage
+    static constexpr bool IN_PLACE = Op::RPT == 2 && Op::WO0 == Op::WI0 && Op::WO1 == 0;
+    static constexpr int NOBUF = (WOTOT > 0 && !IN_PLACE) ? 2 : 0;
     static constexpr int TR = kTile * Op::RPT;  // records per tile (RPT records per thread)
     static constexpr int kBarBytes = 128;
     static constexpr int kStageBytes = TR * 4 * WITOT;
@@ -68,6 +70,15 @@ __device__ __forceinline__ void lds_pair(const float* s, int t, int stride, F2* 
     lds_record<W>(s, t + stride, b);
 #pragma unroll
     for (int i = 0; i < W; ++i) r[i] = F2{a[i], b[i]};
+}
+
+template <int W>
+__device__ __forceinline__ void sts_pair(float* s, int t, int stride, const F2* r) {
+    float a[W], b[W];
+#pragma unroll
+    for (int i = 0; i < W; ++i) { a[i] = r[i].x; b[i] = r[i].y; }
+    sts_record<W>(s, t, a);
+    sts_record<W>(s, t + stride, b);
 }
 
 template <class Op>
@@ -97,10 +108,21 @@ __device__ __forceinline__ void block_reduce_and_publish(double* red, int flag, 
 }
 
 // ---------------------------------------------------------------------------------------------------------------
+// Lazy source of a record pair (records t and t + stride of one input tile): the op decides WHEN the registers
+// are filled, so inputs that are only needed after the SVD (R_true, the second read of M) do not occupy registers
+// while the Jacobi rotations run.  This is what lets the two-matrices-per-thread kernels stay under 85 registers.
+template <int W>
+struct PairSrc {
+    const float* s;
+    int t, stride;
+    __device__ __forceinline__ void load(F2* dst) const { lds_pair<W>(s, t, stride, dst); }
+};
+
 template <class Op>
 __global__ void __launch_bounds__(kTile, Op::MINB) stream_tma_kernel(const Params<Op> p) {
     using G = Geometry<Op>;
     constexpr int T = kTile, TR = G::TR, S = Op::STAGES;
+    constexpr bool IP = G::IN_PLACE;  // the output record overwrites the thread's own in[0] record in the stage
     extern __shared__ __align__(128) unsigned char smem_raw[];
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw);
     float* s_in = reinterpret_cast<float*>(smem_raw + G::kBarBytes);
@@ -148,15 +170,26 @@ __global__ void __launch_bounds__(kTile, Op::MINB) stream_tma_kernel(const Param
     for (int k = 0; k < (Op::NRED > 0 ? Op::NRED : 1); ++k) red[k] = 0.0;
     int flag = 0;
 
-    long long it = 0;
-    for (long long tile = blockIdx.x; tile < ntiles; tile += gstep, ++it) {
-        const int s = (int)(it % S);
-        const uint32_t parity = (uint32_t)((it / S) & 1);
+    int s = 0;
+    uint32_t parity = 0;
+    int obuf = 0;
+    long long refill_tile = -1;  // IP mode: tile to load into the stage vacated by the previous iteration
+    int refill_stage = 0;
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gstep) {
         const long long base = tile * TR;
         const bool full = tile < nfull;
         const int cnt = full ? TR : (int)(n - base);
         float* si = s_in + s * TR * G::WITOT;
+        float* so = IP ? si : s_out + obuf * TR * G::WOTOT;
 
+        if constexpr (IP) {
+            // the stage used one iteration ago was stored from in place: once the TMA store has finished reading
+            // it, refill it (prefetch distance: S - 1 tiles)
+            if (tid == 0 && refill_tile >= 0) {
+                bulk_wait_read<0>();
+                if (refill_tile < nfull) issue(refill_stage, refill_tile);
+            }
+        }
         if (full) {
             mbar_wait(&bars[s], parity);
         } else {
@@ -173,7 +206,6 @@ __global__ void __launch_bounds__(kTile, Op::MINB) stream_tma_kernel(const Param
             __syncthreads();
         }
 
-        float* so = s_out + (G::NOBUF ? (int)(it & 1) : 0) * TR * G::WOTOT;
         const float* si1 = si + TR * Op::WI0;
         const float* si2 = si + TR * (Op::WI0 + Op::WI1);
         RegArr<Op::WO0 * Op::RPT> o0;
@@ -188,30 +220,29 @@ __global__ void __launch_bounds__(kTile, Op::MINB) stream_tma_kernel(const Param
             if (tid < cnt) Op::run(i0.v, i1.v, i2.v, o0.v, o1.v, red, flag, p.ex);
         } else {
             // two records per thread (tid and tid + T), one in each half of a packed fp32x2 register pair
-            PairArr<Op::WI0> i0;
-            PairArr<Op::WI1> i1;
-            PairArr<Op::WI2> i2;
             PairArr<Op::WO0> q0;
             PairArr<Op::WO1> q1;
-            if constexpr (Op::WI0 > 0) lds_pair<Op::WI0>(si, tid, T, i0.v);
-            if constexpr (Op::WI1 > 0) lds_pair<Op::WI1>(si1, tid, T, i1.v);
-            if constexpr (Op::WI2 > 0) lds_pair<Op::WI2>(si2, tid, T, i2.v);
-            Op::run2(i0.v, i1.v, i2.v, q0.v, q1.v, red, flag, tid < cnt, tid + T < cnt, p.ex);
+            Op::run2(PairSrc<Op::WI0>{si, tid, T}, PairSrc<Op::WI1>{si1, tid, T}, PairSrc<Op::WI2>{si2, tid, T}, q0.v,
+                     q1.v, red, flag, tid < cnt, tid + T < cnt, p.ex);
 #pragma unroll
             for (int w = 0; w < Op::WO0; ++w) { o0.v[w] = q0.v[w].x; o0.v[Op::WO0 + w] = q0.v[w].y; }
 #pragma unroll
             for (int w = 0; w < Op::WO1; ++w) { o1.v[w] = q1.v[w].x; o1.v[Op::WO1 + w] = q1.v[w].y; }
         }
 
-        if constexpr (G::NOBUF > 0) {
-            if (tid == 0) bulk_wait_read<1>();  // the store issued two tiles ago has finished reading `so`
+        if constexpr (!IP) {
+            if constexpr (G::NOBUF > 0) {
+                if (tid == 0) bulk_wait_read<1>();  // the store issued two tiles ago has finished reading `so`
+            }
+            __syncthreads();  // (A) every thread is done with stage s; `so` is free
+            if (tid == 0) {
+                long long next = tile + S * gstep;
+                if (next < nfull) issue(s, next);
+            }
         }
-        __syncthreads();  // (A) every thread is done with stage s; `so` is free
-        if (tid == 0) {
-            long long next = tile + S * gstep;
-            if (next < nfull) issue(s, next);
-        }
-        if constexpr (G::NOBUF > 0) {
+        if constexpr (G::WOTOT > 0) {
+            // IP: a thread only ever reads its OWN records of in[0], and it has finished reading them, so it may
+            // overwrite them without a barrier in between
 #pragma unroll
             for (int rr = 0; rr < Op::RPT; ++rr) {
                 if constexpr (Op::WO0 > 0) sts_record<Op::WO0>(so, tid + rr * T, o0.v + rr * Op::WO0);
@@ -237,9 +268,15 @@ __global__ void __launch_bounds__(kTile, Op::MINB) stream_tma_kernel(const Param
                     for (int w = tid; w < cnt * Op::WO1; w += T) dst[w] = so[TR * Op::WO0 + w];
                 }
             }
+            obuf ^= 1;
         }
+        if constexpr (IP) {
+            refill_tile = tile + S * gstep;
+            refill_stage = s;
+        }
+        if (++s == S) { s = 0; parity ^= 1; }
     }
-    if constexpr (G::NOBUF > 0) {
+    if constexpr (G::WOTOT > 0) {
         if (tid == 0) bulk_wait<0>();  // shared memory must outlive the stores that read it
     }
     block_reduce_and_publish<Op>(red, flag, p.sums, p.flag, s_red);
