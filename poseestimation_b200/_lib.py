@@ -1,7 +1,7 @@
 """ctypes binding of ``libpe_rotation.so`` (C ABI: ``include/pe_rotation.h``).
 
 There is no fallback: if the shared library is missing, or an entry point is missing from it, importing this module
-raises.  Build it with ``python -m poseestimation_b200.build`` (or ``__graft_entry__.build()``).
+raises.  Build it with ``python poseestimation_b200/build.py`` (or ``__graft_entry__.build()``).
 """
 from __future__ import annotations
 
@@ -45,7 +45,7 @@ SIGNATURES = {
 def _load():
     if not os.path.exists(LIB_PATH):
         raise ImportError(
-            f"{LIB_PATH} not found: the CUDA extension has not been built (python -m poseestimation_b200.build). "
+            f"{LIB_PATH} not found: the CUDA extension has not been built (python poseestimation_b200/build.py). "
             "There is no CPU or PyTorch fallback for the rotation-mapping path.")
     lib = ctypes.CDLL(LIB_PATH)
     for name, argtypes in SIGNATURES.items():

@@ -1,4 +1,4 @@
-"""Build ``libpe_rotation.so`` in-tree for sm_100a:  ``python -m poseestimation_b200.build [-v]``.
+"""Build ``libpe_rotation.so`` in-tree for sm_100a:  ``python poseestimation_b200/build.py [-v]``.
 
 nvcc cross-compiles without a GPU.  The library is git-ignored (source-only history) but travels to the GPU box with
 the working-tree snapshot.
