@@ -104,6 +104,14 @@ int pe_svd_orth_frobenius_fwd(const float* m, int64_t m_stride, const float* r_t
 int pe_svd_orth_frobenius_bwd(const float* m, int64_t m_stride, const float* r_true, const float* gout,
                               float inv_n, float* dm, int64_t n, void* stream);
 
+/* single pass of the same step: ONE decomposition per matrix yields the loss and the gradient (108 B/matrix).
+ * *sum = sum_b |r_true_b - r_b|_F and dm = inv_n * pullback((r - r_true)/|r - r_true|_F), i.e. the gradient of the
+ * batch-mean loss for an upstream gradient of 1.  The autograd backward is then pe_scale_by_scalar(dm, gout). */
+int pe_svd_orth_frobenius_step(const float* m, int64_t m_stride, const float* r_true, float inv_n, float* dm,
+                               double* sum, int64_t n, void* stream);
+/* y[i] = x[i] * (*g) for nwords floats; g is a DEVICE scalar (no host sync); x, y 16-byte aligned, y may alias x. */
+int pe_scale_by_scalar(const float* x, const float* g, float* y, int64_t nwords, void* stream);
+
 /* ---- a9  Kabsch alignment - no reference function (site: point_cloud/main.py:171-181) --------------------------
  * p, q: (b, npts, 3) dense.  r[b][9] = the rotation minimising sum_k |R p_k + t - q_k|^2, i.e.
  * pe_svd_orth of sum_k (q_k - qbar)(p_k - pbar)^T;  t (nullable, b x 3) = qbar - R pbar. */

@@ -38,6 +38,8 @@ SIGNATURES = {
     "pe_angle_error_fwd": [_f, _f, _f, _f, _f, _i64, _f],
     "pe_svd_orth_frobenius_fwd": [_f, _i64, _f, _f, _f, _i64, _f],
     "pe_svd_orth_frobenius_bwd": [_f, _i64, _f, _f, _flt, _f, _i64, _f],
+    "pe_svd_orth_frobenius_step": [_f, _i64, _f, _flt, _f, _f, _i64, _f],
+    "pe_scale_by_scalar": [_f, _f, _f, _i64, _f],
     "pe_kabsch_fwd": [_f, _f, _i64, _i64, _f, _f, _f],
 }
 

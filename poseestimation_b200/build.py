@@ -13,7 +13,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 SOURCES = ["pe_api.cu", "pe_kabsch.cu"]
-HEADERS = ["pe_common.h", "pe_math.cuh", "pe_stage.cuh", "pe_stream.cuh", "pe_ops.cuh",
+HEADERS = ["pe_common.h", "pe_math.cuh", "pe_stage.cuh", "pe_stream.cuh", "pe_lanes.cuh", "pe_ops.cuh",
            os.path.join("..", "..", "include", "pe_rotation.h")]
 OUT = os.path.join(HERE, "libpe_rotation.so")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]

@@ -37,6 +37,22 @@ int run(const float* i0, long long stride0, const float* i1, const float* i2, fl
     return stream_launch<Op>(make_params<Op>(i0, stride0, i1, i2, o0, o1, n, sums, flag, ex), st);
 }
 
+// y = x * (*g): the backward of a single-pass step (the gradient for a unit upstream gradient times the upstream
+// scalar, read on the device so that no host synchronisation is needed).  Pure stream: 8 B per word.
+__global__ void __launch_bounds__(256) scale_by_scalar_kernel(const float4* __restrict__ x, const float* __restrict__ g,
+                                                              float4* __restrict__ y, long long n4,
+                                                              const float* __restrict__ xt, float* __restrict__ yt,
+                                                              int tail) {
+    const float k = __ldg(g);
+    const long long step = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += step) {
+        float4 v = __ldcs(x + i);
+        v.x *= k; v.y *= k; v.z *= k; v.w *= k;
+        __stcs(y + i, v);
+    }
+    if (blockIdx.x == 0 && (int)threadIdx.x < tail) yt[threadIdx.x] = xt[threadIdx.x] * k;
+}
+
 }  // namespace
 
 extern "C" {
@@ -121,6 +137,32 @@ int pe_svd_orth_frobenius_bwd(const float* m, int64_t m_stride, const float* r_t
                               float inv_n, float* dm, int64_t n, void* stream) {
     if (!gout) return fail(PE_ERR_BAD_ARG, "null upstream-gradient pointer");
     return run<SvdFrobBwd>(m, m_stride, r_true, nullptr, dm, nullptr, n, nullptr, nullptr, {gout, inv_n}, stream);
+}
+
+int pe_svd_orth_frobenius_step(const float* m, int64_t m_stride, const float* r_true, float inv_n, float* dm,
+                               double* sum, int64_t n, void* stream) {
+    return run<SvdFrobStep>(m, m_stride, r_true, nullptr, dm, nullptr, n, sum, nullptr, {inv_n}, stream);
+}
+int pe_scale_by_scalar(const float* x, const float* g, float* y, int64_t nwords, void* stream) {
+    if (nwords < 0) return fail(PE_ERR_BAD_ARG, "negative word count");
+    if (nwords == 0) return 0;
+    if (!x || !g || !y) return fail(PE_ERR_BAD_ARG, "null pointer");
+    if (!aligned16(x) || !aligned16(y)) return fail(PE_ERR_BAD_ARG, "pe_scale_by_scalar needs 16-byte aligned arrays");
+    int dev = 0, sms = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (e != cudaSuccess) return fail_cuda(e, "cudaDeviceGetAttribute");
+    const long long n4 = nwords / 4;
+    long long grid = (n4 + 255) / 256;
+    if (grid > (long long)sms * 8) grid = (long long)sms * 8;
+    if (grid < 1) grid = 1;
+    scale_by_scalar_kernel<<<(unsigned)grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        reinterpret_cast<const float4*>(x), g, reinterpret_cast<float4*>(y), n4, x + 4 * n4, y + 4 * n4,
+        (int)(nwords - 4 * n4));
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return fail_cuda(e, "scale_by_scalar");
+    count_launch();
+    return 0;
 }
 
 }  // extern "C"

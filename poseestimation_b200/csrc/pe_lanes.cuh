@@ -22,6 +22,7 @@ PE_DEV float t_abs(float a) { return fabsf(a); }
 PE_DEV float t_max(float a, float b) { return fmaxf(a, b); }
 PE_DEV float t_rsq(float a) { return rsqrt_fast(a); }
 PE_DEV float t_sqrt(float a) { return sqrtf(a); }
+PE_DEV float t_sqrt_fast(float a) { return sqrt_fast(a); }
 PE_DEV bool t_ltz(float a) { return a < 0.f; }
 PE_DEV float t_sel(bool m, float a, float b) { return m ? a : b; }
 PE_DEV float t_prescale(const float* m) { return pow2_prescale(m); }
@@ -44,6 +45,7 @@ PE_DEV F2 t_abs(F2 a) { return F2{fabsf(a.x), fabsf(a.y)}; }
 PE_DEV F2 t_max(F2 a, F2 b) { return F2{fmaxf(a.x, b.x), fmaxf(a.y, b.y)}; }
 PE_DEV F2 t_rsq(F2 a) { return F2{rsqrt_fast(a.x), rsqrt_fast(a.y)}; }
 PE_DEV F2 t_sqrt(F2 a) { return F2{sqrtf(a.x), sqrtf(a.y)}; }
+PE_DEV F2 t_sqrt_fast(F2 a) { return F2{sqrt_fast(a.x), sqrt_fast(a.y)}; }
 PE_DEV B2 t_ltz(F2 a) { return B2{a.x < 0.f, a.y < 0.f}; }
 PE_DEV F2 t_sel(B2 m, F2 a, F2 b) { return F2{m.x ? a.x : b.x, m.y ? a.y : b.y}; }
 PE_DEV F2 t_prescale(const F2* m) {
@@ -68,11 +70,13 @@ PE_DEV void hestenes_t(T& p0, T& p1, T& p2, T& q0, T& q1, T& q2) {
     T ga = t_fma(p2, q2, t_fma(p1, q1, t_mul(p0, q0)));
     T dh = t_mul(t_set(z, 0.5f), t_sub(al, be));
     T ad = t_max(t_abs(dh), t_set(z, 1e-18f));
-    T r = t_rsq(t_fma(ad, ad, t_mul(ga, ga)));
-    T c2 = t_mul(ad, r), s2 = t_mul(ga, r);
-    T w = t_fma(t_set(z, 2.0f), c2, t_set(z, 2.0f));
-    T h = t_rsq(w);
-    T c = t_mul(t_mul(t_set(z, 0.5f), w), h), s = t_mul(s2, h);
+    // tan(theta) = ga / (rho + |dh|) with rho = sqrt(dh^2 + ga^2)  (= sin 2theta / (1 + cos 2theta)): no cancellation,
+    // two MUFU ops, and (c, s) = (u, ga) / sqrt(u^2 + ga^2) share one reciprocal square root
+    T g2 = t_mul(ga, ga);
+    T rho = t_sqrt_fast(t_fma(ad, ad, g2));
+    T u = t_add(rho, ad);
+    T k = t_rsq(t_fma(u, u, g2));
+    T c = t_mul(u, k), s = t_mul(ga, k);
     auto neg = t_ltz(dh);
     T cp = t_sel(neg, s, c), sp = t_sel(neg, c, s), ns = t_neg(sp);
     T t;

@@ -25,6 +25,15 @@ PE_DEV float rsqrt_fast(float x) {  // MUFU.RSQ, ~2^-22 relative error, flush-to
     return 1.0f / sqrtf(x);
 #endif
 }
+PE_DEV float sqrt_fast(float x) {  // MUFU.SQRT, ~2^-22 relative error, flush-to-zero
+#ifdef __CUDA_ARCH__
+    float y;
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+#else
+    return sqrtf(x);
+#endif
+}
 PE_DEV int f2i(float x) {
 #ifdef __CUDA_ARCH__
     return __float_as_int(x);
@@ -202,11 +211,12 @@ PE_DEV void hestenes_a(F2& p01, float& p2, F2& q01, float& q2) {
     float ga = fmaf(p2, q2, fmaf(p01.y, q01.y, p01.x * q01.x));
     float dh = 0.5f * (al - be);
     float ad = fmaxf(fabsf(dh), 1e-18f);
-    float r = rsqrt_fast(fmaf(ad, ad, ga * ga));
-    float c2 = ad * r, s2 = ga * r;
-    float w = fmaf(2.0f, c2, 2.0f);
-    float h = rsqrt_fast(w);
-    float c = 0.5f * w * h, s = s2 * h;
+    // tan(theta) = ga / (rho + |dh|), rho = sqrt(dh^2 + ga^2); (c, s) = (u, ga) / sqrt(u^2 + ga^2)  [pe_lanes.cuh]
+    float g2 = ga * ga;
+    float rho = sqrt_fast(fmaf(ad, ad, g2));
+    float u = rho + ad;
+    float k = rsqrt_fast(fmaf(u, u, g2));
+    float c = u * k, s = ga * k;
     bool neg = dh < 0.0f;
     float cp = neg ? s : c, sp = neg ? c : s;
     F2 C{cp, cp}, S{sp, sp}, N{-sp, -sp};

@@ -21,7 +21,7 @@ struct NoExtra {};
     static constexpr int RPT = (R);                                                          \
     static constexpr bool kInPlace = (R) == 2 && WO0 == WI0 && WO1 == 0;                     \
     static constexpr int STAGES = stages_for((R) * (WI0 + WI1 + WI2), kInPlace ? 0 : (R) * (WO0 + WO1), \
-                                             (R) == 2 ? 75 * 1024 : 54 * 1024);              \
+                                             (R) == 2 && (MB) < 4 ? 75 * 1024 : 54 * 1024);              \
     static constexpr int MINB = (MB);                                                        \
     static const char* name() { return NAME; }
 // one record per thread
@@ -260,6 +260,45 @@ struct SvdFrobBwd {
     __device__ static __forceinline__ void run2(const PairSrc<9>& m, const PairSrc<9>& rt, const PairSrc<0>&, F2* dm, F2*,
                                                 double*, int&, bool, bool, const Extra& ex) {
         body<F2>(m, rt, dm, __ldg(ex.gout) * ex.mul);
+    }
+};
+
+// single pass of the training step: the loss AND the gradient for a unit upstream gradient from ONE decomposition
+// (reads M, R_true; writes dM = mul * pullback((R - R_true)/|R - R_true|_F); adds |R - R_true|_F to the sum).  108 B.
+struct StepScale {
+    float mul;  // 1/n of the batch mean
+};
+struct SvdFrobStep {
+    PE_OP_COMMON2("svd_orth_frobenius_step", 9, 9, 0, 9, 0, 1, false, 3)
+    using Extra = StepScale;
+    template <class T, class S0, class S1>
+    __device__ static __forceinline__ T body(const S0& ms, const S1& rts, T* dm, float gs) {
+        T r[9], g[9], m[9], ds;
+        svd_from<T>(ms, r, ds);
+        rts.load(m);
+        T s = diff9_sq(r, m, g);
+        T k = s, f = s;
+#pragma unroll
+        for (int l = 0; l < LaneCount<T>::value; ++l) {
+            float sl = lane_get(s, l);
+            float inv = sl > 0.f ? rsqrt_nr(sl) : 0.f;
+            lane_put(k, l, gs * inv);
+            lane_put(f, l, sl * inv);  // |R - R_true|_F
+        }
+#pragma unroll
+        for (int i = 0; i < 9; ++i) g[i] = t_mul(g[i], k);
+        ms.load(m);
+        svd_orth_pullback_t(m, r, g, dm);
+        return f;
+    }
+    __device__ static __forceinline__ void run(const float* m, const float* rt, const float*, float* dm, float*,
+                                               double* red, int&, const Extra& ex) {
+        red[0] += (double)body<float>(RegSrc<9>{m}, RegSrc<9>{rt}, dm, ex.mul);
+    }
+    __device__ static __forceinline__ void run2(const PairSrc<9>& m, const PairSrc<9>& rt, const PairSrc<0>&, F2* dm, F2*,
+                                                double* red, int&, bool v0, bool v1, const Extra& ex) {
+        F2 f = body<F2>(m, rt, dm, ex.mul);
+        red[0] += (double)((v0 ? f.x : 0.f) + (v1 ? f.y : 0.f));
     }
 };
 

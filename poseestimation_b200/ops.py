@@ -454,6 +454,66 @@ def _sof_backward(ctx, g):
 svd_orth_frobenius.register_autograd(_sof_backward, setup_context=_sof_setup)
 
 
+# single pass: one decomposition per matrix gives the loss and the gradient for a unit upstream gradient (108 B/matrix);
+# the autograd backward is one scaling pass with the upstream scalar read on the device.
+@torch.library.custom_op(f"{NS}::svd_orth_frobenius_step", mutates_args=(), device_types="cuda")
+def svd_orth_frobenius_step(x: Tensor, r_true: Tensor) -> tuple[Tensor, Tensor]:
+    """-> (0-d float32 loss = mean_b |r_true_b - svd_orth(x_b)|_F,  d loss / d x as (n, 9))."""
+    x, stride = _rec(x, 9)
+    n = x.shape[0]
+    rt = _mat(r_true)
+    if rt.shape[0] != n:
+        raise ValueError("batch mismatch")
+    s = torch.zeros((1,), dtype=torch.float64, device=x.device)
+    dx = torch.empty((n, 9), dtype=torch.float32, device=x.device)
+    if n:
+        with torch.cuda.device(x.device):
+            check(lib.pe_svd_orth_frobenius_step(x.data_ptr(), stride, rt.data_ptr(), 1.0 / n, dx.data_ptr(),
+                                                 s.data_ptr(), n, _stream()), "pe_svd_orth_frobenius_step")
+        loss = (s / n).to(torch.float32).reshape(())
+    else:
+        loss = s.to(torch.float32).reshape(()) * float("nan")
+    return loss, dx
+
+
+@svd_orth_frobenius_step.register_fake
+def _(x, r_true):
+    return x.new_empty(()), x.new_empty((x.shape[0], 9))
+
+
+@torch.library.custom_op(f"{NS}::scale_by_scalar", mutates_args=(), device_types="cuda")
+def scale_by_scalar(x: Tensor, g: Tensor) -> Tensor:
+    """x * g for a one-element device tensor g, without reading g on the host."""
+    if x.dtype != torch.float32:
+        raise TypeError("pe_b200 ops compute in float32")
+    x = x.contiguous()
+    g = g.to(torch.float32).reshape(1).contiguous()
+    y = torch.empty_like(x)
+    if x.numel():
+        with torch.cuda.device(x.device):
+            check(lib.pe_scale_by_scalar(x.data_ptr(), g.data_ptr(), y.data_ptr(), x.numel(), _stream()),
+                  "pe_scale_by_scalar")
+    return y
+
+
+@scale_by_scalar.register_fake
+def _(x, g):
+    return torch.empty_like(x)
+
+
+def _step_setup(ctx, inputs, output):
+    ctx.save_for_backward(output[1])
+    ctx.mark_non_differentiable(output[1])
+
+
+def _step_backward(ctx, g_loss, _g_dx):
+    (dx,) = ctx.saved_tensors
+    return scale_by_scalar(dx, g_loss), None
+
+
+svd_orth_frobenius_step.register_autograd(_step_backward, setup_context=_step_setup)
+
+
 # ---------------------------------------------------------------------------------------------------------------------
 # a9  Kabsch (no reference function; site /root/reference/point_cloud/main.py:171-181)
 @torch.library.custom_op(f"{NS}::kabsch", mutates_args=(), device_types="cuda")

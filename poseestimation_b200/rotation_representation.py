@@ -31,7 +31,7 @@ __all__ = [
     "compute_rotation_matrix_from_quaternion", "symmetric_orthogonalization",
     "compute_geodesic_distance_from_two_matrices", "angle_error", "so3_exp_map", "hat", "vec_3d_to_SO3",
     "transform_output", "get_scene_parameters", "parametrization",
-    "loss_frobenius", "geodesic", "kabsch", "svd_frobenius_loss", "mean_angle_error", "install",
+    "loss_frobenius", "geodesic", "kabsch", "svd_frobenius_loss", "svd_frobenius_loss_and_grad", "mean_angle_error", "install",
 ]
 
 
@@ -166,10 +166,24 @@ def loss_frobenius(R_pred, R_true):
     return _ops.frobenius_mean(R_pred, R_true)
 
 
-def svd_frobenius_loss(x, R_true):
-    """``loss_frobenius(symmetric_orthogonalization(x), R_true)`` as one kernel per direction (108 B/matrix)."""
+def svd_frobenius_loss(x, R_true, single_pass=True):
+    """``loss_frobenius(symmetric_orthogonalization(x), R_true)`` fused (Comparison/main.py:59-62 and the 7 copies).
+
+    When ``x`` needs a gradient the default is the single-pass step: ONE decomposition per matrix yields the loss and
+    d loss/d x (108 B/matrix), and ``backward`` only scales that gradient by the upstream scalar (72 B/matrix).
+    ``single_pass=False`` keeps nothing between the passes (72 B forward, 108 B backward that recomputes the SVD)."""
     rec = x if (x.dim() == 2 and x.shape[1] == 9) else x.reshape(-1, 9)
+    if single_pass and torch.is_grad_enabled() and rec.requires_grad:
+        return _ops.svd_orth_frobenius_step(rec, R_true)[0]
     return _ops.svd_orth_frobenius(rec, R_true)
+
+
+def svd_frobenius_loss_and_grad(x, R_true):
+    """(loss, d loss / d x) of the fused step in one kernel, without autograd: for training loops that call
+    ``x.backward(grad)`` themselves.  ``grad`` has the shape of ``x``."""
+    rec = x if (x.dim() == 2 and x.shape[1] == 9) else x.reshape(-1, 9)
+    loss, dx = _ops.svd_orth_frobenius_step(rec.detach(), R_true)
+    return loss, dx.reshape(x.shape)
 
 
 def kabsch(P, Q):

@@ -30,9 +30,10 @@ def test_header_declares_the_expected_surface():
     d = _declared()
     for name in ("pe_version", "pe_last_error", "pe_launch_count", "pe_svd_orth_fwd", "pe_svd_orth_bwd",
                  "pe_ortho6d_fwd", "pe_quat_fwd", "pe_euler_fwd", "pe_frobenius_fwd", "pe_geodesic_fwd",
-                 "pe_angle_error_fwd", "pe_svd_orth_frobenius_fwd", "pe_svd_orth_frobenius_bwd", "pe_kabsch_fwd"):
+                 "pe_angle_error_fwd", "pe_svd_orth_frobenius_fwd", "pe_svd_orth_frobenius_bwd", "pe_svd_orth_frobenius_step",
+                 "pe_scale_by_scalar", "pe_kabsch_fwd"):
         assert name in d
-    assert len(d) >= 23
+    assert len(d) >= 25
 
 
 def test_library_exports_every_declared_symbol(built):

@@ -163,6 +163,39 @@ def test_config1_svd_plus_frobenius(rr):
     assert _relrows(xf.grad.cpu().numpy(), xr.grad.numpy())[cond > 0.1].max() <= 1e-4
 
 
+@pytest.mark.parametrize("n", [1, 63, 511, 512, 513, 4096 + 77])
+def test_single_pass_step_matches_two_pass_and_reference(rr, n):
+    """svd_frobenius_loss in its default single-pass form (one SVD per matrix, backward = one scaling pass), against
+    the recompute form and the float64 reference; upstream gradient != 1 to exercise the device-scalar scaling."""
+    torch.manual_seed(n)
+    x = torch.randn(n, 9)
+    r_true = O.symmetric_orthogonalization(torch.randn(n, 9).double()).float()
+    xr = x.double().requires_grad_(True)
+    loss_ref = O.loss_frobenius(O.symmetric_orthogonalization(xr), r_true.double())
+    (loss_ref * 2.5).backward()
+    grads = []
+    for single in (True, False):
+        xd = x.cuda().requires_grad_(True)
+        loss = rr.svd_frobenius_loss(xd, r_true.cuda(), single_pass=single)
+        assert loss.dtype == torch.float32 and loss.dim() == 0 and loss.requires_grad
+        (loss * 2.5).backward()
+        assert abs(loss.item() - loss_ref.item()) <= 2e-6
+        grads.append(xd.grad.cpu().numpy())
+    cond = O.svd_orth_conditioning(x).numpy()
+    ok = cond > 0.1
+    if ok.any():
+        assert _relrows(grads[0], xr.grad.numpy())[ok].max() <= 1e-4
+        assert _relrows(grads[1], xr.grad.numpy())[ok].max() <= 1e-4
+    # the two forms run the same per-matrix arithmetic
+    assert np.abs(grads[0] - grads[1]).max() <= 1e-6 * max(1.0, np.abs(grads[1]).max())
+    # explicit loss-and-gradient call, no autograd
+    l2, g2 = rr.svd_frobenius_loss_and_grad(x.cuda(), r_true.cuda())
+    assert abs(l2.item() - loss_ref.item()) <= 2e-6 and g2.shape == (n, 9) and not g2.requires_grad
+    assert np.abs(g2.cpu().numpy() * 2.5 - grads[0]).max() <= 1e-6 * max(1.0, np.abs(grads[0]).max())
+    # no gradient requested: the forward-only kernel serves the call
+    assert not rr.svd_frobenius_loss(x.cuda(), r_true.cuda()).requires_grad
+
+
 def test_degenerate_inputs_are_finite_rotations(rr):
     cases = torch.tensor([
         [0.0] * 9, [1, 0, 0, 0, 1, 0, 0, 0, 1], [-1, 0, 0, 0, -1, 0, 0, 0, -1], [1, 0, 0, 0, 1, 0, 0, 0, -1],
@@ -183,6 +216,8 @@ def test_opcheck(ops):
     a = torch.randn(33, 3, 3, device="cuda", requires_grad=True)
     b = torch.randn(33, 3, 3, device="cuda")
     torch.library.opcheck(ops.frobenius_mean, (a, b),
+                          test_utils=("test_schema", "test_faketensor", "test_autograd_registration"))
+    torch.library.opcheck(ops.svd_orth_frobenius_step, (x, b),
                           test_utils=("test_schema", "test_faketensor", "test_autograd_registration"))
     torch.library.opcheck(ops.ortho6d, (torch.randn(33, 6, device="cuda", requires_grad=True),),
                           test_utils=("test_schema", "test_faketensor", "test_autograd_registration"))

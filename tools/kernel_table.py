@@ -66,6 +66,8 @@ def main():
     add("svd_orth_bwd (recompute)", 108, lambda: check(lib.pe_svd_orth_bwd(P(x9), 9, None, P(g9), P(o9b), n, st), ""))
     add("svd_orth_frobenius_fwd", 72, lambda: check(lib.pe_svd_orth_frobenius_fwd(P(x9), 9, P(r1), None, P(sums), n, st), ""))
     add("svd_orth_frobenius_bwd", 108, lambda: check(lib.pe_svd_orth_frobenius_bwd(P(x9), 9, P(r1), P(one), 1.0 / n, P(o9b), n, st), ""))
+    add("svd_orth_frobenius_step (loss + grad, one SVD)", 108, lambda: check(lib.pe_svd_orth_frobenius_step(P(x9), 9, P(r1), 1.0 / n, P(o9b), P(sums), n, st), ""))
+    add("scale_by_scalar (backward of the step)", 72, lambda: check(lib.pe_scale_by_scalar(P(o9b), P(one), P(o9), 9 * n, st), ""))
     for name, w in (("ortho6d", 6), ("quat", 4), ("euler", 3), ("ortho5d", 5), ("expmap", 3)):
         xi, dxi = rnd(n, w), torch.empty(n, w, device=dev)
         f, b = getattr(lib, f"pe_{name}_fwd"), getattr(lib, f"pe_{name}_bwd")
