@@ -6,13 +6,16 @@
 Metric (BASELINE.json): 3x3 SVD orthogonalisations per second, forward + backward.
 A *step* is one pass of the reference's training step over one resident batch (Comparison/main.py:59-62,
 UPNA/main.py:54-58):  loss = loss_frobenius(symmetric_orthogonalization(x), R_true);  loss.backward()
-as two kernels through the C ABI - forward (reads x, R_true; sum of norms) and backward (reads x, R_true; writes
-dL/dx) - plus, for N > 1, one NCCL all-reduce of the loss sum between them.  180 algorithmic bytes per matrix.
+as the two launches the public API makes for it through the C ABI: the single-pass step kernel (reads x, R_true;
+ONE decomposition per matrix; writes the loss sum and dL/dx for a unit upstream gradient: 108 B/matrix) and the
+backward's scaling pass by the upstream scalar (72 B/matrix) - plus, for N > 1, one NCCL all-reduce of the loss sum
+between them.  180 bytes per matrix.  The recompute pair (forward 72 B + backward 108 B, two decompositions) and the
+unfused svd_orth kernels are timed as well and reported under "also".
 
   value        whole-job matrices/s with x, R_true resident in HBM (CUDA events, max over ranks)
   e2e          same step through the public API (rotation_representation.svd_frobenius_loss + autograd) with HOST
                pinned inputs: H2D of x and R_true and D2H of the loss inside the timed region
-  roofline     dominant kernel (backward): algorithmic bytes / event-timed duration vs MEASURED_PEAKS.json
+  roofline     dominant kernel (the step kernel): algorithmic bytes / event-timed duration vs MEASURED_PEAKS.json
   cpu_baseline the oracle port (= the reference's torch code) in fp32 on this box's host cores, bounded sample
   --impl reference   times that CPU implementation as the headline instead (rank 0 only)
 """
@@ -33,6 +36,9 @@ sys.path.insert(0, ROOT)
 METRIC = "svd_orthogonalizations_per_sec_fwd_bwd"
 UNIT = "matrices/s"
 BYTES_FWD, BYTES_BWD = 72, 108            # algorithmic bytes per matrix per launch
+BYTES_STEP, BYTES_SCALE = 108, 72         # single-pass step kernel; scaling pass of its backward
+TRAFFIC_STEP = 1.7552e9                   # dram read + write bytes per launch of the step kernel at n = 2^24
+                                          # (ncu --set full, profiles/r1f_ncu_full_summary.csv: 1.208 GB + 547 MB)
 N_DEFAULT = 1 << 24                       # BASELINE config 2: 16M matrices on one B200
 
 
@@ -197,11 +203,20 @@ def run_native(args):
     inv_n_global = 1.0 / (n * world)
     stream = torch.cuda.current_stream().cuda_stream
 
-    def k_fwd():
+    dx_unit = torch.empty(n, 9, device=dev)
+
+    def k_fwd():     # forward of svd_frobenius_loss: loss sum + gradient for a unit upstream gradient, one SVD
+        check(lib.pe_svd_orth_frobenius_step(x.data_ptr(), 9, r_true.data_ptr(), inv_n_global, dx_unit.data_ptr(),
+                                             loss_sum.data_ptr(), n, stream), "step")
+
+    def k_bwd():     # its backward: scale by the upstream scalar (read on the device)
+        check(lib.pe_scale_by_scalar(dx_unit.data_ptr(), gout.data_ptr(), dx.data_ptr(), 9 * n, stream), "scale")
+
+    def k_fwd2():    # the recompute pair (single_pass=False)
         check(lib.pe_svd_orth_frobenius_fwd(x.data_ptr(), 9, r_true.data_ptr(), None, loss_sum.data_ptr(), n, stream),
               "fwd")
 
-    def k_bwd():
+    def k_bwd2():
         check(lib.pe_svd_orth_frobenius_bwd(x.data_ptr(), 9, r_true.data_ptr(), gout.data_ptr(), inv_n_global,
                                             dx.data_ptr(), n, stream), "bwd")
 
@@ -273,7 +288,10 @@ def run_native(args):
             x.data_ptr(), 9, r_out.data_ptr(), g_up.data_ptr(), dx.data_ptr(), n, stream), "b"))
         also["svd_orth_bwd_recompute_ms"] = time_kernel(lambda: check(lib.pe_svd_orth_bwd(
             x.data_ptr(), 9, None, g_up.data_ptr(), dx.data_ptr(), n, stream), "b"))
-        also["fused_fwd_ms"], also["fused_bwd_ms"] = fwd_ms, bwd_ms
+        also["step_kernel_ms"], also["scale_kernel_ms"] = fwd_ms, bwd_ms
+        also["recompute_fwd_ms"], also["recompute_bwd_ms"] = time_kernel(k_fwd2), time_kernel(k_bwd2)
+        also["recompute_pair_matrices_per_s"] = n / ((also["recompute_fwd_ms"] + also["recompute_bwd_ms"]) * 1e-3)
+        also["loss_and_grad_only_matrices_per_s"] = n / (fwd_ms * 1e-3)
         also["loss"] = loss_value
 
     # ---- e2e: public API, host-resident inputs ---------------------------------------------------------------------
@@ -315,11 +333,11 @@ def run_native(args):
         return
 
     peak, peak_src = measured_peak_gbs()
-    achieved = BYTES_BWD * n / (bwd_ms * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "stream_tma_kernel<SvdFrobBwd> (pe_svd_orth_frobenius_bwd)",
-                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
-                "peak_source": peak_src, "bytes_per_matrix": BYTES_BWD, "ms": bwd_ms,
-                "step_frac": (BYTES_FWD + BYTES_BWD) * n / (ms_per_step * 1e-3) / 1e9 / peak}
+    achieved = BYTES_STEP * n / (fwd_ms * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": "stream_tma_kernel<SvdFrobStep> (pe_svd_orth_frobenius_step)",
+                "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": TRAFFIC_STEP * n / N_DEFAULT,
+                "peak_source": peak_src, "bytes_per_matrix": BYTES_STEP, "ms": fwd_ms,
+                "step_frac": (BYTES_STEP + BYTES_SCALE) * n / (ms_per_step * 1e-3) / 1e9 / peak}
 
     cpu = None
     if not args.no_cpu_baseline:
@@ -333,6 +351,7 @@ def run_native(args):
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
         "config": {"workload": f"svd_orth+frobenius fwd+bwd, {n} random 3x3 fp32 matrices per GPU (BASELINE config 2)",
+                   "launches_per_step": "svd_orth_frobenius_step (108 B) + scale_by_scalar (72 B)",
                    "matrices_per_gpu": n, "l2": "inputs (2 x %.0f MB) larger than the 126 MB L2" % (n * 36 / 1e6),
                    "collective": "ncclAllReduce(3 x f64) per step" if world > 1 else "none"},
         "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
