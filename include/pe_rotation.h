@@ -117,6 +117,47 @@ int pe_scale_by_scalar(const float* x, const float* g, float* y, int64_t nwords,
  * pe_svd_orth of sum_k (q_k - qbar)(p_k - pbar)^T;  t (nullable, b x 3) = qbar - R pbar. */
 int pe_kabsch_fwd(const float* p, const float* q, int64_t b, int64_t npts, float* r, float* t, void* stream);
 
+/* as pe_kabsch_fwd, and additionally ctx[b][15] = (H row-major 9, pbar 3, qbar 3): what pe_kabsch_bwd_coeffs needs. */
+int pe_kabsch_fwd_ctx(const float* p, const float* q, int64_t b, int64_t npts, float* r, float* t, float* ctx,
+                      void* stream);
+/* Kabsch backward, per-pair part.  g[b][12] = (dL/dR 9, dL/dt 3).  Writes the affine coefficients
+ * (A row-major 9, offset 3) of the two point gradients:  dL/dq_k = A_q p_k + b_q,  dL/dp_k = A_p q_k + b_p,
+ * which two pe_affine_points launches then apply (48 B per point pair in total). */
+int pe_kabsch_bwd_coeffs(const float* ctx, const float* r, const float* g, int64_t npts, float* coef_q, float* coef_p,
+                         int64_t b, void* stream);
+/* m[b][9] = sum_k g[b][k] p[b][k]^T (uncentred), gsum[b][3] = sum_k g[b][k] (nullable): the reduction behind the
+ * gradient of pe_affine_points w.r.t. its matrix and offset. */
+int pe_cloud_outer_sum(const float* g, const float* p, int64_t b, int64_t npts, float* m, float* gsum, void* stream);
+
+/* ---- per-cloud affine map of xyz points ---------------------------------------------------------------------------
+ * out[b][k] = A_b p[b][k] + t_b.  Serves pc2 = gt_rmat @ pc1 (point_cloud/main.py:173-181, without the (B*N,3,3)
+ * expansion), transform_pts (Iterative/loss.py:51-69: a = T, a_stride 16, a_row 4, t = T + 3, t_stride 16, t_elem 4)
+ * and the Kabsch backward.  a_row = floats between rows of A; transpose != 0 applies A^T; t nullable. */
+int pe_affine_points(const float* a, int64_t a_stride, int a_row, int transpose, const float* t, int64_t t_stride,
+                     int t_elem, const float* p, int64_t b, int64_t npts, float* out, void* stream);
+
+/* ---- cloud-pair rotation sampler, deterministic part      point_cloud/prepare.py:21-49 ---------------------------
+ * r_b = matrix of the quaternion (cos theta_b, normalize(axis_b) sin theta_b); |axis| floored at 1e-8 (:12-18).
+ * theta (n), axis (n, 3) come from the caller's RNG (the reference: uniform(-pi, pi) and randn). */
+int pe_axis_angle_fwd(const float* theta, const float* axis, float* r, int64_t n, void* stream);
+
+/* ---- CosyPose pose update                                 Iterative/utility.py:90-128 ----------------------------
+ * out[b][>=12] = network output (9 rotation entries, vx, vy, vz), t_init/t_pred = 4x4 row-major.
+ * dR = pe_svd_orth(out[:9]); R' = dR R_k; z' = vz z_k; x' = (vx/fx + x_k/z_k) z'; y' likewise; last row (0,0,0,1).
+ * bwd: d_out[b][12] from g_t[b][16] = dL/dT_pred (T_init is a detached input, Iterative/main.py:93). */
+int pe_pose_update_fwd(const float* out, int64_t out_stride, const float* t_init, float fx, float fy, float* t_pred,
+                       int64_t n, void* stream);
+int pe_pose_update_bwd(const float* out, int64_t out_stride, const float* t_init, const float* g_t, float fx, float fy,
+                       float* d_out, int64_t n, void* stream);
+
+/* ---- ADD-L1 mesh losses                                   Iterative/loss.py:10-69 --------------------------------
+ * t_gt, t_pred: (b, 16) poses; pts: (b, npts, 3) vertices, read ONCE (12 B/vertex).
+ * disentangled == 0: item_b = mean_{k,i} |(T_gt p_k - T_pred p_k)_i|                       (compute_ADD_L1_loss)
+ * disentangled != 0: rotation + xy-translation + depth terms of compute_disentangled_ADD_L1_loss.
+ * item (b, nullable), *sum = sum_b item_b (nullable), grad[b][12] = d item_b / d T_pred[:3, :4] (nullable). */
+int pe_add_l1(const float* t_gt, const float* t_pred, const float* pts, int64_t b, int64_t npts, int disentangled,
+              float* item, double* sum, float* grad, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

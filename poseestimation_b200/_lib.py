@@ -41,6 +41,14 @@ SIGNATURES = {
     "pe_svd_orth_frobenius_step": [_f, _i64, _f, _flt, _f, _f, _i64, _f],
     "pe_scale_by_scalar": [_f, _f, _f, _i64, _f],
     "pe_kabsch_fwd": [_f, _f, _i64, _i64, _f, _f, _f],
+    "pe_kabsch_fwd_ctx": [_f, _f, _i64, _i64, _f, _f, _f, _f],
+    "pe_kabsch_bwd_coeffs": [_f, _f, _f, _i64, _f, _f, _i64, _f],
+    "pe_cloud_outer_sum": [_f, _f, _i64, _i64, _f, _f, _f],
+    "pe_affine_points": [_f, _i64, _int, _int, _f, _i64, _int, _f, _i64, _i64, _f, _f],
+    "pe_axis_angle_fwd": [_f, _f, _f, _i64, _f],
+    "pe_pose_update_fwd": [_f, _i64, _f, _flt, _flt, _f, _i64, _f],
+    "pe_pose_update_bwd": [_f, _i64, _f, _f, _flt, _flt, _f, _i64, _f],
+    "pe_add_l1": [_f, _f, _f, _i64, _i64, _int, _f, _f, _f, _f],
 }
 
 

@@ -143,6 +143,24 @@ int pe_svd_orth_frobenius_step(const float* m, int64_t m_stride, const float* r_
                                double* sum, int64_t n, void* stream) {
     return run<SvdFrobStep>(m, m_stride, r_true, nullptr, dm, nullptr, n, sum, nullptr, {inv_n}, stream);
 }
+int pe_axis_angle_fwd(const float* theta, const float* axis, float* r, int64_t n, void* stream) {
+    return run<AxisAngleFwd>(theta, 1, axis, nullptr, r, nullptr, n, nullptr, nullptr, {}, stream);
+}
+int pe_kabsch_bwd_coeffs(const float* ctx, const float* r, const float* g, int64_t npts, float* coef_q, float* coef_p,
+                         int64_t b, void* stream) {
+    if (npts < 1) return fail(PE_ERR_BAD_ARG, "bad cloud size");
+    return run<KabschBwdCoeffs>(ctx, 15, r, g, coef_q, coef_p, b, nullptr, nullptr, {1.0f / (float)npts}, stream);
+}
+int pe_pose_update_fwd(const float* out, int64_t out_stride, const float* t_init, float fx, float fy, float* t_pred,
+                       int64_t n, void* stream) {
+    return run<PoseUpdateFwd>(out, out_stride, t_init, nullptr, t_pred, nullptr, n, nullptr, nullptr,
+                              {1.0f / fx, 1.0f / fy}, stream);
+}
+int pe_pose_update_bwd(const float* out, int64_t out_stride, const float* t_init, const float* g_t, float fx, float fy,
+                       float* d_out, int64_t n, void* stream) {
+    return run<PoseUpdateBwd>(out, out_stride, t_init, g_t, d_out, nullptr, n, nullptr, nullptr,
+                              {1.0f / fx, 1.0f / fy}, stream);
+}
 int pe_scale_by_scalar(const float* x, const float* g, float* y, int64_t nwords, void* stream) {
     if (nwords < 0) return fail(PE_ERR_BAD_ARG, "negative word count");
     if (nwords == 0) return 0;

@@ -26,6 +26,8 @@ struct KabschParams {
     const float* q;
     float* r;
     float* t;  // nullable
+    float* ctx;  // nullable: per pair H (9), pbar (3), qbar (3) - what the backward needs besides R
+    int raw;     // 1: no alignment; r = sum_k q_k p_k^T (uncentred), t = sum_k q_k  (reduction of an outer product)
     long long b;
     int npts;
     int use_tma;
@@ -86,9 +88,28 @@ __global__ void __launch_bounds__(kKWarps * 32, 1) kabsch_kernel(const KabschPar
     int parked = 0;
 
     auto flush = [&]() {
-        if (lane < parked) {
+        if (lane < parked && prm.raw) {
+            // sum q p^T = sum (q - qbar)(p - pbar)^T + N qbar pbar^T ;  sum q = N qbar
+            const float nn = (float)npts;
+            float* dst = prm.r + kpair * 9;
+#pragma unroll
+            for (int i = 0; i < 3; ++i)
+#pragma unroll
+                for (int j = 0; j < 3; ++j) dst[3 * i + j] = fmaf(nn * kq[i], kp[j], keep[3 * i + j]);
+            if (prm.t) {
+                float* td = prm.t + kpair * 3;
+                td[0] = nn * kq[0]; td[1] = nn * kq[1]; td[2] = nn * kq[2];
+            }
+        } else if (lane < parked) {
             float r[9], ds;
             svd_orth_fast(keep, r, ds);
+            if (prm.ctx) {
+                float* cd = prm.ctx + kpair * 15;
+#pragma unroll
+                for (int i = 0; i < 9; ++i) cd[i] = keep[i];
+                cd[9] = kp[0]; cd[10] = kp[1]; cd[11] = kp[2];
+                cd[12] = kq[0]; cd[13] = kq[1]; cd[14] = kq[2];
+            }
             float* dst = prm.r + kpair * 9;
 #pragma unroll
             for (int i = 0; i < 9; ++i) dst[i] = r[i];
@@ -165,11 +186,11 @@ __global__ void __launch_bounds__(kKWarps * 32, 1) kabsch_kernel(const KabschPar
 
 using namespace pe;
 
-extern "C" int pe_kabsch_fwd(const float* p, const float* q, int64_t b, int64_t npts, float* r, float* t,
-                             void* stream) {
-    if (b < 0 || npts < 1 || npts > (1 << 24)) return fail(PE_ERR_BAD_ARG, "bad cloud count or cloud size");
-    if (b == 0) return 0;
-    if (!p || !q || !r) return fail(PE_ERR_BAD_ARG, "null pointer");
+namespace {
+int kabsch_launch(KabschParams prm, void* stream) {
+    if (prm.b < 0 || prm.npts < 1 || prm.npts > (1 << 24)) return fail(PE_ERR_BAD_ARG, "bad cloud count or cloud size");
+    if (prm.b == 0) return 0;
+    if (!prm.p || !prm.q || !prm.r) return fail(PE_ERR_BAD_ARG, "null pointer");
     int dev = 0;
     cudaError_t e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return fail_cuda(e, "cudaGetDevice");
@@ -184,14 +205,28 @@ extern "C" int pe_kabsch_fwd(const float* p, const float* q, int64_t b, int64_t 
         if (e != cudaSuccess) return fail_cuda(e, "cudaFuncSetAttribute(smem)");
         sms[dev] = prop.multiProcessorCount;
     }
-    KabschParams prm{p, q, r, t, (long long)b, (int)npts, 0};
-    prm.use_tma = (npts % 4 == 0) && ((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(q)) & 15u) == 0 &&
-                  !force_direct();
-    long long grid = (b + kKWarps - 1) / kKWarps;
+    prm.use_tma = (prm.npts % 4 == 0) &&
+                  ((reinterpret_cast<uintptr_t>(prm.p) | reinterpret_cast<uintptr_t>(prm.q)) & 15u) == 0 && !force_direct();
+    long long grid = (prm.b + kKWarps - 1) / kKWarps;
     if (grid > sms[dev]) grid = sms[dev];
     kabsch_kernel<<<(unsigned)grid, kKWarps * 32, kKSmem, static_cast<cudaStream_t>(stream)>>>(prm);
     e = cudaGetLastError();
     if (e != cudaSuccess) return fail_cuda(e, "kabsch_kernel");
     count_launch();
     return 0;
+}
+}  // namespace
+
+extern "C" int pe_kabsch_fwd(const float* p, const float* q, int64_t b, int64_t npts, float* r, float* t,
+                             void* stream) {
+    return kabsch_launch(KabschParams{p, q, r, t, nullptr, 0, (long long)b, (int)npts, 0}, stream);
+}
+extern "C" int pe_kabsch_fwd_ctx(const float* p, const float* q, int64_t b, int64_t npts, float* r, float* t,
+                                 float* ctx, void* stream) {
+    if (!ctx) return fail(PE_ERR_BAD_ARG, "null context pointer");
+    return kabsch_launch(KabschParams{p, q, r, t, ctx, 0, (long long)b, (int)npts, 0}, stream);
+}
+extern "C" int pe_cloud_outer_sum(const float* g, const float* p, int64_t b, int64_t npts, float* m, float* gsum,
+                                  void* stream) {
+    return kabsch_launch(KabschParams{p, g, m, gsum, nullptr, 1, (long long)b, (int)npts, 0}, stream);
 }

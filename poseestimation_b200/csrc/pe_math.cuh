@@ -547,6 +547,90 @@ PE_DEV void expmap_pullback(const float* v, const float* g, float* dv) {
 }
 
 // ---------------------------------------------------------------------------------------------------------
+// Cloud-pair rotation sampler, deterministic part (reference: get_sampled_rotation_matrices_by_axisAngle,
+// point_cloud/prepare.py:21-49): theta and the un-normalised axis come from the caller's RNG; the axis is divided by
+// max(|axis|, 1e-8) (prepare.py:12-18) and the matrix is built from q = (cos theta, axis sin theta) with the unit
+// quaternion formula.  NOTE the reference feeds the FULL angle into the quaternion, so the rotation is by 2 theta;
+// that is reproduced, not corrected.
+PE_DEV void axis_angle_matrix(float theta, const float* axis, float* r) {
+    float n2 = fmaf(axis[2], axis[2], fmaf(axis[1], axis[1], axis[0] * axis[0]));
+    float k = n2 > kQuatFloor * kQuatFloor ? rsqrt_nr(n2) : (1.0f / kQuatFloor);
+    float sn, cs;
+    sincos_f(theta, &sn, &cs);
+    float w = cs, x = axis[0] * k * sn, y = axis[1] * k * sn, z = axis[2] * k * sn;
+    float xx = x * x, yy = y * y, zz = z * z, xy = x * y, xz = x * z, yz = y * z, xw = x * w, yw = y * w, zw = z * w;
+    r[0] = 1.f - 2.f * yy - 2.f * zz; r[1] = 2.f * xy - 2.f * zw;       r[2] = 2.f * xz + 2.f * yw;
+    r[3] = 2.f * xy + 2.f * zw;       r[4] = 1.f - 2.f * xx - 2.f * zz; r[5] = 2.f * yz - 2.f * xw;
+    r[6] = 2.f * xz - 2.f * yw;       r[7] = 2.f * yz + 2.f * xw;       r[8] = 1.f - 2.f * xx - 2.f * yy;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Kabsch backward, per-pair part.  Forward (pe_kabsch.cu): H = sum_k (q_k - qbar)(p_k - pbar)^T, R = svd_orth(H),
+// t = qbar - R pbar.  With upstream gR (9) and gt (3):
+//   gR' = gR - gt pbar^T ;  G_H = pullback(H, R, gR') ;
+//   dq_k = G_H (p_k - pbar) + gt/N           = A_q p_k + b_q ,  A_q = G_H   , b_q = gt/N - G_H pbar
+//   dp_k = G_H^T (q_k - qbar) - R^T gt / N   = A_p q_k + b_p ,  A_p = G_H^T , b_p = -R^T gt/N - G_H^T qbar
+// (the centroid terms of dH/dq_k vanish because sum_k (p_k - pbar) = 0).  ctx = (H, pbar, qbar); cq, cp = (A, b).
+PE_DEV void kabsch_bwd_coeffs(const float* ctx, const float* r, const float* g, float inv_n, float* cq, float* cp) {
+    const float* h = ctx;
+    const float* pb = ctx + 9;
+    const float* qb = ctx + 12;
+    const float* gt = g + 9;
+    float gr[9], gh[9];
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = 0; j < 3; ++j) gr[3 * i + j] = fmaf(-gt[i], pb[j], g[3 * i + j]);
+    svd_orth_pullback(h, r, gr, gh);
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+#pragma unroll
+        for (int j = 0; j < 3; ++j) { cq[3 * i + j] = gh[3 * i + j]; cp[3 * i + j] = gh[3 * j + i]; }
+        cq[9 + i] = fmaf(gt[i], inv_n, -(gh[3 * i] * pb[0] + gh[3 * i + 1] * pb[1] + gh[3 * i + 2] * pb[2]));
+        float rtg = r[i] * gt[0] + r[3 + i] * gt[1] + r[6 + i] * gt[2];
+        cp[9 + i] = -fmaf(rtg, inv_n, gh[i] * qb[0] + gh[3 + i] * qb[1] + gh[6 + i] * qb[2]);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// CosyPose-style pose update (reference: calculate_T_pred, Iterative/utility.py:90-128; camera constants from
+// get_scene_parameters, :73-88).  o = network output (9 rotation entries, then vx, vy, vz); ti = T_init (4x4,
+// row-major); to = T_pred.   dR = svd_orth(o[0:9]);  R_new = dR R_k;  z' = vz z_k;
+// x' = (vx/fx + x_k/z_k) z';  y' = (vy/fy + y_k/z_k) z';  last row (0, 0, 0, 1)  (the intent of `combine`, :63-71).
+PE_DEV void pose_update(const float* o, const float* ti, float inv_fx, float inv_fy, float* to) {
+    float dr[9], ds;
+    svd_orth_fast(o, dr, ds);
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = 0; j < 3; ++j)
+            to[4 * i + j] = fmaf(dr[3 * i + 2], ti[8 + j], fmaf(dr[3 * i + 1], ti[4 + j], dr[3 * i] * ti[j]));
+    float zk = ti[11], zn = o[11] * zk;
+    to[3] = (o[9] * inv_fx + ti[3] / zk) * zn;
+    to[7] = (o[10] * inv_fy + ti[7] / zk) * zn;
+    to[11] = zn;
+    to[12] = 0.f; to[13] = 0.f; to[14] = 0.f; to[15] = 1.f;
+}
+// pullback of pose_update w.r.t. the network output (T_init is a detached input in the reference, Iterative/main.py:93)
+PE_DEV void pose_update_pullback(const float* o, const float* ti, const float* g, float inv_fx, float inv_fy,
+                                 float* d_o) {
+    float dr[9], ds, gd[9];
+    svd_orth_fast(o, dr, ds);
+    // G_dR = G_Rnew R_k^T
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = 0; j < 3; ++j)
+            gd[3 * i + j] = fmaf(g[4 * i + 2], ti[4 * j + 2], fmaf(g[4 * i + 1], ti[4 * j + 1], g[4 * i] * ti[4 * j]));
+    svd_orth_pullback(o, dr, gd, d_o);
+    float zk = ti[11], zn = o[11] * zk;
+    float ax = o[9] * inv_fx + ti[3] / zk, ay = o[10] * inv_fy + ti[7] / zk;
+    d_o[9] = g[3] * zn * inv_fx;
+    d_o[10] = g[7] * zn * inv_fy;
+    d_o[11] = zk * (g[11] + g[3] * ax + g[7] * ay);
+}
+
+// ---------------------------------------------------------------------------------------------------------
 // Distances on SO(3). tr(A B^T) = tr(A^T B) = sum_ij A_ij B_ij, so one inner product serves
 // compute_geodesic_distance_from_two_matrices (rotation_representation.py:209-227, m1 m2^T),
 // angle_error (:230-242, R1^T R2, float64, degrees) and geodesic (point_cloud/main.py:61-73).

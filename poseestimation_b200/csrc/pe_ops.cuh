@@ -263,6 +263,46 @@ struct SvdFrobBwd {
     }
 };
 
+// ---- 8f.4 cloud-pair rotation sampler, deterministic part (point_cloud/prepare.py:21-49): (theta, axis) -> R ------
+struct AxisAngleFwd {
+    PE_OP_COMMON("axis_angle_fwd", 1, 3, 0, 9, 0, 0, false, 4)
+    using Extra = NoExtra;
+    __device__ static __forceinline__ void run(const float* th, const float* ax, const float*, float* r, float*,
+                                               double*, int&, const Extra&) { axis_angle_matrix(th[0], ax, r); }
+};
+// ---- 8f.3 Kabsch backward, per-pair part: (ctx, R, [gR | gt]) -> affine coefficients for dQ and dP -----------------
+struct InvCount {
+    float inv_n;
+};
+struct KabschBwdCoeffs {
+    PE_OP_COMMON("kabsch_bwd_coeffs", 15, 9, 12, 12, 12, 0, false, 2)
+    using Extra = InvCount;
+    __device__ static __forceinline__ void run(const float* ctx, const float* r, const float* g, float* cq, float* cp,
+                                               double*, int&, const Extra& ex) {
+        kabsch_bwd_coeffs(ctx, r, g, ex.inv_n, cq, cp);
+    }
+};
+// ---- 8f.2 CosyPose pose update (Iterative/utility.py:90-128): (net output 12, T_init 16) -> T_pred 16 ---------------
+struct Camera {
+    float inv_fx, inv_fy;
+};
+struct PoseUpdateFwd {
+    PE_OP_COMMON("pose_update_fwd", 12, 16, 0, 16, 0, 0, false, 2)
+    using Extra = Camera;
+    __device__ static __forceinline__ void run(const float* o, const float* ti, const float*, float* to, float*,
+                                               double*, int&, const Extra& ex) {
+        pose_update(o, ti, ex.inv_fx, ex.inv_fy, to);
+    }
+};
+struct PoseUpdateBwd {
+    PE_OP_COMMON("pose_update_bwd", 12, 16, 16, 12, 0, 0, false, 2)
+    using Extra = Camera;
+    __device__ static __forceinline__ void run(const float* o, const float* ti, const float* g, float* d_o, float*,
+                                               double*, int&, const Extra& ex) {
+        pose_update_pullback(o, ti, g, ex.inv_fx, ex.inv_fy, d_o);
+    }
+};
+
 // single pass of the training step: the loss AND the gradient for a unit upstream gradient from ONE decomposition
 // (reads M, R_true; writes dM = mul * pullback((R - R_true)/|R - R_true|_F); adds |R - R_true|_F to the sum).  108 B.
 struct StepScale {

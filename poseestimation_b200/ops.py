@@ -536,3 +536,293 @@ def kabsch(p: Tensor, q: Tensor) -> tuple[Tensor, Tensor]:
 @kabsch.register_fake
 def _(p, q):
     return p.new_empty((p.shape[0], 3, 3)), p.new_empty((p.shape[0], 3))
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# per-cloud affine map of points: out[b, k] = A_b p[b, k] + t_b
+# (pc2 = gt_rmat @ pc1, /root/reference/point_cloud/main.py:173-181; transform_pts, Iterative/loss.py:51-69)
+def _clouds(p: Tensor) -> Tensor:
+    if p.dtype != torch.float32:
+        raise TypeError("pe_b200 ops compute in float32")
+    if p.dim() != 3 or p.shape[2] != 3:
+        raise ValueError(f"expected (B, N, 3) points, got {tuple(p.shape)}")
+    return p.contiguous()
+
+
+def _affine_launch(a: Tensor, t: Tensor | None, p: Tensor, transpose: bool) -> Tensor:
+    """a: (B, 3, 3) view with unit inner stride (e.g. T[:, :3, :3]); t: (B, 3) view or None (e.g. T[:, :3, 3])."""
+    b, npts = p.shape[0], p.shape[1]
+    if a.dtype != torch.float32 or a.shape != (b, 3, 3):
+        raise ValueError(f"expected a float32 ({b}, 3, 3) matrix batch, got {a.dtype} {tuple(a.shape)}")
+    if b > 1 and (a.stride(2) != 1 or a.stride(1) < 3 or a.stride(0) < 2 * a.stride(1) + 3):
+        a = a.contiguous()
+    if b <= 1:
+        a = a.contiguous()
+    if t is not None:
+        if t.dtype != torch.float32 or t.shape != (b, 3):
+            raise ValueError(f"expected a float32 ({b}, 3) offset batch, got {t.dtype} {tuple(t.shape)}")
+        if b <= 1 or t.stride(1) < 1 or t.stride(0) < 2 * t.stride(1) + 1:
+            t = t.contiguous()
+    out = torch.empty_like(p)
+    if b and npts:
+        with torch.cuda.device(p.device):
+            check(lib.pe_affine_points(a.data_ptr(), a.stride(0), a.stride(1), int(transpose), _p(t),
+                                       t.stride(0) if t is not None else 3, t.stride(1) if t is not None else 1,
+                                       p.data_ptr(), b, npts, out.data_ptr(), _stream()), "pe_affine_points")
+    return out
+
+
+@torch.library.custom_op(f"{NS}::affine_points", mutates_args=(), device_types="cuda")
+def affine_points(a: Tensor, t: Tensor | None, p: Tensor, transpose: bool) -> Tensor:
+    return _affine_launch(a, t, _clouds(p), transpose)
+
+
+@affine_points.register_fake
+def _(a, t, p, transpose):
+    return p.new_empty(p.shape)
+
+
+@torch.library.custom_op(f"{NS}::cloud_outer_sum", mutates_args=(), device_types="cuda")
+def cloud_outer_sum(g: Tensor, p: Tensor) -> tuple[Tensor, Tensor]:
+    """(sum_k g[b, k] p[b, k]^T as (B, 3, 3),  sum_k g[b, k] as (B, 3))."""
+    g, p = _clouds(g), _clouds(p)
+    if g.shape != p.shape:
+        raise ValueError("cloud shapes differ")
+    b, npts = p.shape[0], p.shape[1]
+    m = torch.zeros((b, 3, 3), dtype=torch.float32, device=p.device)
+    s = torch.zeros((b, 3), dtype=torch.float32, device=p.device)
+    if b and npts:
+        with torch.cuda.device(p.device):
+            check(lib.pe_cloud_outer_sum(g.data_ptr(), p.data_ptr(), b, npts, m.data_ptr(), s.data_ptr(), _stream()),
+                  "pe_cloud_outer_sum")
+    return m, s
+
+
+@cloud_outer_sum.register_fake
+def _(g, p):
+    return p.new_empty((p.shape[0], 3, 3)), p.new_empty((p.shape[0], 3))
+
+
+def _affine_setup(ctx, inputs, output):
+    a, t, p, transpose = inputs
+    ctx.save_for_backward(a, p)
+    ctx.transpose = transpose
+    ctx.has_t = t is not None
+
+
+def _affine_backward(ctx, g):
+    a, p = ctx.saved_tensors
+    need_a, need_t, need_p = ctx.needs_input_grad[0], ctx.needs_input_grad[1], ctx.needs_input_grad[2]
+    da = dt = dp = None
+    if need_p:
+        dp = affine_points(a, None, g, not ctx.transpose)
+    if need_a or (need_t and ctx.has_t):
+        m, s = cloud_outer_sum(g, p)
+        if need_a:
+            da = m.transpose(1, 2) if ctx.transpose else m
+        if need_t and ctx.has_t:
+            dt = s
+    return da, dt, dp, None
+
+
+affine_points.register_autograd(_affine_backward, setup_context=_affine_setup)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# 8f.3  differentiable Kabsch: forward keeps (H, pbar, qbar) per pair, backward = per-pair coefficients + two affine
+# passes over the clouds (48 B per point pair)
+@torch.library.custom_op(f"{NS}::kabsch_ctx", mutates_args=(), device_types="cuda")
+def kabsch_ctx(p: Tensor, q: Tensor) -> tuple[Tensor, Tensor, Tensor]:
+    p, q = _clouds(p), _clouds(q)
+    if p.shape != q.shape:
+        raise ValueError(f"expected two (B, N, 3) clouds, got {tuple(p.shape)} and {tuple(q.shape)}")
+    b, npts = p.shape[0], p.shape[1]
+    r = torch.empty((b, 3, 3), dtype=torch.float32, device=p.device)
+    t = torch.empty((b, 3), dtype=torch.float32, device=p.device)
+    c = torch.empty((b, 15), dtype=torch.float32, device=p.device)
+    if b:
+        with torch.cuda.device(p.device):
+            check(lib.pe_kabsch_fwd_ctx(p.data_ptr(), q.data_ptr(), b, npts, r.data_ptr(), t.data_ptr(), c.data_ptr(),
+                                        _stream()), "pe_kabsch_fwd_ctx")
+    return r, t, c
+
+
+@kabsch_ctx.register_fake
+def _(p, q):
+    b = p.shape[0]
+    return p.new_empty((b, 3, 3)), p.new_empty((b, 3)), p.new_empty((b, 15))
+
+
+@torch.library.custom_op(f"{NS}::kabsch_bwd", mutates_args=(), device_types="cuda")
+def kabsch_bwd(p: Tensor, q: Tensor, r: Tensor, c: Tensor, g_r: Tensor, g_t: Tensor) -> tuple[Tensor, Tensor]:
+    p, q = _clouds(p), _clouds(q)
+    b, npts = p.shape[0], p.shape[1]
+    g = torch.cat([g_r.reshape(b, 9), g_t.reshape(b, 3)], dim=1).to(torch.float32).contiguous()
+    cq = torch.empty((b, 12), dtype=torch.float32, device=p.device)
+    cp = torch.empty((b, 12), dtype=torch.float32, device=p.device)
+    dp, dq = torch.empty_like(p), torch.empty_like(q)
+    if b:
+        st = _stream()
+        with torch.cuda.device(p.device):
+            check(lib.pe_kabsch_bwd_coeffs(c.contiguous().data_ptr(), r.contiguous().data_ptr(), g.data_ptr(), npts,
+                                           cq.data_ptr(), cp.data_ptr(), b, st), "pe_kabsch_bwd_coeffs")
+            check(lib.pe_affine_points(cq.data_ptr(), 12, 3, 0, cq.data_ptr() + 36, 12, 1, p.data_ptr(), b, npts,
+                                       dq.data_ptr(), st), "pe_affine_points(dq)")
+            check(lib.pe_affine_points(cp.data_ptr(), 12, 3, 0, cp.data_ptr() + 36, 12, 1, q.data_ptr(), b, npts,
+                                       dp.data_ptr(), st), "pe_affine_points(dp)")
+    return dp, dq
+
+
+@kabsch_bwd.register_fake
+def _(p, q, r, c, g_r, g_t):
+    return p.new_empty(p.shape), q.new_empty(q.shape)
+
+
+def _kabsch_setup(ctx, inputs, output):
+    ctx.save_for_backward(inputs[0], inputs[1], output[0], output[2])
+    ctx.mark_non_differentiable(output[2])
+
+
+def _kabsch_backward(ctx, g_r, g_t, _g_c):
+    p, q, r, c = ctx.saved_tensors
+    if g_r is None:
+        g_r = torch.zeros_like(r)
+    if g_t is None:
+        g_t = r.new_zeros((r.shape[0], 3))
+    return kabsch_bwd(p, q, r, c, g_r, g_t)
+
+
+kabsch_ctx.register_autograd(_kabsch_backward, setup_context=_kabsch_setup)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# 8f.4  cloud-pair rotation sampler, deterministic part            /root/reference/point_cloud/prepare.py:21-49
+@torch.library.custom_op(f"{NS}::axis_angle_matrix", mutates_args=(), device_types="cuda")
+def axis_angle_matrix(theta: Tensor, axis: Tensor) -> Tensor:
+    if theta.dtype != torch.float32 or axis.dtype != torch.float32:
+        raise TypeError("pe_b200 ops compute in float32")
+    n = theta.numel()
+    if axis.shape != (n, 3):
+        raise ValueError(f"expected axis of shape ({n}, 3), got {tuple(axis.shape)}")
+    theta, axis = theta.reshape(n).contiguous(), axis.contiguous()
+    r = torch.empty((n, 3, 3), dtype=torch.float32, device=theta.device)
+    if n:
+        with torch.cuda.device(theta.device):
+            check(lib.pe_axis_angle_fwd(theta.data_ptr(), axis.data_ptr(), r.data_ptr(), n, _stream()),
+                  "pe_axis_angle_fwd")
+    return r
+
+
+@axis_angle_matrix.register_fake
+def _(theta, axis):
+    return axis.new_empty((theta.numel(), 3, 3))
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# 8f.2  CosyPose pose update                                       /root/reference/Iterative/utility.py:90-128
+def _poses(t: Tensor) -> Tensor:
+    if t.dtype != torch.float32:
+        raise TypeError("pe_b200 ops compute in float32")
+    if t.dim() != 3 or t.shape[1:] != (4, 4):
+        raise ValueError(f"expected (B, 4, 4) poses, got {tuple(t.shape)}")
+    return t.contiguous()
+
+
+@torch.library.custom_op(f"{NS}::pose_update", mutates_args=(), device_types="cuda")
+def pose_update(out: Tensor, t_init: Tensor, fx: float, fy: float) -> Tensor:
+    out, stride = _rec(out, 12)
+    ti = _poses(t_init)
+    n = out.shape[0]
+    if ti.shape[0] != n:
+        raise ValueError("batch mismatch")
+    tp = torch.empty((n, 4, 4), dtype=torch.float32, device=out.device)
+    if n:
+        with torch.cuda.device(out.device):
+            check(lib.pe_pose_update_fwd(out.data_ptr(), stride, ti.data_ptr(), fx, fy, tp.data_ptr(), n, _stream()),
+                  "pe_pose_update_fwd")
+    return tp
+
+
+@pose_update.register_fake
+def _(out, t_init, fx, fy):
+    return out.new_empty((out.shape[0], 4, 4))
+
+
+@torch.library.custom_op(f"{NS}::pose_update_bwd", mutates_args=(), device_types="cuda")
+def pose_update_bwd(out: Tensor, t_init: Tensor, g: Tensor, fx: float, fy: float) -> Tensor:
+    out, stride = _rec(out, 12)
+    ti, g = _poses(t_init), _poses(g)
+    n = out.shape[0]
+    d = torch.empty((n, 12), dtype=torch.float32, device=out.device)
+    if n:
+        with torch.cuda.device(out.device):
+            check(lib.pe_pose_update_bwd(out.data_ptr(), stride, ti.data_ptr(), g.data_ptr(), fx, fy, d.data_ptr(), n,
+                                         _stream()), "pe_pose_update_bwd")
+    return d
+
+
+@pose_update_bwd.register_fake
+def _(out, t_init, g, fx, fy):
+    return out.new_empty((out.shape[0], 12))
+
+
+def _pose_setup(ctx, inputs, output):
+    ctx.save_for_backward(inputs[0], inputs[1])
+    ctx.fx, ctx.fy = inputs[2], inputs[3]
+
+
+def _pose_backward(ctx, g):
+    out, ti = ctx.saved_tensors
+    return pose_update_bwd(out, ti, g, ctx.fx, ctx.fy), None, None, None
+
+
+pose_update.register_autograd(_pose_backward, setup_context=_pose_setup)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# 8f.2  ADD-L1 mesh losses                                         /root/reference/Iterative/loss.py:10-69
+@torch.library.custom_op(f"{NS}::add_l1", mutates_args=(), device_types="cuda")
+def add_l1(t_gt: Tensor, t_pred: Tensor, points: Tensor, disentangled: bool) -> tuple[Tensor, Tensor, Tensor]:
+    """-> (per-item loss (B,), sum of them (1,) float64, d item / d T_pred[:, :3, :4] as (B, 3, 4))."""
+    tg, tp, pts = _poses(t_gt), _poses(t_pred), _clouds(points)
+    b, npts = pts.shape[0], pts.shape[1]
+    if tg.shape[0] != b or tp.shape[0] != b:
+        raise ValueError("batch mismatch")
+    item = torch.empty((b,), dtype=torch.float32, device=pts.device)
+    s = torch.zeros((1,), dtype=torch.float64, device=pts.device)
+    grad = torch.empty((b, 3, 4), dtype=torch.float32, device=pts.device)
+    if b:
+        with torch.cuda.device(pts.device):
+            check(lib.pe_add_l1(tg.data_ptr(), tp.data_ptr(), pts.data_ptr(), b, npts, int(disentangled),
+                                item.data_ptr(), s.data_ptr(), grad.data_ptr(), _stream()), "pe_add_l1")
+    return item, s, grad
+
+
+@add_l1.register_fake
+def _(t_gt, t_pred, points, disentangled):
+    b = points.shape[0]
+    return points.new_empty((b,)), points.new_empty((1,), dtype=torch.float64), points.new_empty((b, 3, 4))
+
+
+def _addl1_setup(ctx, inputs, output):
+    ctx.save_for_backward(output[2])
+    ctx.mark_non_differentiable(output[2])
+
+
+def _addl1_backward(ctx, g_item, g_sum, _g_grad):
+    (seed,) = ctx.saved_tensors                      # (B, 3, 4)
+    b = seed.shape[0]
+    w = None                                         # per-item upstream weight, (B,)
+    if g_item is not None:
+        w = g_item.to(torch.float32)
+    if g_sum is not None:
+        gs = g_sum.to(torch.float32).reshape(1).expand(b)
+        w = gs if w is None else w + gs
+    if w is None:
+        return None, None, None, None
+    d = seed.new_zeros((b, 4, 4))
+    d[:, :3, :] = seed * w.reshape(b, 1, 1)          # B x 12 numbers: glue, not a pass over the vertices
+    return None, d, None, None
+
+
+add_l1.register_autograd(_addl1_backward, setup_context=_addl1_setup)

@@ -189,7 +189,11 @@ def svd_frobenius_loss_and_grad(x, R_true):
 def kabsch(P, Q):
     """Rotation and translation aligning cloud P onto Q: (B, N, 3) x2 -> ((B, 3, 3), (B, 3)), R p + t ~ q.
 
-    Not in the reference; the cloud pair is the (pc1, pc_out) of point_cloud/main.py:171-181."""
+    Not in the reference; the cloud pair is the (pc1, pc_out) of point_cloud/main.py:171-181.
+    Differentiable w.r.t. both clouds (poseestimation_b200.point_cloud.kabsch is the same function)."""
+    if torch.is_grad_enabled() and (P.requires_grad or Q.requires_grad):
+        r, t, _ = _ops.kabsch_ctx(P, Q)
+        return r, t
     return _ops.kabsch(P, Q)
 
 
