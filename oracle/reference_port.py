@@ -271,5 +271,77 @@ def sample_rotations_axis_angle(batch: int, generator: torch.Generator | None = 
     return compute_rotation_matrix_from_quaternion(q)                                         # :33-47 same rows
 
 
+def rotation_matrices_from_axis_angle(theta: torch.Tensor, axis: torch.Tensor) -> torch.Tensor:
+    """Deterministic part of point_cloud/prepare.py:21-49 for given theta (B,) and un-normalised axis (B, 3)."""
+    axis = axis / axis.norm(dim=1, keepdim=True).clamp_min(1e-8)                              # :26 (normalize_vector)
+    q = torch.cat((torch.cos(theta)[:, None], axis * torch.sin(theta)[:, None]), dim=1)       # :27-30
+    # :33-47 are the rows of the unit-quaternion matrix WITHOUT re-normalising q (|q| = 1 by construction)
+    w, x, y, z = q[:, 0], q[:, 1], q[:, 2], q[:, 3]
+    xx, yy, zz, xy, xz, yz, xw, yw, zw = x * x, y * y, z * z, x * y, x * z, y * z, x * w, y * w, z * w
+    row0 = torch.stack((1 - 2 * yy - 2 * zz, 2 * xy - 2 * zw, 2 * xz + 2 * yw), 1)
+    row1 = torch.stack((2 * xy + 2 * zw, 1 - 2 * xx - 2 * zz, 2 * yz - 2 * xw), 1)
+    row2 = torch.stack((2 * xz - 2 * yw, 2 * yz + 2 * xw, 1 - 2 * xx - 2 * yy), 1)
+    return torch.stack((row0, row1, row2), 1)
+
+
+def rotate_cloud(rmat: torch.Tensor, pc: torch.Tensor) -> torch.Tensor:
+    """pc2 = gt_rmat @ pc1 per point (point_cloud/main.py:173-181, without the (B*N, 3, 3) expansion)."""
+    return (rmat @ pc.transpose(1, 2)).transpose(1, 2)
+
+
+# --------------------------------------------------------------------------------------------------------------
+# 8f.2  iterative refiner: pose update and ADD-L1 losses           Iterative/utility.py:73-128, Iterative/loss.py:10-69
+
+
+def get_scene_parameters_iterative():
+    """Iterative/utility.py:73-88: (fx, fy)."""
+    sw, img_res, flen = 36, 320, 50
+    ppm = sw / img_res
+    fx = fy = flen / ppm
+    return fx, fy
+
+
+def calculate_T_pred(model_output: torch.Tensor, T_init: torch.Tensor) -> torch.Tensor:
+    """Iterative/utility.py:90-128.  ``combine`` (:63-71) reads undefined globals (``model_output``, ``R_new``) and
+    cannot run; its evident intent - ones((B,4,4)), rotation block, translation column, T[:, 3, :3] = 0 - is
+    restated inline."""
+    dR = symmetric_orthogonalization(model_output[:, :9])                       # :107
+    transl = model_output[:, 9:12]
+    vx, vy, vz = transl[:, 0], transl[:, 1], transl[:, 2]                       # :110
+    R_k = T_init[:, :3, :3].to(model_output.dtype)                              # :112, :124
+    fx, fy = get_scene_parameters_iterative()
+    z_k = T_init[:, 2, 3]
+    z_new = vz * z_k                                                            # :118
+    x_k, y_k = T_init[:, 0, 3], T_init[:, 1, 3]
+    x_new = (vx / fx + x_k / z_k) * z_new                                       # :122
+    y_new = (vy / fy + y_k / z_k) * z_new                                       # :123
+    R_new = torch.einsum('bij,bjk->bik', dR, R_k)                               # :125
+    top = torch.cat((R_new, torch.stack((x_new, y_new, z_new), 1)[:, :, None]), dim=2)
+    last = torch.zeros(model_output.shape[0], 1, 4, dtype=model_output.dtype)
+    last[:, 0, 3] = 1
+    return torch.cat((top, last), dim=1)
+
+
+def transform_pts(T: torch.Tensor, pts: torch.Tensor) -> torch.Tensor:
+    """Iterative/loss.py:51-69 for T of shape (B, 4, 4)."""
+    return (T[:, None, :3, :3] @ pts[..., None]).squeeze(-1) + T[:, None, :3, 3]
+
+
+def compute_ADD_L1_loss(TCO_gt, TCO_pred, points, use_batch_mean=True):
+    """Iterative/loss.py:10-28."""
+    dists = (transform_pts(TCO_gt, points) - transform_pts(TCO_pred, points)).abs().mean(dim=(-1, -2))
+    return dists.mean() if use_batch_mean else dists
+
+
+def compute_disentangled_ADD_L1_loss(T_CO_pred, T_CO_gt, points):
+    """Iterative/loss.py:31-48."""
+    rot, dep, tra = T_CO_gt.clone(), T_CO_gt.clone(), T_CO_gt.clone()
+    rot[:, :3, :3] = T_CO_pred[:, :3, :3]
+    tra[:, :2, 3] = T_CO_pred[:, :2, 3]
+    dep[:, 2, 3] = T_CO_pred[:, 2, 3]
+    return (compute_ADD_L1_loss(T_CO_gt, rot, points) + compute_ADD_L1_loss(T_CO_gt, tra, points)
+            + compute_ADD_L1_loss(T_CO_gt, dep, points))
+
+
 TRANSFORM_OUTPUT = {"SVD": (9, symmetric_orthogonalization), "6D": (6, compute_rotation_matrix_from_ortho6d),
                     "3D": (3, vec_3d_to_SO3)}                                # rotation_representation.py:323-324

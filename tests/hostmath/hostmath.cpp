@@ -21,6 +21,17 @@ void hm_ortho5d(const float* x, float* r, long n) { LOOP pe::ortho5d(x + 5 * i, 
 void hm_ortho5d_bwd(const float* x, const float* g, float* dx, long n) { LOOP pe::ortho5d_pullback(x + 5 * i, g + 9 * i, dx + 5 * i); }
 void hm_expmap(const float* x, float* r, long n) { LOOP pe::expmap(x + 3 * i, r + 9 * i); }
 void hm_expmap_bwd(const float* x, const float* g, float* dx, long n) { LOOP pe::expmap_pullback(x + 3 * i, g + 9 * i, dx + 3 * i); }
+// sampler map, Kabsch backward coefficients, CosyPose pose update (fx = fy = 4000/9, utility.py:73-88)
+void hm_axis_angle(const float* th, const float* ax, float* r, long n) { LOOP pe::axis_angle_matrix(th[i], ax + 3 * i, r + 9 * i); }
+void hm_kabsch_bwd_coeffs(const float* ctx, const float* r, const float* g, const float* inv_n, float* cq, float* cp, long n) {
+    LOOP pe::kabsch_bwd_coeffs(ctx + 15 * i, r + 9 * i, g + 12 * i, inv_n[i], cq + 12 * i, cp + 12 * i);
+}
+void hm_pose_update(const float* o, const float* ti, float* to, long n) {
+    LOOP pe::pose_update(o + 12 * i, ti + 16 * i, 9.0f / 4000.0f, 9.0f / 4000.0f, to + 16 * i);
+}
+void hm_pose_update_bwd(const float* o, const float* ti, const float* g, float* d, long n) {
+    LOOP pe::pose_update_pullback(o + 12 * i, ti + 16 * i, g + 16 * i, 9.0f / 4000.0f, 9.0f / 4000.0f, d + 12 * i);
+}
 // the two-matrices-per-thread (packed fp32x2) instantiation: record i rides with record i + n/2 (n even)
 void hm_svd_orth_x2(const float* m, float* r, float* d, long n) {
     long h = n / 2;

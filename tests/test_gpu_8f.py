@@ -1,0 +1,190 @@
+"""GPU parity for the SURVEY 8(f) rows: cloud-pair construction, differentiable Kabsch, CosyPose pose update, ADD-L1."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import reference_port as O
+
+pytestmark = pytest.mark.gpu
+
+T = lambda a: torch.from_numpy(np.asarray(a))
+
+
+@pytest.fixture(scope="module")
+def it():
+    import poseestimation_b200.iterative as m
+    return m
+
+
+@pytest.fixture(scope="module")
+def pc():
+    import poseestimation_b200.point_cloud as m
+    return m
+
+
+def _rel(a, b):
+    a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+    a, b = a.reshape(len(a), -1), b.reshape(len(b), -1)
+    return np.abs(a - b).max(1) / (np.abs(b).max(1) + 1e-30)
+
+
+# ---- 8f.4 cloud-pair construction ------------------------------------------------------------------------------------
+def test_sampler_map_matches_reference_golden(pc, golden):
+    z = golden("sampler")
+    m = pc.rotation_matrices_from_axis_angle(T(z["theta"]).cuda(), T(z["axis"]).cuda())
+    assert m.shape == (256, 3, 3) and m.dtype == torch.float32
+    assert np.abs(m.cpu().numpy() - z["matrix"]).max() <= 2e-6
+    r = pc.get_sampled_rotation_matrices_by_axisAngle(1000).cpu().double()
+    assert (r @ r.transpose(1, 2) - torch.eye(3, dtype=torch.float64)).abs().max() <= 1e-5
+    assert (torch.linalg.det(r) - 1).abs().max() <= 1e-5
+    # rotation angle is 2 * theta (the reference's quirk): uniform theta -> trace spread over [-1, 3]
+    tr = r.diagonal(dim1=1, dim2=2).sum(1)
+    assert tr.min() < -0.9 and tr.max() > 2.9
+
+
+def test_rotate_cloud_matches_reference_construction(pc, golden):
+    z = golden("kabsch_kat")                      # pc2 = bmm(expanded gt_rmat, pc1), point_cloud/main.py:173-181
+    out = pc.rotate_cloud(T(z["gt_rmat"]).cuda(), T(z["pc1"]).cuda())
+    assert np.abs(out.cpu().numpy() - z["pc2"]).max() <= 1e-6
+
+
+@pytest.mark.parametrize("b,n", [(1, 4), (3, 5), (7, 1024), (33, 1021), (2, 4096)])
+def test_affine_points_forward_backward(b, n):
+    from poseestimation_b200 import ops
+    torch.manual_seed(b * 1000 + n)
+    a, t, p, g = torch.randn(b, 3, 3), torch.randn(b, 3), torch.randn(b, n, 3), torch.randn(b, n, 3)
+    for transpose in (False, True):
+        ad, td, pd = (v.cuda().requires_grad_(True) for v in (a, t, p))
+        out = ops.affine_points(ad, td, pd, transpose)
+        out.backward(g.cuda())
+        a64, t64, p64 = (v.double().requires_grad_(True) for v in (a, t, p))
+        m = a64.transpose(1, 2) if transpose else a64
+        ref = p64 @ m.transpose(1, 2) + t64[:, None]
+        ref.backward(g.double())
+        assert np.abs(out.detach().cpu().numpy() - ref.detach().numpy()).max() <= 1e-5
+        assert _rel(pd.grad.cpu(), p64.grad).max() <= 1e-5
+        assert _rel(ad.grad.cpu(), a64.grad).max() <= 1e-4      # fp32 sums over n points
+        assert _rel(td.grad.cpu(), t64.grad).max() <= 1e-4
+
+
+def test_transform_pts_reads_the_pose_in_place(it, golden):
+    z = golden("iterative")
+    out = it.transform_pts(T(z["T_gt"]).cuda(), T(z["verts"]).cuda())
+    assert np.abs(out.cpu().numpy() - z["transform_pts"]).max() <= 1e-6
+
+
+# ---- 8f.3 differentiable Kabsch --------------------------------------------------------------------------------------
+@pytest.mark.parametrize("b,n,noise", [(64, 40, 0.05), (9, 1024, 0.01), (40, 257, 0.1)])
+def test_kabsch_backward_matches_oracle_autograd(pc, b, n, noise):
+    torch.manual_seed(n)
+    p = (torch.rand(b, n, 3) - 0.5).float()
+    rot = O.sample_rotations_axis_angle(b, torch.Generator().manual_seed(3)).float()
+    q = (p @ rot.transpose(1, 2) + noise * torch.randn(b, n, 3) + torch.randn(b, 1, 3)).float()
+    g_r, g_t = torch.randn(b, 3, 3), torch.randn(b, 3)
+    p64, q64 = p.double().requires_grad_(True), q.double().requires_grad_(True)
+    r64, t64 = O.kabsch(p64, q64)
+    ((r64 * g_r.double()).sum() + (t64 * g_t.double()).sum()).backward()
+    pd, qd = p.cuda().requires_grad_(True), q.cuda().requires_grad_(True)
+    r, t = pc.kabsch(pd, qd)
+    ((r * g_r.cuda()).sum() + (t * g_t.cuda()).sum()).backward()
+    assert np.abs(r.detach().cpu().numpy() - r64.detach().numpy()).max() <= 2e-5
+    assert np.abs(t.detach().cpu().numpy() - t64.detach().numpy()).max() <= 2e-5
+    # per cloud: gradient error relative to the largest gradient entry of that cloud
+    assert _rel(pd.grad.cpu(), p64.grad).max() <= 2e-4
+    assert _rel(qd.grad.cpu(), q64.grad).max() <= 2e-4
+    # only R used, only one cloud needs a gradient
+    pd2 = p.cuda().requires_grad_(True)
+    r2, _ = pc.kabsch(pd2, q.cuda())
+    (r2 * g_r.cuda()).sum().backward()
+    p64b = p.double().requires_grad_(True)
+    (O.kabsch(p64b, q.double())[0] * g_r.double()).sum().backward()
+    assert _rel(pd2.grad.cpu(), p64b.grad).max() <= 2e-4
+
+
+# ---- 8f.2 CosyPose pose update and ADD-L1 ----------------------------------------------------------------------------
+def test_pose_update_matches_reference_golden(it, golden):
+    z = golden("iterative")
+    n = len(z["out"])
+    wide = torch.zeros(n, 16)
+    wide[:, :12] = T(z["out"])                      # the network emits more columns than the update reads
+    for src in (T(z["out"]).cuda(), wide.cuda()):
+        o = src.requires_grad_(True)
+        tp = it.calculate_T_pred(o, T(z["T_init"]).cuda(), "cuda")
+        assert tp.shape == (n, 4, 4) and tp.dtype == torch.float32
+        assert np.abs(tp.detach().cpu().numpy() - z["T_pred_ref_fp32"]).max() <= 2e-5     # the reference, fp32
+        o64 = T(z["out"]).double().requires_grad_(True)
+        t64 = O.calculate_T_pred(o64, T(z["T_init"]).double())
+        assert np.abs(tp.detach().cpu().numpy() - t64.detach().numpy()).max() <= 1e-5
+        tp.backward(T(z["g_T"]).float().cuda())
+        (g64,) = torch.autograd.grad(t64, o64, T(z["g_T"]))
+        assert _rel(o.grad.cpu()[:, :12], g64).max() <= 1e-4
+        assert o.grad.shape == src.shape and (o.grad[:, 12:] == 0).all()
+    with pytest.raises(ValueError):
+        it.calculate_T_pred(T(z["out"]).cuda(), T(z["T_init"]).cuda(), "cuda", rot_repr="6D")
+
+
+def test_add_l1_losses_match_reference_golden(it, golden):
+    z = golden("iterative")
+    tg, v = T(z["T_gt"]).cuda(), T(z["verts"]).cuda()
+    tp = T(z["T_pred_ref_fp32"]).cuda().requires_grad_(True)
+    add = it.compute_ADD_L1_loss(tg, tp, v)
+    assert add.dim() == 0 and add.dtype == torch.float32
+    add.backward()
+    assert abs(add.item() - float(z["add_l1"])) <= 1e-6
+    assert np.abs(tp.grad.cpu().numpy() - z["add_l1_grad_pred"]).max() <= 1e-6
+    items = it.compute_ADD_L1_loss(tg, tp.detach(), v, use_batch_mean=False)
+    assert np.abs(items.cpu().numpy() - z["add_l1_items"]).max() <= 1e-6
+    tp2 = T(z["T_pred_ref_fp32"]).cuda().requires_grad_(True)
+    dis = it.compute_disentangled_ADD_L1_loss(tp2, tg, v)
+    dis.backward()
+    assert abs(dis.item() - float(z["disentangled"])) <= 1e-6
+    assert np.abs(tp2.grad.cpu().numpy() - z["disentangled_grad_pred"]).max() <= 1e-6
+    # per-item form with a non-uniform upstream gradient
+    tp3 = T(z["T_pred_ref_fp32"]).cuda().requires_grad_(True)
+    w = torch.randn(len(z["out"]))
+    (it.compute_ADD_L1_loss(tg, tp3, v, use_batch_mean=False) * w.cuda()).sum().backward()
+    a64 = T(z["T_pred_ref_fp32"]).double().requires_grad_(True)
+    (O.compute_ADD_L1_loss(T(z["T_gt"]).double(), a64, T(z["verts"]).double(), use_batch_mean=False) * w.double()).sum().backward()
+    assert np.abs(tp3.grad.cpu().numpy() - a64.grad.numpy()).max() <= 1e-5
+
+
+@pytest.mark.parametrize("b,n", [(1, 1), (5, 3), (19, 512), (8, 1500), (150, 2048 + 4), (3, 5000)])
+def test_add_l1_shapes_and_ragged_sizes(it, b, n):
+    torch.manual_seed(b + n)
+    def poses(k):
+        t = torch.zeros(k, 4, 4)
+        t[:, :3, :3] = O.symmetric_orthogonalization(torch.randn(k, 9).double()).float()
+        t[:, :3, 3] = torch.randn(k, 3)
+        t[:, 3, 3] = 1
+        return t
+    tg, tp, v = poses(b), poses(b), torch.randn(b, n, 3)
+    for fn_gpu, fn_ref in ((lambda a, c, d: it.compute_ADD_L1_loss(a, c, d), lambda a, c, d: O.compute_ADD_L1_loss(a, c, d)),
+                           (lambda a, c, d: it.compute_disentangled_ADD_L1_loss(c, a, d),
+                            lambda a, c, d: O.compute_disentangled_ADD_L1_loss(c, a, d))):
+        x = tp.cuda().requires_grad_(True)
+        loss = fn_gpu(tg.cuda(), x, v.cuda())
+        loss.backward()
+        x64 = tp.double().requires_grad_(True)
+        ref = fn_ref(tg.double(), x64, v.double())
+        ref.backward()
+        assert abs(loss.item() - ref.item()) <= 1e-5 * max(1.0, abs(ref.item()))
+        assert np.abs(x.grad.cpu().numpy() - x64.grad.numpy()).max() <= 1e-5 * max(1.0, x64.grad.abs().max().item())
+
+
+def test_refiner_step_end_to_end(it, golden):
+    """Iterative/main.py:85-94: network output -> calculate_T_pred -> disentangled ADD-L1 -> backward."""
+    z = golden("iterative")
+    o = T(z["out"]).cuda().requires_grad_(True)
+    loss = it.compute_disentangled_ADD_L1_loss(it.calculate_T_pred(o, T(z["T_init"]).cuda(), "cuda"),
+                                               T(z["T_gt"]).cuda(), T(z["verts"]).cuda())
+    loss.backward()
+    o64 = T(z["out"]).double().requires_grad_(True)
+    ref = O.compute_disentangled_ADD_L1_loss(O.calculate_T_pred(o64, T(z["T_init"]).double()), T(z["T_gt"]).double(),
+                                             T(z["verts"]).double())
+    ref.backward()
+    assert abs(loss.item() - ref.item()) <= 1e-5
+    # sign(.) flips of individual vertices between fp32 and float64 move the L1 gradient by O(1/N) per flip
+    assert _rel(o.grad.cpu(), o64.grad).max() <= 5e-3
+    ang = it.angle_error(it.calculate_T_pred(o.detach(), T(z["T_init"]).cuda(), "cuda")[:, :3, :3].contiguous(),
+                         T(z["T_gt"])[:, :3, :3].contiguous().cuda())
+    assert ang.dtype == torch.float64 and ang.shape == (len(z["out"]),)

@@ -148,3 +148,52 @@ def test_packed_two_lane_instantiation_matches_scalar(hm):
     assert np.isfinite(b2).all()
     scale = np.abs(b1).max(1)
     assert (np.abs(b1 - b2).max(1) / np.maximum(scale, 0.1 * np.median(scale))).max() <= 1e-5
+
+
+# ---- SURVEY 8(f) rows ------------------------------------------------------------------------------------------------
+def test_sampler_map_vs_golden(hm, golden):
+    z = golden("sampler")
+    r = hostmath.call(hm, "hm_axis_angle", z["theta"], z["axis"], (len(z["theta"]), 9))
+    assert np.abs(r.reshape(-1, 3, 3) - z["matrix"]).max() <= 2e-6
+
+
+def test_pose_update_and_pullback_vs_golden_and_oracle(hm, golden):
+    z = golden("iterative")
+    n = len(z["out"])
+    tp = hostmath.call(hm, "hm_pose_update", z["out"], z["T_init"].reshape(n, 16), (n, 16))
+    assert np.abs(tp.reshape(n, 4, 4) - z["T_pred_ref_fp32"]).max() <= 2e-5          # the reference itself, fp32
+    o = T(z["out"]).double().requires_grad_(True)
+    t64 = O.calculate_T_pred(o, T(z["T_init"]).double())
+    assert np.abs(tp.reshape(n, 4, 4) - t64.detach().numpy()).max() <= 1e-5
+    (g,) = torch.autograd.grad(t64, o, T(z["g_T"]))
+    d = hostmath.call(hm, "hm_pose_update_bwd", z["out"], z["T_init"].reshape(n, 16),
+                      z["g_T"].astype(np.float32).reshape(n, 16), (n, 12))
+    assert _rel(d, g.numpy()).max() <= 1e-4
+
+
+def test_kabsch_backward_coefficients_vs_oracle_autograd(hm):
+    """dL/dP, dL/dQ of L = sum(gR * R) + sum(gt * t) through the oracle's Kabsch (float64 autograd through torch.svd)
+    against the affine coefficients the kernel computes per pair."""
+    torch.manual_seed(11)
+    b, npts = 64, 40
+    p = (torch.rand(b, npts, 3) - 0.5).float()
+    rot = O.sample_rotations_axis_angle(b, torch.Generator().manual_seed(3)).float()
+    q = (p @ rot.transpose(1, 2) + 0.05 * torch.randn(b, npts, 3) + torch.randn(b, 1, 3)).float()
+    g_r, g_t = torch.randn(b, 3, 3).double(), torch.randn(b, 3).double()
+    p64, q64 = p.double().requires_grad_(True), q.double().requires_grad_(True)
+    r, t = O.kabsch(p64, q64)
+    dp_ref, dq_ref = torch.autograd.grad((r * g_r).sum() + (t * g_t).sum(), (p64, q64))
+    # context as the forward kernel leaves it: H = sum (q - qbar)(p - pbar)^T, pbar, qbar
+    pb, qb = p.double().mean(1), q.double().mean(1)
+    h = (q.double() - qb[:, None]).transpose(1, 2) @ (p.double() - pb[:, None])
+    ctx = torch.cat([h.reshape(b, 9), pb, qb], 1).float().numpy()
+    g = torch.cat([g_r.reshape(b, 9), g_t], 1).float().numpy()
+    inv_n = np.full((b, 1), 1.0 / npts, np.float32)
+    cq, cp = hostmath.call(hm, "hm_kabsch_bwd_coeffs", ctx, r.detach().float().numpy().reshape(b, 9), g, inv_n,
+                           (b, 12), (b, 12))
+    A_q, b_q = T(cq[:, :9]).double().reshape(b, 3, 3), T(cq[:, 9:]).double()
+    A_p, b_p = T(cp[:, :9]).double().reshape(b, 3, 3), T(cp[:, 9:]).double()
+    dq = p.double() @ A_q.transpose(1, 2) + b_q[:, None]
+    dp = q.double() @ A_p.transpose(1, 2) + b_p[:, None]
+    assert _rel(dq.numpy(), dq_ref.numpy()).max() <= 1e-4
+    assert _rel(dp.numpy(), dp_ref.numpy()).max() <= 1e-4

@@ -121,3 +121,42 @@ def test_sampler_gives_rotations():
     r = O.sample_rotations_axis_angle(64, g).numpy()
     assert np.abs(r @ r.transpose(0, 2, 1) - np.eye(3)).max() < 1e-12
     assert np.allclose(np.linalg.det(r), 1.0)
+
+
+# ---- iterative refiner and cloud-pair sampler (tests/golden/make_golden_8f.py) ---------------------
+def test_pose_update_matches_reference(golden):
+    z = golden("iterative")
+    tp = O.calculate_T_pred(T(z["out"]).double(), T(z["T_init"]).double())
+    # the reference can only run this function in float32 (R_k.float(), utility.py:124): compare at fp32 accuracy
+    assert np.abs(tp.numpy() - z["T_pred_ref_fp32"]).max() <= 2e-5
+    o = T(z["out"]).double().requires_grad_(True)
+    (g,) = torch.autograd.grad(O.calculate_T_pred(o, T(z["T_init"]).double()), o, T(z["g_T"]))
+    ref = z["d_out_ref_fp32"]
+    scale = np.abs(ref).max(axis=1, keepdims=True)
+    assert (np.abs(g.numpy() - ref) / scale).max() <= 2e-3       # torch's fp32 svd_backward is the noisy side here
+
+
+def test_add_l1_losses_match_reference(golden):
+    z = golden("iterative")
+    tg, tp, v = T(z["T_gt"]).double(), T(z["T_pred_ref_fp32"]).double(), T(z["verts"]).double()
+    assert np.abs(O.transform_pts(tg, v).numpy() - z["transform_pts"]).max() <= 1e-14
+    a = tp.clone().requires_grad_(True)
+    add = O.compute_ADD_L1_loss(tg, a, v)
+    (ga,) = torch.autograd.grad(add, a)
+    assert abs(add.item() - float(z["add_l1"])) <= 1e-14 and np.abs(ga.numpy() - z["add_l1_grad_pred"]).max() <= 1e-14
+    assert np.abs(O.compute_ADD_L1_loss(tg, tp, v, use_batch_mean=False).numpy() - z["add_l1_items"]).max() <= 1e-14
+    a = tp.clone().requires_grad_(True)
+    dis = O.compute_disentangled_ADD_L1_loss(a, tg, v)
+    (gd,) = torch.autograd.grad(dis, a)
+    assert abs(dis.item() - float(z["disentangled"])) <= 1e-14
+    assert np.abs(gd.numpy() - z["disentangled_grad_pred"]).max() <= 1e-14
+
+
+def test_sampler_map_matches_reference(golden):
+    z = golden("sampler")
+    m = O.rotation_matrices_from_axis_angle(T(z["theta"]).double(), T(z["axis"]).double())
+    assert np.abs(m.numpy() - z["matrix"]).max() <= 2e-6          # the reference evaluates this in float32
+    pc = torch.rand(8, 50, 3, dtype=torch.float64)
+    r = m[:8]
+    want = torch.bmm(r[:, None].expand(8, 50, 3, 3).reshape(-1, 3, 3), pc.reshape(-1, 3, 1)).view(8, 50, 3)
+    assert np.abs(O.rotate_cloud(r, pc).numpy() - want.numpy()).max() <= 1e-15   # point_cloud/main.py:173-181
