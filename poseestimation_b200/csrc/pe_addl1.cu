@@ -18,9 +18,9 @@
 
 namespace pe {
 
-constexpr int kAWarps = 8;
-constexpr int kAStages = 3;
-constexpr int kAChunk = 512;  // vertices per stage (6 KB)
+constexpr int kAWarps = 16;   // 12 B per vertex: twice the vertex rate of the Kabsch kernel for the same GB/s, so twice
+constexpr int kAStages = 3;   // the warps per SM (4 per scheduler) to cover the latency of the 13 accumulator chains
+constexpr int kAChunk = 256;  // vertices per stage (3 KB)
 constexpr int kAStageWords = kAChunk * 3;
 constexpr int kASmem = 1024 + kAWarps * kAStages * kAStageWords * 4;
 
@@ -42,7 +42,7 @@ __device__ __forceinline__ float wsum(float v) {
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
     return v;
 }
-__device__ __forceinline__ float sgn(float v) { return (float)((v > 0.f) - (v < 0.f)); }
+__device__ __forceinline__ float sgn(float v) { return v > 0.f ? 1.f : (v < 0.f ? -1.f : 0.f); }
 
 __global__ void __launch_bounds__(kAWarps * 32, 1) add_l1_kernel(const AddL1Params prm) {
     extern __shared__ __align__(128) unsigned char smem_raw[];

@@ -87,6 +87,35 @@ def main():
     rk, tk = torch.empty(b, 9, device=dev), torch.empty(b, 3, device=dev)
     add("kabsch_fwd (65536 x 1024)", 24 * npts + 48, lambda: check(lib.pe_kabsch_fwd(P(pc), P(qc), b, npts, P(rk), P(tk), st), ""),
         units=b, unit_name="pair")
+    # SURVEY 8(f) rows at the same cloud shape
+    ctx, cq, cp = torch.empty(b, 15, device=dev), torch.empty(b, 12, device=dev), torch.empty(b, 12, device=dev)
+    gk = torch.randn(b, 12, device=dev, generator=g)
+    oc = torch.empty(b, npts, 3, device=dev)
+    add("kabsch_fwd + context", 24 * npts + 108, lambda: check(lib.pe_kabsch_fwd_ctx(P(pc), P(qc), b, npts, P(rk), P(tk), P(ctx), st), ""),
+        units=b, unit_name="pair")
+    add("kabsch_bwd_coeffs (per pair)", 4 * (36 + 24), lambda: check(lib.pe_kabsch_bwd_coeffs(P(ctx), P(rk), P(gk), npts, P(cq), P(cp), b, st), ""),
+        units=b, unit_name="pair")
+    add("affine_points (rotate cloud / dQ / dP)", 24, lambda: check(lib.pe_affine_points(P(cq), 12, 3, 0, P(cq) + 36, 12, 1, P(pc), b, npts, P(oc), st), ""),
+        units=b * npts, unit_name="point")
+    add("cloud_outer_sum (dA, dt of affine)", 24 * npts + 48, lambda: check(lib.pe_cloud_outer_sum(P(qc), P(pc), b, npts, P(rk), P(tk), st), ""),
+        units=b, unit_name="pair")
+    tg = torch.eye(4, device=dev).repeat(b, 1, 1) + 0.1 * torch.randn(b, 4, 4, device=dev, generator=g)
+    tp = torch.eye(4, device=dev).repeat(b, 1, 1) + 0.1 * torch.randn(b, 4, 4, device=dev, generator=g)
+    item, gsd = torch.empty(b, device=dev), torch.empty(b, 12, device=dev)
+    for dis in (0, 1):
+        add(f"add_l1 loss + grad ({'disentangled' if dis else 'plain'})", 12 * npts + 128 + 52,
+            lambda dis=dis: check(lib.pe_add_l1(P(tg), P(tp), P(pc), b, npts, dis, P(item), P(sums), P(gsd), st), ""),
+            units=b, unit_name="item")
+    mo, tpo, dmo = torch.randn(n // 8, 12, device=dev, generator=g), torch.empty(n // 8, 16, device=dev), torch.empty(n // 8, 12, device=dev)
+    tin = (torch.eye(4, device=dev).repeat(n // 8, 1, 1) + 0.1 * torch.randn(n // 8, 4, 4, device=dev, generator=g)).contiguous()
+    gto = torch.randn(n // 8, 16, device=dev, generator=g)
+    add("pose_update_fwd", 4 * (12 + 16 + 16), lambda: check(lib.pe_pose_update_fwd(P(mo), 12, P(tin), 444.4, 444.4, P(tpo), n // 8, st), ""),
+        units=n // 8)
+    add("pose_update_bwd", 4 * (12 + 16 + 16 + 12), lambda: check(lib.pe_pose_update_bwd(P(mo), 12, P(tin), P(gto), 444.4, 444.4, P(dmo), n // 8, st), ""),
+        units=n // 8)
+    th1, ax3 = torch.randn(n, device=dev, generator=g), torch.randn(n, 3, device=dev, generator=g)
+    o9c = torch.empty(n, 9, device=dev)
+    add("axis_angle_fwd (sampler map)", 16 + 36, lambda: check(lib.pe_axis_angle_fwd(P(th1), P(ax3), P(o9c), n, st), ""))
     print(f"{'kernel':42s} {'B/unit':>7s} {'ms':>8s} {'GB/s':>8s} {'of peak':>8s}  (peak {peak} GB/s measured, n = {n})")
     for r in rows:
         print(f"{r['kernel']:42s} {r['bytes_per_unit']:7d} {r['ms']:8.4f} {r['GBps']:8.1f} {r['frac_of_measured_peak']:8.3f}")
