@@ -8,9 +8,12 @@ A *step* is one pass of the reference's training step over one resident batch (C
 UPNA/main.py:54-58):  loss = loss_frobenius(symmetric_orthogonalization(x), R_true);  loss.backward()
 as the two launches the public API makes for it through the C ABI: the single-pass step kernel (reads x, R_true;
 ONE decomposition per matrix; writes the loss sum and dL/dx for a unit upstream gradient: 108 B/matrix) and the
-backward's scaling pass by the upstream scalar (72 B/matrix) - plus, for N > 1, one NCCL all-reduce of the loss sum
-between them.  180 bytes per matrix.  The recompute pair (forward 72 B + backward 108 B, two decompositions) and the
-unfused svd_orth kernels are timed as well and reported under "also".
+backward's in-place scaling by the upstream scalar, which tests the scalar ON THE DEVICE and does nothing when it is
+exactly 1 - the case of `loss.backward()`, i.e. of every call site of the reference - plus, for N > 1, one NCCL
+all-reduce of the loss sum between them.  108 algorithmic bytes per matrix.  The step with an upstream gradient
+other than 1 (a 72 B/matrix scaling pass on top), the recompute pair (forward 72 B + backward 108 B, two
+decompositions: the 180 B definition of SURVEY 8d) and the unfused svd_orth kernels are timed as well and reported
+under "also".
 
   value        whole-job matrices/s with x, R_true resident in HBM (CUDA events, max over ranks)
   e2e          same step through the public API (rotation_representation.svd_frobenius_loss + autograd) with HOST
@@ -211,7 +214,10 @@ def run_native(args):
         check(lib.pe_svd_orth_frobenius_step(x.data_ptr(), 9, r_true.data_ptr(), inv_n_global, dx_unit.data_ptr(),
                                              loss_sum.data_ptr(), n, stream), "step")
 
-    def k_bwd():     # its backward: scale by the upstream scalar (read on the device)
+    def k_bwd():     # its backward under loss.backward(): upstream gradient 1, tested on the device -> no pass at all
+        check(lib.pe_scale_by_scalar_inplace(dx_unit.data_ptr(), gout.data_ptr(), 9 * n, stream), "scale")
+
+    def k_scale():   # the same backward when the upstream gradient is NOT 1 (e.g. a weighted sum of losses)
         check(lib.pe_scale_by_scalar(dx_unit.data_ptr(), gout.data_ptr(), dx.data_ptr(), 9 * n, stream), "scale")
 
     def k_fwd2():    # the recompute pair (single_pass=False)
@@ -290,10 +296,11 @@ def run_native(args):
             x.data_ptr(), 9, r_out.data_ptr(), g_up.data_ptr(), dx.data_ptr(), n, stream), "b"))
         also["svd_orth_bwd_recompute_ms"] = time_kernel(lambda: check(lib.pe_svd_orth_bwd(
             x.data_ptr(), 9, None, g_up.data_ptr(), dx.data_ptr(), n, stream), "b"))
-        also["step_kernel_ms"], also["scale_kernel_ms"] = fwd_ms, bwd_ms
+        also["step_kernel_ms"], also["backward_upstream_one_ms"] = fwd_ms, bwd_ms
+        also["backward_upstream_not_one_ms"] = time_kernel(k_scale)
+        also["matrices_per_s_upstream_not_one"] = n / ((fwd_ms + also["backward_upstream_not_one_ms"]) * 1e-3)
         also["recompute_fwd_ms"], also["recompute_bwd_ms"] = time_kernel(k_fwd2), time_kernel(k_bwd2)
         also["recompute_pair_matrices_per_s"] = n / ((also["recompute_fwd_ms"] + also["recompute_bwd_ms"]) * 1e-3)
-        also["loss_and_grad_only_matrices_per_s"] = n / (fwd_ms * 1e-3)
         also["loss"] = loss_value
 
     # ---- e2e: public API, host-resident inputs ---------------------------------------------------------------------
@@ -339,7 +346,8 @@ def run_native(args):
     roofline = {"bound": "hbm", "kernel": "stream_tma_kernel<SvdFrobStep> (pe_svd_orth_frobenius_step)",
                 "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": TRAFFIC_STEP * n / N_DEFAULT,
                 "peak_source": peak_src, "bytes_per_matrix": BYTES_STEP, "ms": fwd_ms,
-                "step_frac": (BYTES_STEP + BYTES_SCALE) * n / (ms_per_step * 1e-3) / 1e9 / peak}
+                "step_frac": BYTES_STEP * n / (ms_per_step * 1e-3) / 1e9 / peak,
+                "step_frac_vs_180B_two_pass_definition": (BYTES_FWD + BYTES_BWD) * n / (ms_per_step * 1e-3) / 1e9 / peak}
 
     cpu = None
     if not args.no_cpu_baseline:
@@ -353,7 +361,8 @@ def run_native(args):
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
         "config": {"workload": f"svd_orth+frobenius fwd+bwd, {n} random 3x3 fp32 matrices per GPU (BASELINE config 2)",
-                   "launches_per_step": "svd_orth_frobenius_step (108 B) + scale_by_scalar (72 B)",
+                   "launches_per_step": "svd_orth_frobenius_step (108 B: loss + gradient from one SVD) + "
+                                        "scale_by_scalar_inplace (upstream gradient 1: device-side no-op)",
                    "matrices_per_gpu": n, "l2": "inputs (2 x %.0f MB) larger than the 126 MB L2" % (n * 36 / 1e6),
                    "collective": "ncclAllReduce(3 x f64) per step" if world > 1 else "none"},
         "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,

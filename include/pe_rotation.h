@@ -111,6 +111,9 @@ int pe_svd_orth_frobenius_step(const float* m, int64_t m_stride, const float* r_
                                double* sum, int64_t n, void* stream);
 /* y[i] = x[i] * (*g) for nwords floats; g is a DEVICE scalar (no host sync); x, y 16-byte aligned, y may alias x. */
 int pe_scale_by_scalar(const float* x, const float* g, float* y, int64_t nwords, void* stream);
+/* x[i] *= (*g) in place; does nothing when *g == 1 (tested on the device, no host sync): the backward of the
+ * single-pass step under `loss.backward()`, whose upstream gradient is exactly 1 at every call site of the reference. */
+int pe_scale_by_scalar_inplace(float* x, const float* g, int64_t nwords, void* stream);
 
 /* ---- a9  Kabsch alignment - no reference function (site: point_cloud/main.py:171-181) --------------------------
  * p, q: (b, npts, 3) dense.  r[b][9] = the rotation minimising sum_k |R p_k + t - q_k|^2, i.e.

@@ -501,14 +501,34 @@ def _(x, g):
     return torch.empty_like(x)
 
 
+@torch.library.custom_op(f"{NS}::scale_by_scalar_", mutates_args=("x",), device_types="cuda")
+def scale_by_scalar_(x: Tensor, g: Tensor) -> None:
+    """x *= g in place for a one-element device tensor g; a no-op on the device when g == 1 (no host sync)."""
+    if x.dtype != torch.float32 or not x.is_contiguous():
+        raise TypeError("scale_by_scalar_ needs a contiguous float32 tensor")
+    g = g.to(torch.float32).reshape(1).contiguous()
+    if x.numel():
+        with torch.cuda.device(x.device):
+            check(lib.pe_scale_by_scalar_inplace(x.data_ptr(), g.data_ptr(), x.numel(), _stream()),
+                  "pe_scale_by_scalar_inplace")
+
+
 def _step_setup(ctx, inputs, output):
-    ctx.save_for_backward(output[1])
+    # the gradient for a unit upstream gradient is kept on the node (not via save_for_backward: the backward hands
+    # this very buffer to autograd, scaled in place, instead of writing a second (n, 9) tensor)
+    ctx.dx = output[1]
     ctx.mark_non_differentiable(output[1])
 
 
 def _step_backward(ctx, g_loss, _g_dx):
-    (dx,) = ctx.saved_tensors
-    return scale_by_scalar(dx, g_loss), None
+    dx = ctx.dx
+    if dx is None:
+        raise RuntimeError("svd_frobenius_loss: second backward through the single-pass step - its stored gradient "
+                           "was handed to autograd by the first one; call svd_frobenius_loss(..., single_pass=False) "
+                           "if the graph must be traversed more than once")
+    ctx.dx = None                       # sole owner from here on: AccumulateGrad can take the buffer without a copy
+    scale_by_scalar_(dx, g_loss)        # nothing to do on the device when the upstream gradient is exactly 1
+    return dx, None
 
 
 svd_orth_frobenius_step.register_autograd(_step_backward, setup_context=_step_setup)

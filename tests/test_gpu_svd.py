@@ -196,6 +196,38 @@ def test_single_pass_step_matches_two_pass_and_reference(rr, n):
     assert not rr.svd_frobenius_loss(x.cuda(), r_true.cuda()).requires_grad
 
 
+def test_single_pass_step_backward_details(rr, ops):
+    torch.manual_seed(5)
+    x = torch.randn(1000, 9, device="cuda")
+    rt = rr.symmetric_orthogonalization(torch.randn(1000, 9, device="cuda"))
+    # upstream gradient exactly 1 (loss.backward()): the stored gradient is handed over untouched
+    x1 = x.clone().requires_grad_(True)
+    rr.svd_frobenius_loss(x1, rt).backward()
+    _, g = rr.svd_frobenius_loss_and_grad(x, rt)
+    assert torch.equal(x1.grad, g)
+    # gradient accumulation over two steps adds up
+    rr.svd_frobenius_loss(x1, rt).backward()
+    assert torch.allclose(x1.grad, 2 * g, rtol=1e-6, atol=0)
+    # a second traversal of the same graph is refused loudly, and single_pass=False allows it
+    x2 = x.clone().requires_grad_(True)
+    loss = rr.svd_frobenius_loss(x2, rt)
+    loss.backward(retain_graph=True)
+    with pytest.raises(RuntimeError, match="second backward"):
+        loss.backward()
+    x3 = x.clone().requires_grad_(True)
+    loss = rr.svd_frobenius_loss(x3, rt, single_pass=False)
+    loss.backward(retain_graph=True)
+    loss.backward()
+    assert torch.allclose(x3.grad, 2 * g, rtol=1e-5, atol=1e-9)
+    # the in-place scaling op itself, ragged length
+    v = torch.randn(1003, device="cuda")
+    w = v.clone()
+    ops.scale_by_scalar_(w, torch.tensor(1.0, device="cuda"))
+    assert torch.equal(w, v)
+    ops.scale_by_scalar_(w, torch.tensor(-0.5, device="cuda"))
+    assert torch.equal(w, v * -0.5)
+
+
 def test_degenerate_inputs_are_finite_rotations(rr):
     cases = torch.tensor([
         [0.0] * 9, [1, 0, 0, 0, 1, 0, 0, 0, 1], [-1, 0, 0, 0, -1, 0, 0, 0, -1], [1, 0, 0, 0, 1, 0, 0, 0, -1],
