@@ -62,11 +62,15 @@ template <class T> struct LaneCount { static constexpr int value = 1; };
 template <> struct LaneCount<F2> { static constexpr int value = 2; };
 
 // ---- the Jacobi rotation, one (or two) matrices, columns as three separate rows ----------------------------------
-template <class T>
-PE_DEV void hestenes_t(T& p0, T& p1, T& p2, T& q0, T& q1, T& q2) {
+template <bool FRESH, class T>
+PE_DEV void hestenes_t(T& p0, T& p1, T& p2, T& q0, T& q1, T& q2, T& np, T& nq) {
     const T z = p0;  // overload selector
-    T al = t_fma(p2, p2, t_fma(p1, p1, t_mul(p0, p0)));
-    T be = t_fma(q2, q2, t_fma(q1, q1, t_mul(q0, q0)));
+    // squared norms: tracked from the previous rotations, or recomputed (see hestenes_a in pe_math.cuh)
+    T al = np, be = nq;
+    if constexpr (FRESH) {
+        al = t_fma(p2, p2, t_fma(p1, p1, t_mul(p0, p0)));
+        be = t_fma(q2, q2, t_fma(q1, q1, t_mul(q0, q0)));
+    }
     T ga = t_fma(p2, q2, t_fma(p1, q1, t_mul(p0, q0)));
     T dh = t_mul(t_set(z, 0.5f), t_sub(al, be));
     T ad = t_max(t_abs(dh), t_set(z, 1e-18f));
@@ -77,6 +81,8 @@ PE_DEV void hestenes_t(T& p0, T& p1, T& p2, T& q0, T& q1, T& q2) {
     T u = t_add(rho, ad);
     T k = t_rsq(t_fma(u, u, g2));
     T c = t_mul(u, k), s = t_mul(ga, k);
+    T mean = t_sub(al, dh);
+    np = t_add(mean, rho); nq = t_sub(mean, rho);
     auto neg = t_ltz(dh);
     T cp = t_sel(neg, s, c), sp = t_sel(neg, c, s), ns = t_neg(sp);
     T t;
@@ -101,16 +107,19 @@ PE_DEV void svd_orth_f(const Fetch& fetch, T* r, T& dsign) {
     T c00 = t_mul(a[0], sc), c01 = t_mul(a[1], sc), c02 = t_mul(a[2], sc), c10 = t_mul(a[3], sc),
       c11 = t_mul(a[4], sc), c12 = t_mul(a[5], sc), c20 = t_mul(a[6], sc), c21 = t_mul(a[7], sc),
       c22 = t_mul(a[8], sc);
-    hestenes_t(c00, c10, c20, c01, c11, c21);
-    hestenes_t(c00, c10, c20, c02, c12, c22);
-    hestenes_t(c01, c11, c21, c02, c12, c22);
-    hestenes_t(c00, c10, c20, c02, c12, c22);
-    hestenes_t(c00, c10, c20, c01, c11, c21);
-    hestenes_t(c01, c11, c21, c02, c12, c22);
-    hestenes_t(c00, c10, c20, c02, c12, c22);
-    hestenes_t(c00, c10, c20, c01, c11, c21);
-    hestenes_t(c00, c10, c20, c02, c12, c22);
-    hestenes_t(c01, c11, c21, c02, c12, c22);
+    T q0n = t_fma(c20, c20, t_fma(c10, c10, t_mul(c00, c00)));
+    T q1n = t_fma(c21, c21, t_fma(c11, c11, t_mul(c01, c01)));
+    T q2n = t_fma(c22, c22, t_fma(c12, c12, t_mul(c02, c02)));
+    hestenes_t<false>(c00, c10, c20, c01, c11, c21, q0n, q1n);
+    hestenes_t<false>(c00, c10, c20, c02, c12, c22, q0n, q2n);
+    hestenes_t<false>(c01, c11, c21, c02, c12, c22, q1n, q2n);
+    hestenes_t<false>(c00, c10, c20, c02, c12, c22, q0n, q2n);
+    hestenes_t<false>(c00, c10, c20, c01, c11, c21, q0n, q1n);
+    hestenes_t<false>(c01, c11, c21, c02, c12, c22, q1n, q2n);
+    hestenes_t<false>(c00, c10, c20, c02, c12, c22, q0n, q2n);
+    hestenes_t<(kFreshTail >= 3)>(c00, c10, c20, c01, c11, c21, q0n, q1n);
+    hestenes_t<(kFreshTail >= 2)>(c00, c10, c20, c02, c12, c22, q0n, q2n);
+    hestenes_t<(kFreshTail >= 1)>(c01, c11, c21, c02, c12, c22, q1n, q2n);
     T al0 = t_fma(c20, c20, t_fma(c10, c10, t_mul(c00, c00)));
     T al1 = t_fma(c21, c21, t_fma(c11, c11, t_mul(c01, c01)));
     T k0 = t_rsq(al0), k1 = t_rsq(al1);
@@ -177,8 +186,10 @@ PE_DEV void svd_orth_t(const T* m, T* r, T& dsign) {
 }
 
 // Pullback of R = svd_orth(M), lane-generic (formulas and guards: svd_orth_pullback in pe_math.cuh).
+// H = tr(P) I - P for P = sym(R^T M), scaled by the power-of-two prescale `sc`, and the solve y = H^-1 z, dM = R [y]_x.
+// Shared by the generic pullback and by the fused Frobenius step (whose z comes from R^T R_true directly).
 template <class T>
-PE_DEV void svd_orth_pullback_t(const T* m, const T* r, const T* g, T* dm) {
+PE_DEV void svd_orth_pullback_solve(const T* m, const T* r, T z0, T z1, T z2, T* dm) {
     const T z = m[0];
     const T sc = t_prescale(m);
     T n[9];
@@ -186,18 +197,10 @@ PE_DEV void svd_orth_pullback_t(const T* m, const T* r, const T* g, T* dm) {
     for (int i = 0; i < 3; ++i)
 #pragma unroll
         for (int j = 0; j < 3; ++j)
-            n[3 * i + j] = t_mul(sc, t_fma(r[6 + i], m[6 + j], t_fma(r[3 + i], m[3 + j], t_mul(r[i], m[j]))));
-    const T half = t_set(z, 0.5f);
-    T h01 = t_neg(t_mul(half, t_add(n[1], n[3]))), h02 = t_neg(t_mul(half, t_add(n[2], n[6]))),
-      h12 = t_neg(t_mul(half, t_add(n[5], n[7])));
-    T h00 = t_add(n[4], n[8]), h11 = t_add(n[0], n[8]), h22 = t_add(n[0], n[4]);
-    T t01 = t_fma(r[6], g[7], t_fma(r[3], g[4], t_mul(r[0], g[1])));
-    T t02 = t_fma(r[6], g[8], t_fma(r[3], g[5], t_mul(r[0], g[2])));
-    T t10 = t_fma(r[7], g[6], t_fma(r[4], g[3], t_mul(r[1], g[0])));
-    T t12 = t_fma(r[7], g[8], t_fma(r[4], g[5], t_mul(r[1], g[2])));
-    T t20 = t_fma(r[8], g[6], t_fma(r[5], g[3], t_mul(r[2], g[0])));
-    T t21 = t_fma(r[8], g[7], t_fma(r[5], g[4], t_mul(r[2], g[1])));
-    T z0 = t_sub(t21, t12), z1 = t_sub(t02, t20), z2 = t_sub(t10, t01);
+            n[3 * i + j] = t_fma(r[6 + i], m[6 + j], t_fma(r[3 + i], m[3 + j], t_mul(r[i], m[j])));
+    const T hs = t_mul(t_set(z, -0.5f), sc);
+    T h01 = t_mul(hs, t_add(n[1], n[3])), h02 = t_mul(hs, t_add(n[2], n[6])), h12 = t_mul(hs, t_add(n[5], n[7]));
+    T h00 = t_mul(sc, t_add(n[4], n[8])), h11 = t_mul(sc, t_add(n[0], n[8])), h22 = t_mul(sc, t_add(n[0], n[4]));
     T c00 = t_fma(h11, h22, t_neg(t_mul(h12, h12))), c01 = t_fma(h02, h12, t_neg(t_mul(h01, h22))),
       c02 = t_fma(h01, h12, t_neg(t_mul(h02, h11)));
     T c11 = t_fma(h00, h22, t_neg(t_mul(h02, h02))), c12 = t_fma(h01, h02, t_neg(t_mul(h00, h12))),
@@ -210,7 +213,7 @@ PE_DEV void svd_orth_pullback_t(const T* m, const T* r, const T* g, T* dm) {
 #pragma unroll
     for (int k = 0; k < LaneCount<T>::value; ++k) {
         float d = lane_get(det, k);
-        lane_put(inv, k, d > 1e-30f ? lane_get(sc, k) / d : 0.f);
+        lane_put(inv, k, d > 1e-30f ? lane_get(sc, k) * rcp_fast(d) : 0.f);
     }
     T y0 = t_mul(inv, t_fma(c00, z0, t_fma(c01, z1, t_mul(c02, z2))));
     T y1 = t_mul(inv, t_fma(c01, z0, t_fma(c11, z1, t_mul(c12, z2))));
@@ -223,6 +226,26 @@ PE_DEV void svd_orth_pullback_t(const T* m, const T* r, const T* g, T* dm) {
         dm[3 * i + 1] = t_fma(r2, y0, t_mul(r0, ny2));
         dm[3 * i + 2] = t_fma(r0, y1, t_mul(r1, ny0));
     }
+}
+
+// axial vector of T - T^T for T = R^T G (only the six off-diagonal entries of T are formed)
+template <class T>
+PE_DEV void skew_axial_rtg(const T* r, const T* g, T& z0, T& z1, T& z2) {
+    T t01 = t_fma(r[6], g[7], t_fma(r[3], g[4], t_mul(r[0], g[1])));
+    T t02 = t_fma(r[6], g[8], t_fma(r[3], g[5], t_mul(r[0], g[2])));
+    T t10 = t_fma(r[7], g[6], t_fma(r[4], g[3], t_mul(r[1], g[0])));
+    T t12 = t_fma(r[7], g[8], t_fma(r[4], g[5], t_mul(r[1], g[2])));
+    T t20 = t_fma(r[8], g[6], t_fma(r[5], g[3], t_mul(r[2], g[0])));
+    T t21 = t_fma(r[8], g[7], t_fma(r[5], g[4], t_mul(r[2], g[1])));
+    z0 = t_sub(t21, t12); z1 = t_sub(t02, t20); z2 = t_sub(t10, t01);
+}
+
+// Pullback of R = svd_orth(M), lane-generic (formulas and guards: svd_orth_pullback in pe_math.cuh).
+template <class T>
+PE_DEV void svd_orth_pullback_t(const T* m, const T* r, const T* g, T* dm) {
+    T z0, z1, z2;
+    skew_axial_rtg(r, g, z0, z1, z2);
+    svd_orth_pullback_solve(m, r, z0, z1, z2, dm);
 }
 
 // d = a - b and |d|_F^2, lane-generic

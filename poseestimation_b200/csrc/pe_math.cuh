@@ -34,6 +34,15 @@ PE_DEV float sqrt_fast(float x) {  // MUFU.SQRT, ~2^-22 relative error, flush-to
     return sqrtf(x);
 #endif
 }
+PE_DEV float rcp_fast(float x) {  // MUFU.RCP, ~1 ulp, flush-to-zero
+#ifdef __CUDA_ARCH__
+    float y;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+#else
+    return 1.0f / x;
+#endif
+}
 PE_DEV int f2i(float x) {
 #ifdef __CUDA_ARCH__
     return __float_as_int(x);
@@ -204,10 +213,16 @@ PE_DEV F2 f2_mul(F2 a, F2 b) {
     return F2{a.x * b.x, a.y * b.y};
 #endif
 }
-// one sorting Hestenes rotation of columns p, q held as (rows 0-1 packed, row 2 scalar)
-PE_DEV void hestenes_a(F2& p01, float& p2, F2& q01, float& q2) {
-    float al = fmaf(p2, p2, fmaf(p01.y, p01.y, p01.x * p01.x));
-    float be = fmaf(q2, q2, fmaf(q01.y, q01.y, q01.x * q01.x));
+// one sorting Hestenes rotation of columns p, q held as (rows 0-1 packed, row 2 scalar).
+// np, nq carry the squared column norms from rotation to rotation: the rotated pair's new norms are the eigenvalues
+// mean +- rho of its 2x2 Gram matrix, which the angle computation has already formed, so a TRACKED rotation needs one
+// dot product (3 FMA-pipe instructions) instead of three (9).  FRESH recomputes both norms from the columns; the last
+// kFreshTail rotations are fresh, so rounding drift of the tracked values cannot reach the result.
+constexpr int kFreshTail = 1;
+template <bool FRESH>
+PE_DEV void hestenes_a(F2& p01, float& p2, F2& q01, float& q2, float& np, float& nq) {
+    float al = FRESH ? fmaf(p2, p2, fmaf(p01.y, p01.y, p01.x * p01.x)) : np;
+    float be = FRESH ? fmaf(q2, q2, fmaf(q01.y, q01.y, q01.x * q01.x)) : nq;
     float ga = fmaf(p2, q2, fmaf(p01.y, q01.y, p01.x * q01.x));
     float dh = 0.5f * (al - be);
     float ad = fmaxf(fabsf(dh), 1e-18f);
@@ -217,6 +232,8 @@ PE_DEV void hestenes_a(F2& p01, float& p2, F2& q01, float& q2) {
     float u = rho + ad;
     float k = rsqrt_fast(fmaf(u, u, g2));
     float c = u * k, s = ga * k;
+    float mean = al - dh;
+    np = mean + rho; nq = mean - rho;
     bool neg = dh < 0.0f;
     float cp = neg ? s : c, sp = neg ? c : s;
     F2 C{cp, cp}, S{sp, sp}, N{-sp, -sp};
@@ -242,16 +259,19 @@ PE_DEV void svd_orth_fast(const float* m, float* r, float& dsign) {
     // column j: rows 0,1 packed, row 2 scalar
     F2 c0{m[0] * sc, m[3] * sc}, c1{m[1] * sc, m[4] * sc}, c2{m[2] * sc, m[5] * sc};
     float z0 = m[6] * sc, z1 = m[7] * sc, z2 = m[8] * sc;
-    hestenes_a(c0, z0, c1, z1);
-    hestenes_a(c0, z0, c2, z2);
-    hestenes_a(c1, z1, c2, z2);
-    hestenes_a(c0, z0, c2, z2);
-    hestenes_a(c0, z0, c1, z1);
-    hestenes_a(c1, z1, c2, z2);
-    hestenes_a(c0, z0, c2, z2);
-    hestenes_a(c0, z0, c1, z1);
-    hestenes_a(c0, z0, c2, z2);
-    hestenes_a(c1, z1, c2, z2);
+    float q0n = fmaf(z0, z0, fmaf(c0.y, c0.y, c0.x * c0.x));
+    float q1n = fmaf(z1, z1, fmaf(c1.y, c1.y, c1.x * c1.x));
+    float q2n = fmaf(z2, z2, fmaf(c2.y, c2.y, c2.x * c2.x));
+    hestenes_a<false>(c0, z0, c1, z1, q0n, q1n);
+    hestenes_a<false>(c0, z0, c2, z2, q0n, q2n);
+    hestenes_a<false>(c1, z1, c2, z2, q1n, q2n);
+    hestenes_a<false>(c0, z0, c2, z2, q0n, q2n);
+    hestenes_a<false>(c0, z0, c1, z1, q0n, q1n);
+    hestenes_a<false>(c1, z1, c2, z2, q1n, q2n);
+    hestenes_a<false>(c0, z0, c2, z2, q0n, q2n);
+    hestenes_a<(kFreshTail >= 3)>(c0, z0, c1, z1, q0n, q1n);
+    hestenes_a<(kFreshTail >= 2)>(c0, z0, c2, z2, q0n, q2n);
+    hestenes_a<(kFreshTail >= 1)>(c1, z1, c2, z2, q1n, q2n);
     float al0 = fmaf(z0, z0, fmaf(c0.y, c0.y, c0.x * c0.x));
     float al1 = fmaf(z1, z1, fmaf(c1.y, c1.y, c1.x * c1.x));
     float k0 = rsqrt_fast(al0), k1 = rsqrt_fast(al1);
@@ -314,16 +334,16 @@ PE_DEV void svd_orth_fast(const float* m, float* r, float& dsign) {
 constexpr float kDetFloor = 1e-7f;
 PE_DEV void svd_orth_pullback(const float* m, const float* r, const float* g, float* dm) {
     const float sc = pow2_prescale(m);
-    // N = R^T (sc*M)
+    // N = R^T M (unscaled); the power-of-two scale goes onto the six entries of H instead of the nine of N
     float n[9];
 #pragma unroll
     for (int i = 0; i < 3; ++i)
 #pragma unroll
         for (int j = 0; j < 3; ++j)
-            n[3 * i + j] = sc * fmaf(r[6 + i], m[6 + j], fmaf(r[3 + i], m[3 + j], r[i] * m[j]));
-    float p01 = 0.5f * (n[1] + n[3]), p02 = 0.5f * (n[2] + n[6]), p12 = 0.5f * (n[5] + n[7]);
-    float h00 = n[4] + n[8], h11 = n[0] + n[8], h22 = n[0] + n[4];
-    float h01 = -p01, h02 = -p02, h12 = -p12;
+            n[3 * i + j] = fmaf(r[6 + i], m[6 + j], fmaf(r[3 + i], m[3 + j], r[i] * m[j]));
+    const float hs = -0.5f * sc;
+    float h01 = hs * (n[1] + n[3]), h02 = hs * (n[2] + n[6]), h12 = hs * (n[5] + n[7]);
+    float h00 = sc * (n[4] + n[8]), h11 = sc * (n[0] + n[8]), h22 = sc * (n[0] + n[4]);
     // T = R^T G ; z = axial(T - T^T)
     float t01 = fmaf(r[6], g[7], fmaf(r[3], g[4], r[0] * g[1]));
     float t02 = fmaf(r[6], g[8], fmaf(r[3], g[5], r[0] * g[2]));
@@ -339,7 +359,7 @@ PE_DEV void svd_orth_pullback(const float* m, const float* r, const float* g, fl
     float tr3 = (h00 + h11 + h22) * (1.0f / 3.0f);
     float fl = kDetFloor * fabsf(tr3 * tr3 * tr3);
     det = fmaxf(det, fl);
-    float inv = det > 1e-30f ? sc / det : 0.f;  // det = 0 only for the zero matrix: define its gradient as 0
+    float inv = det > 1e-30f ? sc * rcp_fast(det) : 0.f;  // det = 0 only for the zero matrix: define its gradient as 0
     float y0 = inv * fmaf(c00, z0, fmaf(c01, z1, c02 * z2));
     float y1 = inv * fmaf(c01, z0, fmaf(c11, z1, c12 * z2));
     float y2 = inv * fmaf(c02, z0, fmaf(c12, z1, c22 * z2));

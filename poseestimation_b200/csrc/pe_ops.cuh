@@ -207,6 +207,27 @@ struct AngleFwd {
 };
 
 // ---- fused: loss_frobenius(symmetric_orthogonalization(x), R_true) ------------------------------------------------
+// Seed of the pullback for G = gs (R - R_t)/|R - R_t|_F without forming G:  R^T G = k (R^T R - R^T R_t) and R^T R is
+// symmetric, so axial(R^T G - G^T R) = -k axial(S - S^T) with S = R^T R_t.  f = |R - R_t|_F, k = gs / f (0 if f = 0).
+template <class T>
+__device__ __forceinline__ void frob_seed(const T* r, const T* rt, float gs, T& f, T& z0, T& z1, T& z2) {
+    T d = t_sub(r[0], rt[0]);
+    T s = t_mul(d, d);
+#pragma unroll
+    for (int i = 1; i < 9; ++i) { d = t_sub(r[i], rt[i]); s = t_fma(d, d, s); }
+    T nk = s;
+    f = s;
+#pragma unroll
+    for (int l = 0; l < LaneCount<T>::value; ++l) {
+        float sl = lane_get(s, l);
+        float inv = sl > 0.f ? rsqrt_nr(sl) : 0.f;
+        lane_put(nk, l, -gs * inv);
+        lane_put(f, l, sl * inv);
+    }
+    skew_axial_rtg(r, rt, z0, z1, z2);
+    z0 = t_mul(z0, nk); z1 = t_mul(z1, nk); z2 = t_mul(z2, nk);
+}
+
 template <bool WRITE_R>
 struct SvdFrobFwd {
     PE_OP_COMMON2("svd_orth_frobenius_fwd", 9, 9, 0, WRITE_R ? 9 : 0, 0, 1, false, 3)
@@ -238,20 +259,14 @@ struct SvdFrobBwd {
     using Extra = GradScale;
     template <class T, class S0, class S1>
     __device__ static __forceinline__ void body(const S0& ms, const S1& rts, T* dm, float gs) {
-        T r[9], g[9], m[9], ds;
+        T r[9], m[9], ds;
         svd_from<T>(ms, r, ds);
-        rts.load(m);  // R_true, reusing the registers that will hold M next
-        T s = diff9_sq(r, m, g);
-        T k = s;
-#pragma unroll
-        for (int l = 0; l < LaneCount<T>::value; ++l) {
-            float sl = lane_get(s, l);
-            lane_put(k, l, sl > 0.f ? gs * rsqrt_nr(sl) : 0.f);
-        }
-#pragma unroll
-        for (int i = 0; i < 9; ++i) g[i] = t_mul(g[i], k);
+        rts.load(m);  // R_true, in the registers that will hold M next
+        T f;
+        T z0, z1, z2;
+        frob_seed(r, m, gs, f, z0, z1, z2);
         ms.load(m);
-        svd_orth_pullback_t(m, r, g, dm);
+        svd_orth_pullback_solve(m, r, z0, z1, z2, dm);
     }
     __device__ static __forceinline__ void run(const float* m, const float* rt, const float*, float* dm, float*,
                                                double*, int&, const Extra& ex) {
@@ -313,22 +328,14 @@ struct SvdFrobStep {
     using Extra = StepScale;
     template <class T, class S0, class S1>
     __device__ static __forceinline__ T body(const S0& ms, const S1& rts, T* dm, float gs) {
-        T r[9], g[9], m[9], ds;
+        T r[9], m[9], ds;
         svd_from<T>(ms, r, ds);
         rts.load(m);
-        T s = diff9_sq(r, m, g);
-        T k = s, f = s;
-#pragma unroll
-        for (int l = 0; l < LaneCount<T>::value; ++l) {
-            float sl = lane_get(s, l);
-            float inv = sl > 0.f ? rsqrt_nr(sl) : 0.f;
-            lane_put(k, l, gs * inv);
-            lane_put(f, l, sl * inv);  // |R - R_true|_F
-        }
-#pragma unroll
-        for (int i = 0; i < 9; ++i) g[i] = t_mul(g[i], k);
+        T f;
+        T z0, z1, z2;
+        frob_seed(r, m, gs, f, z0, z1, z2);
         ms.load(m);
-        svd_orth_pullback_t(m, r, g, dm);
+        svd_orth_pullback_solve(m, r, z0, z1, z2, dm);
         return f;
     }
     __device__ static __forceinline__ void run(const float* m, const float* rt, const float*, float* dm, float*,
