@@ -18,8 +18,8 @@
 
 namespace pe {
 
-constexpr int kAWarps = 16;   // 12 B per vertex: twice the vertex rate of the Kabsch kernel for the same GB/s, so twice
-constexpr int kAStages = 3;   // the warps per SM (4 per scheduler) to cover the latency of the 13 accumulator chains
+constexpr int kAWarps = 32;   // 12 B per vertex: twice the vertex rate of the Kabsch kernel for the same GB/s; the kernel
+constexpr int kAStages = 2;   // is latency-bound on its 13 accumulator chains, so it runs the full 32 warps per SM
 constexpr int kAChunk = 256;  // vertices per stage (3 KB)
 constexpr int kAStageWords = kAChunk * 3;
 constexpr int kASmem = 1024 + kAWarps * kAStages * kAStageWords * 4;
@@ -44,6 +44,7 @@ __device__ __forceinline__ float wsum(float v) {
 }
 __device__ __forceinline__ float sgn(float v) { return v > 0.f ? 1.f : (v < 0.f ? -1.f : 0.f); }
 
+template <bool TMA>
 __global__ void __launch_bounds__(kAWarps * 32, 1) add_l1_kernel(const AddL1Params prm) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -56,16 +57,9 @@ __global__ void __launch_bounds__(kAWarps * 32, 1) add_l1_kernel(const AddL1Para
     const int cpi = (npts + kAChunk - 1) / kAChunk;  // chunks per item
     const long long my_items = gw < prm.b ? (prm.b - gw + nwarps - 1) / nwarps : 0;
     const long long steps = my_items * cpi;
-    const bool tma = prm.use_tma != 0;
     uint64_t policy = 0;
 
-    if (lane == 0) {
-        policy = l2_evict_first_policy();
-        for (int s = 0; s < kAStages; ++s) mbar_init(&bars[s], 1);
-        mbar_init_fence();
-    }
-    __syncwarp();
-    auto issue = [&](int s, long long j) {
+    auto issue = [&](int s, long long j) {  // lane 0: chunk (j % cpi) of this warp's item number (j / cpi)
         long long it = gw + (j / cpi) * nwarps;
         int ch = (int)(j % cpi);
         int cnt = min(kAChunk, npts - ch * kAChunk);
@@ -73,25 +67,23 @@ __global__ void __launch_bounds__(kAWarps * 32, 1) add_l1_kernel(const AddL1Para
         mbar_arrive_expect_tx(&bars[s], bytes);
         bulk_g2s(ring + s * kAStageWords, prm.pts + (it * npts + (long long)ch * kAChunk) * 3, bytes, &bars[s], policy);
     };
-    if (tma && lane == 0)
-        for (int s = 0; s < kAStages; ++s)
-            if (s < steps) issue(s, s);
+    if constexpr (TMA) {
+        if (lane == 0) {
+            policy = l2_evict_first_policy();
+            for (int s = 0; s < kAStages; ++s) mbar_init(&bars[s], 1);
+            mbar_init_fence();
+            for (int s = 0; s < kAStages; ++s)
+                if (s < steps) issue(s, s);
+        }
+        __syncwarp();
+    }
 
-    float d[9], dt[3];          // R_gt - R_pred, t_gt - t_pred (zero in the rotation term of the disentangled loss)
-    float tdelta[3] = {0, 0, 0};  // t_gt - t_pred
-    float acc = 0.f, S[9], sv[3];
-#pragma unroll
-    for (int i = 0; i < 9; ++i) { S[i] = 0.f; d[i] = 0.f; }
-    sv[0] = sv[1] = sv[2] = dt[0] = dt[1] = dt[2] = 0.f;
     double warp_total = 0.0;  // lane 0 only
-
-    for (long long j = 0; j < steps; ++j) {
-        const int s = (int)(j % kAStages);
-        const uint32_t parity = (uint32_t)((j / kAStages) & 1);
-        const long long it = gw + (j / cpi) * nwarps;
-        const int ch = (int)(j % cpi);
-        const int cnt = min(kAChunk, npts - ch * kAChunk);
-        if (ch == 0) {
+    long long j = 0;          // running chunk counter of this warp (ring position)
+    for (long long it = gw; it < prm.b; it += nwarps) {
+        // R_gt - R_pred and t_gt - t_pred (the latter is dropped from the vertex term of the disentangled loss)
+        float d[9], dt[3], tdelta[3];
+        {
             const float* a = prm.t_gt + it * 16;
             const float* c = prm.t_pred + it * 16;
 #pragma unroll
@@ -102,60 +94,65 @@ __global__ void __launch_bounds__(kAWarps * 32, 1) add_l1_kernel(const AddL1Para
                 dt[i] = prm.disentangled ? 0.f : tdelta[i];
             }
         }
-        const float* sp;
-        if (tma) {
-            mbar_wait(&bars[s], parity);
-            sp = ring + s * kAStageWords;
-        } else {
-            sp = prm.pts + (it * npts + (long long)ch * kAChunk) * 3;
-        }
+        float acc = 0.f, S[9], sv[3];
+#pragma unroll
+        for (int i = 0; i < 9; ++i) S[i] = 0.f;
+        sv[0] = sv[1] = sv[2] = 0.f;
+
+        for (int ch = 0; ch < cpi; ++ch, ++j) {
+            const int s = (int)(j % kAStages);
+            const int cnt = min(kAChunk, npts - ch * kAChunk);
+            const float* sp;
+            if constexpr (TMA) {
+                mbar_wait(&bars[s], (uint32_t)((j / kAStages) & 1));
+                sp = ring + s * kAStageWords;
+            } else {
+                sp = prm.pts + (it * npts + (long long)ch * kAChunk) * 3;
+            }
 #pragma unroll 4
-        for (int k = lane; k < cnt; k += 32) {
-            float x = sp[3 * k], y = sp[3 * k + 1], z = sp[3 * k + 2];
-            float e0 = fmaf(d[2], z, fmaf(d[1], y, fmaf(d[0], x, dt[0])));
-            float e1 = fmaf(d[5], z, fmaf(d[4], y, fmaf(d[3], x, dt[1])));
-            float e2 = fmaf(d[8], z, fmaf(d[7], y, fmaf(d[6], x, dt[2])));
-            acc += fabsf(e0) + fabsf(e1) + fabsf(e2);
-            float g0 = sgn(e0), g1 = sgn(e1), g2 = sgn(e2);
-            S[0] = fmaf(g0, x, S[0]); S[1] = fmaf(g0, y, S[1]); S[2] = fmaf(g0, z, S[2]);
-            S[3] = fmaf(g1, x, S[3]); S[4] = fmaf(g1, y, S[4]); S[5] = fmaf(g1, z, S[5]);
-            S[6] = fmaf(g2, x, S[6]); S[7] = fmaf(g2, y, S[7]); S[8] = fmaf(g2, z, S[8]);
-            sv[0] += g0; sv[1] += g1; sv[2] += g2;
+            for (int k = lane; k < cnt; k += 32) {
+                float x = sp[3 * k], y = sp[3 * k + 1], z = sp[3 * k + 2];
+                float e0 = fmaf(d[2], z, fmaf(d[1], y, fmaf(d[0], x, dt[0])));
+                float e1 = fmaf(d[5], z, fmaf(d[4], y, fmaf(d[3], x, dt[1])));
+                float e2 = fmaf(d[8], z, fmaf(d[7], y, fmaf(d[6], x, dt[2])));
+                acc += fabsf(e0) + fabsf(e1) + fabsf(e2);
+                float g0 = sgn(e0), g1 = sgn(e1), g2 = sgn(e2);
+                S[0] = fmaf(g0, x, S[0]); S[1] = fmaf(g0, y, S[1]); S[2] = fmaf(g0, z, S[2]);
+                S[3] = fmaf(g1, x, S[3]); S[4] = fmaf(g1, y, S[4]); S[5] = fmaf(g1, z, S[5]);
+                S[6] = fmaf(g2, x, S[6]); S[7] = fmaf(g2, y, S[7]); S[8] = fmaf(g2, z, S[8]);
+                sv[0] += g0; sv[1] += g1; sv[2] += g2;
+            }
+            if constexpr (TMA) {
+                __syncwarp();
+                if (lane == 0 && j + kAStages < steps) issue(s, j + kAStages);
+            }
         }
         __syncwarp();
-        if (tma && lane == 0 && j + kAStages < steps) issue(s, j + kAStages);
-
-        if (ch == cpi - 1) {
-            acc = wsum(acc);
+        acc = wsum(acc);
 #pragma unroll
-            for (int i = 0; i < 9; ++i) S[i] = wsum(S[i]);
-            sv[0] = wsum(sv[0]); sv[1] = wsum(sv[1]); sv[2] = wsum(sv[2]);
-            if (lane == 0) {
-                const float k3n = 1.0f / (3.0f * (float)npts);
-                float loss = acc * k3n;
-                float gt3[3] = {-sv[0] * k3n, -sv[1] * k3n, -sv[2] * k3n};
-                if (prm.disentangled) {
-                    // transl pose: (x, y) of T_pred, depth pose: z of T_pred - constant per-vertex distances
-                    loss += (fabsf(tdelta[0]) + fabsf(tdelta[1]) + fabsf(tdelta[2])) * (1.0f / 3.0f);
-                    gt3[0] = -sgn(tdelta[0]) * (1.0f / 3.0f);
-                    gt3[1] = -sgn(tdelta[1]) * (1.0f / 3.0f);
-                    gt3[2] = -sgn(tdelta[2]) * (1.0f / 3.0f);
-                }
-                if (prm.item) prm.item[it] = loss;
-                warp_total += (double)loss;
-                if (prm.grad) {
-                    float* gd = prm.grad + it * 12;
+        for (int i = 0; i < 9; ++i) S[i] = wsum(S[i]);
+        sv[0] = wsum(sv[0]); sv[1] = wsum(sv[1]); sv[2] = wsum(sv[2]);
+        if (lane == 0) {
+            const float k3n = 1.0f / (3.0f * (float)npts);
+            float loss = acc * k3n;
+            float gt3[3] = {-sv[0] * k3n, -sv[1] * k3n, -sv[2] * k3n};
+            if (prm.disentangled) {
+                // transl pose: (x, y) of T_pred, depth pose: z of T_pred - constant per-vertex distances
+                loss += (fabsf(tdelta[0]) + fabsf(tdelta[1]) + fabsf(tdelta[2])) * (1.0f / 3.0f);
+                gt3[0] = -sgn(tdelta[0]) * (1.0f / 3.0f);
+                gt3[1] = -sgn(tdelta[1]) * (1.0f / 3.0f);
+                gt3[2] = -sgn(tdelta[2]) * (1.0f / 3.0f);
+            }
+            if (prm.item) prm.item[it] = loss;
+            warp_total += (double)loss;
+            if (prm.grad) {
+                float* gd = prm.grad + it * 12;
 #pragma unroll
-                    for (int i = 0; i < 3; ++i) {
-                        gd[4 * i] = -S[3 * i] * k3n; gd[4 * i + 1] = -S[3 * i + 1] * k3n; gd[4 * i + 2] = -S[3 * i + 2] * k3n;
-                        gd[4 * i + 3] = gt3[i];
-                    }
+                for (int i = 0; i < 3; ++i) {
+                    gd[4 * i] = -S[3 * i] * k3n; gd[4 * i + 1] = -S[3 * i + 1] * k3n; gd[4 * i + 2] = -S[3 * i + 2] * k3n;
+                    gd[4 * i + 3] = gt3[i];
                 }
             }
-            acc = 0.f;
-#pragma unroll
-            for (int i = 0; i < 9; ++i) S[i] = 0.f;
-            sv[0] = sv[1] = sv[2] = 0.f;
         }
     }
     if (prm.sum && lane == 0 && my_items > 0) atomicAdd(prm.sum, warp_total);
@@ -186,7 +183,7 @@ extern "C" int pe_add_l1(const float* t_gt, const float* t_pred, const float* pt
         e = cudaGetDeviceProperties(&prop, dev);
         if (e != cudaSuccess) return fail_cuda(e, "cudaGetDeviceProperties");
         if (prop.major < 10) return fail(PE_ERR_NO_DEVICE, "this library is built for sm_100a (B200) only");
-        e = cudaFuncSetAttribute(add_l1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kASmem);
+        e = cudaFuncSetAttribute(add_l1_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kASmem);
         if (e != cudaSuccess) return fail_cuda(e, "cudaFuncSetAttribute(smem)");
         sms[dev] = prop.multiProcessorCount;
     }
@@ -194,7 +191,8 @@ extern "C" int pe_add_l1(const float* t_gt, const float* t_pred, const float* pt
     prm.use_tma = (npts % 4 == 0) && (reinterpret_cast<uintptr_t>(pts) & 15u) == 0 && !force_direct();
     long long grid = (b + kAWarps - 1) / kAWarps;
     if (grid > sms[dev]) grid = sms[dev];
-    add_l1_kernel<<<(unsigned)grid, kAWarps * 32, kASmem, st>>>(prm);
+    if (prm.use_tma) add_l1_kernel<true><<<(unsigned)grid, kAWarps * 32, kASmem, st>>>(prm);
+    else add_l1_kernel<false><<<(unsigned)grid, kAWarps * 32, 0, st>>>(prm);
     e = cudaGetLastError();
     if (e != cudaSuccess) return fail_cuda(e, "add_l1_kernel");
     count_launch();
