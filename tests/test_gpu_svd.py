@@ -228,6 +228,33 @@ def test_single_pass_step_backward_details(rr, ops):
     assert torch.equal(w, v * -0.5)
 
 
+@pytest.mark.parametrize("k", [-60, -17, -16, -15, -3, 29, 30, 31, 60])
+def test_scale_sweep_across_the_magnitude_window(rr, k):
+    """R must not depend on a power-of-two scale of the input and dM must scale with its inverse, from 2^-60 to 2^60
+    (the exact power-of-two prescale of the kernels), also inside a batch that mixes scales."""
+    torch.manual_seed(3)
+    n = 4096 + 5
+    x = torch.randn(n, 9, device="cuda")
+    g = torch.randn(n, 3, 3, device="cuda")
+    rt = rr.symmetric_orthogonalization(torch.randn(n, 9, device="cuda"))
+    sc = 2.0 ** k
+    x0, xs = x.clone().requires_grad_(True), (x * sc).requires_grad_(True)
+    r0, rs = rr.symmetric_orthogonalization(x0), rr.symmetric_orthogonalization(xs)
+    assert (r0 - rs).abs().max().item() <= 1e-6
+    r0.backward(g); rs.backward(g)
+    scale = x0.grad.abs().amax(dim=1, keepdim=True)
+    assert ((xs.grad * sc - x0.grad).abs() / scale).max().item() <= 1e-5
+    # the fused step too (loss identical, gradient scaled); mixed batch: half the rows scaled
+    mix = x.clone()
+    mix[::2] *= sc
+    l0, g0 = rr.svd_frobenius_loss_and_grad(x, rt)
+    l1, g1 = rr.svd_frobenius_loss_and_grad(mix, rt)
+    assert abs(l0.item() - l1.item()) <= 1e-6
+    g1 = g1.clone()
+    g1[::2] *= sc
+    assert ((g1 - g0).abs() / g0.abs().amax(dim=1, keepdim=True)).max().item() <= 1e-5
+
+
 def test_degenerate_inputs_are_finite_rotations(rr):
     cases = torch.tensor([
         [0.0] * 9, [1, 0, 0, 0, 1, 0, 0, 0, 1], [-1, 0, 0, 0, -1, 0, 0, 0, -1], [1, 0, 0, 0, 1, 0, 0, 0, -1],
