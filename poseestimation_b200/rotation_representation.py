@@ -246,4 +246,16 @@ def install(namespace) -> list:
         if name in g:
             g[name] = globals()[name]
             done.append(name)
+    # the refiner's and the point-cloud experiment's helpers (Iterative/main.py: `from utility import *`,
+    # `from loss import *`; point_cloud/main.py: `from prepare import *`) live in two sibling modules
+    import importlib
+    pkg = __package__ or "poseestimation_b200"
+    for mod, names in ((".iterative", ("calculate_T_pred", "transform_pts", "compute_ADD_L1_loss",
+                                       "compute_disentangled_ADD_L1_loss")),
+                       (".point_cloud", ("get_sampled_rotation_matrices_by_axisAngle",))):
+        m = importlib.import_module(mod, pkg)
+        for name in names:
+            if name in g:
+                g[name] = getattr(m, name)
+                done.append(name)
     return done

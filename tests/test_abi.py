@@ -111,3 +111,68 @@ def test_fake_kernels_give_shapes():
         assert deg.dtype == torch.float64 and deg.shape == (5,) and flag.dtype == torch.int32
         r, t = ops.kabsch(torch.empty(2, 16, 3, device="cuda"), torch.empty(2, 16, 3, device="cuda"))
         assert r.shape == (2, 3, 3) and t.shape == (2, 3)
+
+
+def test_no_cpu_fallback_for_the_8f_modules():
+    import torch
+    import poseestimation_b200.iterative as it
+    import poseestimation_b200.point_cloud as pc
+    T = torch.eye(4).repeat(2, 1, 1)
+    with pytest.raises(NotImplementedError):
+        it.calculate_T_pred(torch.randn(2, 12), T)
+    with pytest.raises(NotImplementedError):
+        it.compute_disentangled_ADD_L1_loss(T, T, torch.randn(2, 8, 3))
+    with pytest.raises(NotImplementedError):
+        it.transform_pts(T, torch.randn(2, 8, 3))
+    with pytest.raises(NotImplementedError):
+        pc.rotate_cloud(torch.eye(3).repeat(2, 1, 1), torch.randn(2, 8, 3))
+    with pytest.raises(NotImplementedError):
+        pc.rotation_matrices_from_axis_angle(torch.randn(2), torch.randn(2, 3))
+    with pytest.raises(NotImplementedError):
+        pc.kabsch(torch.randn(2, 8, 3).requires_grad_(True), torch.randn(2, 8, 3))
+
+
+def test_fake_kernels_of_the_8f_ops():
+    import torch
+    from torch._subclasses.fake_tensor import FakeTensorMode
+    from poseestimation_b200 import ops
+    with FakeTensorMode():
+        c = lambda *s: torch.empty(*s, device="cuda")
+        assert ops.affine_points(c(2, 3, 3), c(2, 3), c(2, 16, 3), False).shape == (2, 16, 3)
+        assert ops.affine_points(c(2, 3, 3), None, c(2, 16, 3), True).shape == (2, 16, 3)
+        m, s = ops.cloud_outer_sum(c(2, 16, 3), c(2, 16, 3))
+        assert m.shape == (2, 3, 3) and s.shape == (2, 3)
+        r, t, ctx = ops.kabsch_ctx(c(2, 16, 3), c(2, 16, 3))
+        assert r.shape == (2, 3, 3) and t.shape == (2, 3) and ctx.shape == (2, 15)
+        assert ops.axis_angle_matrix(c(7), c(7, 3)).shape == (7, 3, 3)
+        assert ops.pose_update(c(4, 12), c(4, 4, 4), 444.0, 444.0).shape == (4, 4, 4)
+        assert ops.pose_update_bwd(c(4, 12), c(4, 4, 4), c(4, 4, 4), 444.0, 444.0).shape == (4, 12)
+        item, tot, g = ops.add_l1(c(4, 4, 4), c(4, 4, 4), c(4, 32, 3), True)
+        assert item.shape == (4,) and tot.dtype == torch.float64 and g.shape == (4, 3, 4)
+        loss, dx = ops.svd_orth_frobenius_step(c(5, 9), c(5, 3, 3))
+        assert loss.shape == () and dx.shape == (5, 9)
+
+
+def test_iterative_module_mirrors_the_reference_signatures():
+    """Same positional parameters as Iterative/utility.py:90 and Iterative/loss.py:10,31,51."""
+    import inspect
+    import poseestimation_b200.iterative as it
+    assert list(inspect.signature(it.calculate_T_pred).parameters) == ["model_output", "T_init", "device", "rot_repr"]
+    assert list(inspect.signature(it.compute_ADD_L1_loss).parameters) == ["TCO_gt", "TCO_pred", "points", "use_batch_mean"]
+    assert list(inspect.signature(it.compute_disentangled_ADD_L1_loss).parameters) == ["T_CO_pred", "T_CO_gt", "points"]
+    assert list(inspect.signature(it.transform_pts).parameters) == ["T", "pts"]
+    assert it.get_scene_parameters() == (50 / (36 / 320), 50 / (36 / 320))
+
+
+def test_install_rebinds_private_copies_including_the_8f_helpers():
+    import poseestimation_b200.rotation_representation as rr
+    import poseestimation_b200.iterative as it
+    import poseestimation_b200.point_cloud as pc
+    ns = {"symmetric_orthogonalization": None, "calculate_T_pred": None, "compute_disentangled_ADD_L1_loss": None,
+          "get_sampled_rotation_matrices_by_axisAngle": None, "unrelated": 7}
+    done = rr.install(ns)
+    assert set(done) == set(ns) - {"unrelated"} and ns["unrelated"] == 7
+    assert ns["symmetric_orthogonalization"] is rr.symmetric_orthogonalization
+    assert ns["calculate_T_pred"] is it.calculate_T_pred
+    assert ns["compute_disentangled_ADD_L1_loss"] is it.compute_disentangled_ADD_L1_loss
+    assert ns["get_sampled_rotation_matrices_by_axisAngle"] is pc.get_sampled_rotation_matrices_by_axisAngle

@@ -188,3 +188,21 @@ def test_refiner_step_end_to_end(it, golden):
     ang = it.angle_error(it.calculate_T_pred(o.detach(), T(z["T_init"]).cuda(), "cuda")[:, :3, :3].contiguous(),
                          T(z["T_gt"])[:, :3, :3].contiguous().cuda())
     assert ang.dtype == torch.float64 and ang.shape == (len(z["out"]),)
+
+
+def test_empty_and_tiny_batches(it, pc):
+    from poseestimation_b200 import ops
+    z3 = torch.empty(0, 16, 3, device="cuda")
+    assert pc.rotate_cloud(torch.empty(0, 3, 3, device="cuda"), z3).shape == (0, 16, 3)
+    r, t = pc.kabsch(z3, z3)
+    assert r.shape == (0, 3, 3) and t.shape == (0, 3)
+    assert pc.rotation_matrices_from_axis_angle(torch.empty(0, device="cuda"), torch.empty(0, 3, device="cuda")).shape == (0, 3, 3)
+    assert it.calculate_T_pred(torch.empty(0, 12, device="cuda"), torch.empty(0, 4, 4, device="cuda")).shape == (0, 4, 4)
+    item, tot, g = ops.add_l1(torch.empty(0, 4, 4, device="cuda"), torch.empty(0, 4, 4, device="cuda"), z3, True)
+    assert item.shape == (0,) and tot.item() == 0.0 and g.shape == (0, 3, 4)
+    # one item, one vertex, identical poses: zero loss and (sign(0) = 0) zero gradient, as torch's abs() gives
+    T1 = torch.eye(4, device="cuda").reshape(1, 4, 4)
+    tp = T1.clone().requires_grad_(True)
+    loss = it.compute_disentangled_ADD_L1_loss(tp, T1, torch.ones(1, 1, 3, device="cuda"))
+    loss.backward()
+    assert loss.item() == 0.0 and tp.grad.abs().max().item() == 0.0
