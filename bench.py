@@ -55,6 +55,12 @@ def parse_args():
     ap.add_argument("--cpu-sample", type=int, default=1 << 18, help="matrices per CPU-baseline pass")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--total", type=int, default=0,
+                    help="total matrices over all GPUs (BASELINE config 5: 2^30); per-GPU count = total / N "
+                         "(strong scaling over N); overrides --n")
+    ap.add_argument("--lean", action="store_true",
+                    help="only the timed step: no explanation kernels, no e2e, no CPU baseline, 3 resident arrays "
+                         "(x, R_true, dL/dx) - what lets 2^30 matrices (116 GB) fit one 180 GB B200")
     return ap.parse_args()
 
 
@@ -197,12 +203,21 @@ def run_native(args):
     lib, check = _lib.lib, _lib.check
 
     n = args.n
+    if args.total:
+        if args.total % world:
+            raise SystemExit("--total must be divisible by the number of GPUs")
+        n = args.total // world
+    if args.lean:
+        args.no_e2e = args.no_cpu_baseline = True
     gen = torch.Generator(device=dev).manual_seed(rank)
     x = torch.randn(n, 9, device=dev, generator=gen)
-    r_true = rr.symmetric_orthogonalization(torch.randn(n, 9, device=dev, generator=gen)).reshape(n, 9).contiguous()
-    dx = torch.empty(n, 9, device=dev)
-    r_out = torch.empty(n, 9, device=dev)
-    g_up = torch.randn(n, 9, device=dev, generator=gen)
+    r_true = torch.randn(n, 9, device=dev, generator=gen)
+    check(lib.pe_svd_orth_fwd(r_true.data_ptr(), 9, r_true.data_ptr(), None, n,
+                              torch.cuda.current_stream().cuda_stream), "targets")   # in place: rotations as targets
+    if not args.lean:
+        dx = torch.empty(n, 9, device=dev)
+        r_out = torch.empty(n, 9, device=dev)
+        g_up = torch.randn(n, 9, device=dev, generator=gen)
     loss_sum = torch.zeros(3, dtype=torch.float64, device=dev)     # [sum |.|_F, (spare), count] - the all-reduced vector
     gout = torch.ones(1, dtype=torch.float32, device=dev)
     inv_n_global = 1.0 / (n * world)
@@ -289,7 +304,9 @@ def run_native(args):
         return a.elapsed_time(b) / reps
 
     also = {}
-    if rank == 0:
+    if rank == 0 and args.lean:
+        also["step_kernel_ms"], also["backward_upstream_one_ms"], also["loss"] = fwd_ms, bwd_ms, loss_value
+    if rank == 0 and not args.lean:
         also["svd_orth_fwd_ms"] = time_kernel(lambda: check(lib.pe_svd_orth_fwd(
             x.data_ptr(), 9, r_out.data_ptr(), None, n, stream), "f"))
         also["svd_orth_bwd_savedR_ms"] = time_kernel(lambda: check(lib.pe_svd_orth_bwd(
@@ -358,12 +375,14 @@ def run_native(args):
 
     print(json.dumps({
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong" if args.total else "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
-        "config": {"workload": f"svd_orth+frobenius fwd+bwd, {n} random 3x3 fp32 matrices per GPU (BASELINE config 2)",
+        "config": {"workload": f"svd_orth+frobenius fwd+bwd, {n} random 3x3 fp32 matrices per GPU "
+                               + (f"({n * world} in total, sharded: BASELINE config 5)" if args.total
+                                  else "(BASELINE config 2)"),
                    "launches_per_step": "svd_orth_frobenius_step (108 B: loss + gradient from one SVD) + "
                                         "scale_by_scalar_inplace (upstream gradient 1: device-side no-op)",
-                   "matrices_per_gpu": n, "l2": "inputs (2 x %.0f MB) larger than the 126 MB L2" % (n * 36 / 1e6),
+                   "matrices_per_gpu": n, "total_matrices": n * world, "l2": "inputs (2 x %.0f MB) larger than the 126 MB L2" % (n * 36 / 1e6),
                    "collective": "ncclAllReduce(3 x f64) per step" if world > 1 else "none"},
         "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
         "also": also,
