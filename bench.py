@@ -193,9 +193,13 @@ def run_native(args):
         raise SystemExit("bench.py: no CUDA device - the native arm has no CPU path")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    stdout_fd = None
     if world > 1:
-        # NCCL writes its version / debug lines to stdout; stdout carries exactly one JSON line, so send them to stderr
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+        # NCCL (C code) writes its version / debug lines straight to file descriptor 1.  stdout must carry exactly one
+        # JSON line, so fd 1 points at stderr until that line is printed.
+        sys.stdout.flush()
+        stdout_fd = os.dup(1)
+        os.dup2(2, 1)
         dist.init_process_group("nccl", device_id=dev)
 
     from poseestimation_b200 import _lib, launch_count
@@ -373,6 +377,10 @@ def run_native(args):
         cpu = {"value": m / sec, "unit": UNIT, "cores": cores, "kind": "port",
                "sample": f"{m} matrices x 3 passes (best), fp32, oracle port = the reference's torch calls"}
 
+    if stdout_fd is not None:
+        sys.stdout.flush()
+        os.dup2(stdout_fd, 1)
+        os.close(stdout_fd)
     print(json.dumps({
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong" if args.total else "weak", "vs_baseline": None, "dtype": "f32",
