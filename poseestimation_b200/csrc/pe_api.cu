@@ -15,6 +15,7 @@ Params<Op> make_params(const float* i0, long long stride0, const float* i1, cons
     p.in0_stride = stride0;
     p.sums = sums;
     p.flag = flag;
+    p.sched = nullptr;  // assigned by stream_launch
     p.ex = ex;
     return p;
 }

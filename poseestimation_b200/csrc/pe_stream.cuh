@@ -7,8 +7,12 @@
 //   HBM --TMA bulk copy--> smem ring (STAGES deep) --LDS--> registers --Op::run--> registers --STS--> smem
 //       --TMA bulk store--> HBM
 //
-// * grid = (#SMs x resident CTAs/SM) persistent CTAs; CTA c handles tiles c, c + grid, c + 2*grid, ...
-//   so at any moment the whole grid streams through one contiguous window of HBM.
+// * grid = (#SMs x resident CTAs/SM) persistent CTAs that draw tiles from ONE global counter (atomicAdd), in order:
+//   at any moment the whole grid streams through one contiguous window of HBM, a CTA that starts late or shares its SM
+//   with another kernel (the NCCL all-reduce of the loss, overlapped with the next step) simply draws fewer tiles, and
+//   there is no last-wave quantisation (2^24 matrices = 32768 tiles over 444 CTAs would be 74 vs 73 tiles per CTA).
+//   The index for the refill of a stage is drawn one iteration ahead, so the atomic's latency hides behind the math;
+//   the last CTA to finish resets the counter pair for the next launch that uses the slot.
 // * a tile is T consecutive records; one elected thread issues one bulk copy per input array per tile and the
 //   copies complete on the stage's mbarrier (byte-counted).  STAGES-1 tiles are always in flight per CTA.
 // * outputs are double-buffered in shared memory and leave with bulk stores tracked by bulk async-groups.
@@ -34,6 +38,7 @@ struct Params {
     long long in0_stride;  // words between consecutive records of in[0] (direct kernel only)
     double* sums;          // NRED accumulators (device), added to with one atomic per CTA
     int* flag;             // OR-ed with the per-record flags
+    unsigned int* sched;   // {next tile to hand out, CTAs finished}: the dynamic tile scheduler (set by stream_launch)
     typename Op::Extra ex;
 };
 
@@ -47,6 +52,7 @@ struct Geometry {
     static constexpr bool IN_PLACE = Op::RPT == 2 && Op::WO0 == Op::WI0 && Op::WO1 == 0;
     static constexpr int NOBUF = (WOTOT > 0 && !IN_PLACE) ? 2 : 0;
     static constexpr int TR = kTile * Op::RPT;  // records per tile (RPT records per thread)
+    static constexpr bool DYNAMIC = Op::RPT == 2;  // tiles drawn from a global counter (see stream_tma_kernel)
     static constexpr int kBarBytes = 128;
     static constexpr int kStageBytes = TR * 4 * WITOT;
     static constexpr int kOutBytes = TR * 4 * WOTOT;
@@ -133,8 +139,23 @@ __global__ void __launch_bounds__(kTile, Op::MINB) stream_tma_kernel(const Param
     const long long n = p.n;
     const long long ntiles = (n + TR - 1) / TR;
     const long long nfull = n / TR;  // tiles [0, nfull) are complete and move by TMA
-    const long long gstep = gridDim.x;
+    unsigned int* s_tile = reinterpret_cast<unsigned int*>(smem_raw + 64);  // tile held (or awaited) by each stage
     uint64_t policy = 0;
+    // Tile hand-out (thread 0 only).  DYN: one global counter.  Otherwise the static round-robin c, c + grid, ...:
+    // same code path, the "counter" is a register.  The heavy (two-records-per-thread SVD) ops are dynamic; the light
+    // elementwise ops finish a 256-record tile in well under a microsecond and 65536 same-address atomics per launch
+    // would serialise (measured: 0.144 -> 0.204 ms for euler_fwd), so they keep the static order.
+    constexpr bool DYN = G::DYNAMIC;
+    unsigned int static_next = blockIdx.x;
+    auto draw = [&]() -> unsigned int {
+        if constexpr (DYN) {
+            return atomicAdd(p.sched, 1u);
+        } else {
+            const unsigned int t = static_next;
+            static_next += gridDim.x;
+            return t;
+        }
+    };
 
     auto issue = [&](int s, long long tile) {
         // one elected thread: arm the barrier with the byte count, then one bulk copy per input array
@@ -155,15 +176,18 @@ __global__ void __launch_bounds__(kTile, Op::MINB) stream_tma_kernel(const Param
 #pragma unroll
         for (int s = 0; s < S; ++s) mbar_init(&bars[s], 1);
         mbar_init_fence();
-    }
-    __syncthreads();
-    if (tid == 0) {
 #pragma unroll
         for (int s = 0; s < S; ++s) {
-            long long tile = blockIdx.x + s * gstep;
-            if (tile < nfull) issue(s, tile);
+            const unsigned int t = draw();
+            if constexpr (DYN) s_tile[s] = t;
+            if (t < nfull) issue(s, t);
         }
     }
+    // the index that will refill the stage of the current iteration is drawn ONE ITERATION AHEAD (tid 0 only), so the
+    // round trip of the atomic is over long before the index is needed, also for ops with next to no arithmetic
+    unsigned int ahead = 0;
+    if (tid == 0) ahead = draw();
+    __syncthreads();
 
     double red[Op::NRED > 0 ? Op::NRED : 1];
 #pragma unroll
@@ -173,9 +197,17 @@ __global__ void __launch_bounds__(kTile, Op::MINB) stream_tma_kernel(const Param
     int s = 0;
     uint32_t parity = 0;
     int obuf = 0;
-    long long refill_tile = -1;  // IP mode: tile to load into the stage vacated by the previous iteration
+    bool refill = false;         // IP mode: the stage vacated by the previous iteration awaits its next tile
+    unsigned int refill_tile = 0;
     int refill_stage = 0;
-    for (long long tile = blockIdx.x; tile < ntiles; tile += gstep) {
+    long long static_tile = blockIdx.x;  // !DYN: the processing order is known without the shared-memory hand-over
+    for (;;) {
+        // DYN: the same for every thread, written by thread 0 before a __syncthreads
+        const long long tile = DYN ? (long long)s_tile[s] : static_tile;
+        if (tile >= ntiles) break;
+        static_tile += gridDim.x;
+        const unsigned int drawn = ahead;               // for the refill of THIS stage
+        if (tid == 0) ahead = draw();                   // for the next iteration's
         const long long base = tile * TR;
         const bool full = tile < nfull;
         const int cnt = full ? TR : (int)(n - base);
@@ -185,8 +217,9 @@ __global__ void __launch_bounds__(kTile, Op::MINB) stream_tma_kernel(const Param
         if constexpr (IP) {
             // the stage used one iteration ago was stored from in place: once the TMA store has finished reading
             // it, refill it (prefetch distance: S - 1 tiles)
-            if (tid == 0 && refill_tile >= 0) {
+            if (tid == 0 && refill) {
                 bulk_wait_read<0>();
+                if constexpr (DYN) s_tile[refill_stage] = refill_tile;
                 if (refill_tile < nfull) issue(refill_stage, refill_tile);
             }
         }
@@ -234,10 +267,10 @@ __global__ void __launch_bounds__(kTile, Op::MINB) stream_tma_kernel(const Param
             if constexpr (G::NOBUF > 0) {
                 if (tid == 0) bulk_wait_read<1>();  // the store issued two tiles ago has finished reading `so`
             }
-            __syncthreads();  // (A) every thread is done with stage s; `so` is free
+            __syncthreads();  // (A) every thread is done with stage s (and has read s_tile[s]); `so` is free
             if (tid == 0) {
-                long long next = tile + S * gstep;
-                if (next < nfull) issue(s, next);
+                if constexpr (DYN) s_tile[s] = drawn;
+                if (drawn < nfull) issue(s, drawn);
             }
         }
         if constexpr (G::WOTOT > 0) {
@@ -271,7 +304,8 @@ __global__ void __launch_bounds__(kTile, Op::MINB) stream_tma_kernel(const Param
             obuf ^= 1;
         }
         if constexpr (IP) {
-            refill_tile = tile + S * gstep;
+            refill = true;
+            refill_tile = drawn;
             refill_stage = s;
         }
         if (++s == S) { s = 0; parity ^= 1; }
@@ -280,6 +314,15 @@ __global__ void __launch_bounds__(kTile, Op::MINB) stream_tma_kernel(const Param
         if (tid == 0) bulk_wait<0>();  // shared memory must outlive the stores that read it
     }
     block_reduce_and_publish<Op>(red, flag, p.sums, p.flag, s_red);
+    // every CTA has drawn its last index before it gets here; the last one re-arms the scheduler slot
+    if (DYN && tid == 0) {
+        __threadfence();
+        if (atomicAdd(p.sched + 1, 1u) == gridDim.x - 1) {
+            p.sched[0] = 0u;
+            p.sched[1] = 0u;
+            __threadfence();
+        }
+    }
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -349,6 +392,33 @@ int stream_config(LaunchCfg* out) {
 
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
+// Scheduler slots: {next tile, finished CTAs} pairs in device memory, 32 bytes apart, zero when idle (the last CTA of
+// a launch re-arms its slot).  Successive launches take successive slots of a ring, so launches that overlap on
+// different streams never share one (the ring is far longer than any realistic number of launches in flight).
+// This is the one piece of device memory the library owns: 32 KB per device, allocated on the first launch (which
+// therefore must not happen inside a CUDA-graph capture).
+constexpr int kSchedSlots = 1024;
+inline int sched_slot(unsigned int** out) {
+    static std::mutex mu;
+    static unsigned int* pool[64] = {nullptr};
+    static unsigned long long next[64] = {0};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return fail_cuda(e, "cudaGetDevice");
+    if (dev < 0 || dev >= 64) return fail(PE_ERR_BAD_ARG, "device index out of range");
+    std::lock_guard<std::mutex> lk(mu);
+    if (!pool[dev]) {
+        void* ptr = nullptr;
+        e = cudaMalloc(&ptr, kSchedSlots * 32);
+        if (e != cudaSuccess) return fail_cuda(e, "cudaMalloc(scheduler slots)");
+        e = cudaMemset(ptr, 0, kSchedSlots * 32);
+        if (e != cudaSuccess) return fail_cuda(e, "cudaMemset(scheduler slots)");
+        pool[dev] = static_cast<unsigned int*>(ptr);
+    }
+    *out = pool[dev] + (next[dev]++ % kSchedSlots) * 8;
+    return 0;
+}
+
 // force_direct: test hook (PE_FORCE_DIRECT=1) so that the non-TMA kernel is covered on aligned inputs too
 template <class Op>
 int stream_launch(Params<Op> p, cudaStream_t stream) {
@@ -371,6 +441,9 @@ int stream_launch(Params<Op> p, cudaStream_t stream) {
     if (tma) {
         long long grid = (long long)cfg.sms * cfg.ctas_per_sm;
         if (grid > ntiles) grid = ntiles;
+        if constexpr (G::DYNAMIC) {
+            if (int rc = sched_slot(&p.sched)) return rc;
+        }
         stream_tma_kernel<Op><<<(unsigned)grid, kTile, G::kSmemBytes, stream>>>(p);
     } else {
         long long grid = (long long)cfg.sms * 8;
