@@ -39,6 +39,32 @@ def global_means(partials: torch.Tensor, group=None) -> tuple[torch.Tensor, torc
     return partials[0] / n, partials[1] / n, partials[2]
 
 
+class PendingMeans:
+    """Handle of an all-reduce that is still in flight (see :func:`global_means_async`)."""
+
+    def __init__(self, partials: torch.Tensor, work):
+        self.partials, self.work = partials, work
+
+    def wait(self) -> tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+        """Make the current stream wait for the reduction (no host block on CUDA) -> (mean loss, mean angle, count)."""
+        if self.work is not None:
+            self.work.wait()
+            self.work = None
+        n = self.partials[2].clamp_min(1.0)
+        return self.partials[0] / n, self.partials[1] / n, self.partials[2]
+
+
+def global_means_async(partials: torch.Tensor, group=None) -> PendingMeans:
+    """Start the all-reduce of the packed partials and return at once.  Nothing in a training step depends on the
+    reduced loss (the backward scale 1/B_global is known beforehand), so the caller launches the next kernels first
+    and calls ``.wait()`` only where the value is consumed (logging): the 24-byte exchange then overlaps the next
+    step's kernel instead of sitting between two of them.  ``partials`` must stay untouched until ``.wait()``."""
+    work = None
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        work = dist.all_reduce(partials, op=dist.ReduceOp.SUM, group=group, async_op=True)
+    return PendingMeans(partials, work)
+
+
 def backward_scale(global_count: int) -> float:
     """The factor 1/B_global the backward kernels take: known before the step, so the backward needs no collective."""
     return 1.0 / max(int(global_count), 1)

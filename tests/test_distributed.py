@@ -27,6 +27,8 @@ def test_single_rank_identity():
     loss, ang, n = D.global_means(p)
     assert loss.item() == 2.0 and ang.item() == 10.0 and n.item() == 3.0
     assert D.backward_scale(4) == 0.25
+    p2 = D.pack_partials(torch.tensor([6.0], dtype=torch.float64), None, 3)
+    assert D.global_means_async(p2).wait()[0].item() == 2.0
 
 
 def _free_port():
@@ -44,8 +46,11 @@ def _worker(rank, world, port, n, out):
         per_record_angle = torch.rand(n, generator=g, dtype=torch.float64) * 180
         lo, hi = D.shard_bounds(n, rank, world)
         part = D.pack_partials(per_record_loss[lo:hi].sum().reshape(1), per_record_angle[lo:hi].sum().reshape(1), hi - lo)
+        pending = D.global_means_async(part.clone())          # the overlapped form gives the same numbers
         loss, ang, cnt = D.global_means(part)
-        ok = (abs(loss.item() - per_record_loss.mean().item()) < 1e-12 and
+        loss2, ang2, cnt2 = pending.wait()
+        ok = (loss2.item() == loss.item() and ang2.item() == ang.item() and cnt2.item() == cnt.item() and
+              abs(loss.item() - per_record_loss.mean().item()) < 1e-12 and
               abs(ang.item() - per_record_angle.mean().item()) < 1e-9 and int(cnt.item()) == n)
         out[rank] = bool(ok)
     finally:
