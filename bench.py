@@ -337,6 +337,10 @@ def run_native(args):
             x.data_ptr(), 9, r_out.data_ptr(), g_up.data_ptr(), dx.data_ptr(), n, stream), "b"))
         also["svd_orth_bwd_recompute_ms"] = time_kernel(lambda: check(lib.pe_svd_orth_bwd(
             x.data_ptr(), 9, None, g_up.data_ptr(), dx.data_ptr(), n, stream), "b"))
+        # the literal SURVEY 8(d) definition: svd_orth forward (72 B) + its backward from M and G (108 B) = 180 B
+        pair_ms = also["svd_orth_fwd_ms"] + also["svd_orth_bwd_recompute_ms"]
+        also["svd_orth_fwd_plus_bwd_matrices_per_s"] = n / (pair_ms * 1e-3)
+        also["svd_orth_fwd_plus_bwd_frac_of_180B_roofline"] = 180 * n / (pair_ms * 1e-3) / 1e9 / measured_peak_gbs()[0]
         also["step_kernel_ms"], also["backward_upstream_one_ms"] = fwd_ms, bwd_ms
         also["backward_upstream_not_one_ms"] = time_kernel(k_scale)
         also["matrices_per_s_upstream_not_one"] = n / ((fwd_ms + also["backward_upstream_not_one_ms"]) * 1e-3)
