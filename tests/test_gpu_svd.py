@@ -139,6 +139,54 @@ def test_full_size_properties(rr):
     assert float((obj_ref - obj).max()) <= 1e-5
 
 
+def test_full_size_tiles_are_each_processed_once(rr):
+    """The SVD kernels draw their tiles from a global counter: a full-size, ragged batch must give bit for bit what
+    the same records give when they are processed in two separate launches (no tile dropped, none done twice), on
+    repeated launches (the scheduler slot is re-armed), and the fused step must agree with the separate kernels."""
+    n = (1 << 24) + 77
+    torch.manual_seed(1)
+    x = torch.randn(n, 9, device="cuda")
+    r = rr.symmetric_orthogonalization(x)
+    h = (1 << 23) + 5
+    assert torch.equal(r[:h], rr.symmetric_orthogonalization(x[:h]))
+    assert torch.equal(r[h:], rr.symmetric_orthogonalization(x[h:]))
+    for _ in range(3):
+        assert torch.equal(r, rr.symmetric_orthogonalization(x))
+    rt = rr.symmetric_orthogonalization(torch.randn(n, 9, device="cuda"))
+    loss, g = rr.svd_frobenius_loss_and_grad(x, rt)
+    loss_sep = rr.loss_frobenius(r, rt)
+    assert abs(loss.item() - loss_sep.item()) <= 1e-6
+    x2 = x.clone().requires_grad_(True)
+    rr.svd_frobenius_loss(x2, rt, single_pass=False).backward()
+    scale = x2.grad.abs().amax(dim=1, keepdim=True)
+    assert float(((g - x2.grad).abs() / scale).max()) <= 1e-4
+    # halves of the fused step: sums of the two half-batches reproduce the whole (loss is a mean over n)
+    l1, g1 = rr.svd_frobenius_loss_and_grad(x[:h], rt[:h])
+    l2, g2 = rr.svd_frobenius_loss_and_grad(x[h:], rt[h:])
+    assert abs((l1.item() * h + l2.item() * (n - h)) / n - loss.item()) <= 1e-6
+    # (the 1/n factor is folded into the seed ahead of the 3x3 solve, so the roundings differ on ill-conditioned rows)
+    for part, whole, w in ((g1, g[:h], h / n), (g2, g[h:], (n - h) / n)):
+        rel = (part * w - whole).abs() / whole.abs().amax(dim=1, keepdim=True).clamp_min(1e-30)
+        assert float(rel.max()) <= 1e-4
+
+
+def test_full_size_directional_derivative(rr):
+    """2^24 matrices: <dL/dx, V> against a central difference of the loss along V = the row-normalised gradient (a
+    random V gives a derivative that cancels to ~n^-1/2, below the float32 resolution of the returned loss)."""
+    n = 1 << 24
+    torch.manual_seed(2)
+    x = torch.randn(n, 9, device="cuda")
+    rt = rr.symmetric_orthogonalization(torch.randn(n, 9, device="cuda"))
+    _, g = rr.svd_frobenius_loss_and_grad(x, rt)
+    v = g / g.norm(dim=1, keepdim=True).clamp_min(1e-30)
+    lhs = (g.double() * v.double()).sum().item()
+    eps = 1e-3
+    lp = rr.svd_frobenius_loss(x + eps * v, rt).item()      # means accumulated in float64 inside the kernel
+    lm = rr.svd_frobenius_loss(x - eps * v, rt).item()
+    rhs = (lp - lm) / (2 * eps)
+    assert abs(lhs - rhs) <= 2e-2 * max(abs(rhs), 1e-3), (lhs, rhs)
+
+
 def test_config1_svd_plus_frobenius(rr):
     """BASELINE config 1: 4096 random matrices, forward + Frobenius loss, vs the reference formulas on the CPU."""
     torch.manual_seed(0)
