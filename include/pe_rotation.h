@@ -128,6 +128,21 @@ int pe_kabsch_fwd_ctx(const float* p, const float* q, int64_t b, int64_t npts, f
  * which two pe_affine_points launches then apply (48 B per point pair in total). */
 int pe_kabsch_bwd_coeffs(const float* ctx, const float* r, const float* g, int64_t npts, float* coef_q, float* coef_p,
                          int64_t b, void* stream);
+/* Weighted Kabsch ("weighted / with-translation variants"; no reference function - the site is
+ * point_cloud/main.py:171-197).  w: (b, npts) weights >= 0.  With W = sum_k w_k, pbar = sum w p / W, qbar likewise:
+ * r = pe_svd_orth of sum_k w_k (q_k - qbar)(p_k - pbar)^T, t (nullable) = qbar - R pbar, and ctx (nullable)
+ * [b][16] = (that matrix 9, pbar 3, qbar 3, W 1).  A pair whose weights are all zero gets the rotation of the zero
+ * matrix, not NaN.  28 B per point pair. */
+int pe_kabsch_weighted_fwd(const float* p, const float* q, const float* w, int64_t b, int64_t npts, float* r, float* t,
+                           float* ctx, void* stream);
+/* per-pair part of its backward: as pe_kabsch_bwd_coeffs with the 16-word context (1/N becomes 1/W). */
+int pe_kabsch_weighted_bwd_coeffs(const float* ctx, const float* r, const float* g, float* coef_q, float* coef_p,
+                                  int64_t b, void* stream);
+/* point part of its backward, one pass over p, q, w:  dq_k = w_k (A_q p_k + b_q),  dp_k = w_k (A_p q_k + b_p),
+ * dw_k = (q_k - qbar).(A_q p_k + b_q) - (R^T g_t / W).(p_k - pbar).  Each of dp, dq, dw is nullable (not all). */
+int pe_kabsch_weighted_bwd_points(const float* p, const float* q, const float* w, const float* coef_q,
+                                  const float* coef_p, const float* ctx, int64_t b, int64_t npts, float* dp, float* dq,
+                                  float* dw, void* stream);
 /* m[b][9] = sum_k g[b][k] p[b][k]^T (uncentred), gsum[b][3] = sum_k g[b][k] (nullable): the reduction behind the
  * gradient of pe_affine_points w.r.t. its matrix and offset. */
 int pe_cloud_outer_sum(const float* g, const float* p, int64_t b, int64_t npts, float* m, float* gsum, void* stream);

@@ -259,6 +259,20 @@ def kabsch(p: torch.Tensor, q: torch.Tensor):
     return r, t
 
 
+def kabsch_weighted(p: torch.Tensor, q: torch.Tensor, w: torch.Tensor):
+    """Weighted variant (no reference function): weighted centroids and covariance, then the
+    reference's own projection.  Pairs whose weights sum to zero get the projection of the zero matrix."""
+    p, q, w = p.double(), q.double(), w.double()
+    wsum = w.sum(dim=1, keepdim=True)
+    inv = torch.where(wsum > 0, 1.0 / wsum.clamp_min(torch.finfo(w.dtype).tiny), torch.zeros_like(wsum))
+    pbar = (w.unsqueeze(2) * p).sum(dim=1, keepdim=True) * inv.unsqueeze(2)
+    qbar = (w.unsqueeze(2) * q).sum(dim=1, keepdim=True) * inv.unsqueeze(2)
+    c = torch.einsum("bk,bki,bkj->bij", w, q - qbar, p - pbar)
+    r = symmetric_orthogonalization(c.reshape(-1, 9))
+    t = qbar.squeeze(1) - torch.einsum("bij,bj->bi", r, pbar.squeeze(1))
+    return r, t
+
+
 def sample_rotations_axis_angle(batch: int, generator: torch.Generator | None = None) -> torch.Tensor:
     """The cloud-pair rotation sampler of point_cloud/prepare.py:21-49, seeded and on the CPU.
 

@@ -44,6 +44,9 @@ SIGNATURES = {
     "pe_kabsch_fwd": [_f, _f, _i64, _i64, _f, _f, _f],
     "pe_kabsch_fwd_ctx": [_f, _f, _i64, _i64, _f, _f, _f, _f],
     "pe_kabsch_bwd_coeffs": [_f, _f, _f, _i64, _f, _f, _i64, _f],
+    "pe_kabsch_weighted_fwd": [_f, _f, _f, _i64, _i64, _f, _f, _f, _f],
+    "pe_kabsch_weighted_bwd_coeffs": [_f, _f, _f, _f, _f, _i64, _f],
+    "pe_kabsch_weighted_bwd_points": [_f, _f, _f, _f, _f, _f, _i64, _i64, _f, _f, _f, _f],
     "pe_cloud_outer_sum": [_f, _f, _i64, _i64, _f, _f, _f],
     "pe_affine_points": [_f, _i64, _int, _int, _f, _i64, _int, _f, _i64, _i64, _f, _f],
     "pe_axis_angle_fwd": [_f, _f, _f, _i64, _f],

@@ -169,6 +169,10 @@ int pe_kabsch_bwd_coeffs(const float* ctx, const float* r, const float* g, int64
     if (npts < 1) return fail(PE_ERR_BAD_ARG, "bad cloud size");
     return run<KabschBwdCoeffs>(ctx, 15, r, g, coef_q, coef_p, b, nullptr, nullptr, {1.0f / (float)npts}, stream);
 }
+int pe_kabsch_weighted_bwd_coeffs(const float* ctx, const float* r, const float* g, float* coef_q, float* coef_p,
+                                  int64_t b, void* stream) {
+    return run<KabschBwdCoeffsW>(ctx, 16, r, g, coef_q, coef_p, b, nullptr, nullptr, {}, stream);
+}
 int pe_pose_update_fwd(const float* out, int64_t out_stride, const float* t_init, float fx, float fy, float* t_pred,
                        int64_t n, void* stream) {
     return run<PoseUpdateFwd>(out, out_stride, t_init, nullptr, t_pred, nullptr, n, nullptr, nullptr,

@@ -9,6 +9,11 @@
 // relative to the pair's first point so that far-from-origin clouds do not cancel).  A butterfly shuffle reduces
 // them; the 3x3 covariance of pair k is parked in lane k % 32, and every 32 pairs the whole warp runs 32
 // register-resident SVDs at once instead of one lane running them one by one.
+//
+// Weighted variant (what a correspondence-weighting network feeds): per-point weights w_k >= 0,
+//   pbar = sum w p / W,  qbar = sum w q / W,  C = sum w (q - qbar)(p - pbar)^T,  W = sum w,
+// a third 1 KB stream per stage (28 B per point pair instead of 24); W == 0 gives C = 0 (svd_orth's rotation of the
+// zero matrix) rather than NaN.  The context record then carries W as a 16th word.
 #include "pe_common.h"
 #include "pe_math.cuh"
 #include "pe_stage.cuh"
@@ -18,12 +23,17 @@ namespace pe {
 constexpr int kKWarps = 8;     // warps per CTA, one CTA per SM
 constexpr int kKStages = 3;    // ring depth per warp
 constexpr int kChunk = 256;    // points per stage per array
-constexpr int kKStageWords = 2 * kChunk * 3;
-constexpr int kKSmem = 1024 + kKWarps * kKStages * kKStageWords * 4;
+template <bool WT>
+struct KGeo {
+    static constexpr int kStageWords = 2 * kChunk * 3 + (WT ? kChunk : 0);
+    static constexpr int kSmem = 1024 + kKWarps * kKStages * kStageWords * 4;
+    static constexpr int kCtx = WT ? 16 : 15;
+};
 
 struct KabschParams {
     const float* p;
     const float* q;
+    const float* w;  // (b, npts) weights, weighted instantiation only
     float* r;
     float* t;  // nullable
     float* ctx;  // nullable: per pair H (9), pbar (3), qbar (3) - what the backward needs besides R
@@ -39,7 +49,9 @@ __device__ __forceinline__ float warp_sum_f(float v) {
     return v;
 }
 
+template <bool WT>
 __global__ void __launch_bounds__(kKWarps * 32, 1) kabsch_kernel(const KabschParams prm) {
+    constexpr int kKStageWords = KGeo<WT>::kStageWords;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw) + warp * kKStages;
@@ -68,9 +80,12 @@ __global__ void __launch_bounds__(kKWarps * 32, 1) kabsch_kernel(const KabschPar
         uint32_t bytes = (uint32_t)cnt * 12u;
         long long off = (pair * npts + (long long)ch * kChunk) * 3;
         float* dst = ring + s * kKStageWords;
-        mbar_arrive_expect_tx(&bars[s], 2 * bytes);
+        mbar_arrive_expect_tx(&bars[s], 2 * bytes + (WT ? (uint32_t)cnt * 4u : 0u));
         bulk_g2s(dst, prm.p + off, bytes, &bars[s], policy);
         bulk_g2s(dst + kChunk * 3, prm.q + off, bytes, &bars[s], policy);
+        if constexpr (WT)
+            bulk_g2s(dst + 2 * kChunk * 3, prm.w + pair * npts + (long long)ch * kChunk, (uint32_t)cnt * 4u, &bars[s],
+                     policy);
     };
     if (tma && lane == 0) {
         for (int s = 0; s < kKStages; ++s)
@@ -80,6 +95,7 @@ __global__ void __launch_bounds__(kKWarps * 32, 1) kabsch_kernel(const KabschPar
     float sp0 = 0, sp1 = 0, sp2 = 0, sq0 = 0, sq1 = 0, sq2 = 0;
     float c00 = 0, c01 = 0, c02 = 0, c10 = 0, c11 = 0, c12 = 0, c20 = 0, c21 = 0, c22 = 0;
     float p00 = 0, p01 = 0, p02 = 0, q00 = 0, q01 = 0, q02 = 0;  // the pair's first point (the shift)
+    float sw = 0.f, kw = 0.f;  // running / parked sum of weights
     float keep[9], kp[3], kq[3];
     long long kpair = -1;
 #pragma unroll
@@ -88,7 +104,7 @@ __global__ void __launch_bounds__(kKWarps * 32, 1) kabsch_kernel(const KabschPar
     int parked = 0;
 
     auto flush = [&]() {
-        if (lane < parked && prm.raw) {
+        if (!WT && lane < parked && prm.raw) {
             // sum q p^T = sum (q - qbar)(p - pbar)^T + N qbar pbar^T ;  sum q = N qbar
             const float nn = (float)npts;
             float* dst = prm.r + kpair * 9;
@@ -104,11 +120,12 @@ __global__ void __launch_bounds__(kKWarps * 32, 1) kabsch_kernel(const KabschPar
             float r[9], ds;
             svd_orth_fast(keep, r, ds);
             if (prm.ctx) {
-                float* cd = prm.ctx + kpair * 15;
+                float* cd = prm.ctx + kpair * KGeo<WT>::kCtx;
 #pragma unroll
                 for (int i = 0; i < 9; ++i) cd[i] = keep[i];
                 cd[9] = kp[0]; cd[10] = kp[1]; cd[11] = kp[2];
                 cd[12] = kq[0]; cd[13] = kq[1]; cd[14] = kq[2];
+                if constexpr (WT) cd[15] = kw;
             }
             float* dst = prm.r + kpair * 9;
 #pragma unroll
@@ -131,25 +148,40 @@ __global__ void __launch_bounds__(kKWarps * 32, 1) kabsch_kernel(const KabschPar
         const int cnt = min(kChunk, npts - ch * kChunk);
         const float* sP;
         const float* sQ;
+        const float* sW = nullptr;
         if (tma) {
             mbar_wait(&bars[s], parity);
             sP = ring + s * kKStageWords;
             sQ = sP + kChunk * 3;
+            if constexpr (WT) sW = sP + 2 * kChunk * 3;
         } else {  // unaligned clouds (npts % 4 != 0 or odd base): read HBM directly, same arithmetic
             long long off = (pair * npts + (long long)ch * kChunk) * 3;
             sP = prm.p + off;
             sQ = prm.q + off;
+            if constexpr (WT) sW = prm.w + pair * npts + (long long)ch * kChunk;
         }
         if (ch == 0) {
-            p00 = sP[0]; p01 = sP[1]; p02 = sP[2];
-            q00 = sQ[0]; q01 = sQ[1]; q02 = sQ[2];
+            int k0 = 0;
+            if constexpr (WT) {  // shift by a point that counts: the first of the leading 32 with a non-zero weight
+                const unsigned live = __ballot_sync(0xffffffffu, lane < cnt && sW[lane] > 0.f);
+                k0 = live ? __ffs(live) - 1 : 0;
+            }
+            p00 = sP[3 * k0]; p01 = sP[3 * k0 + 1]; p02 = sP[3 * k0 + 2];
+            q00 = sQ[3 * k0]; q01 = sQ[3 * k0 + 1]; q02 = sQ[3 * k0 + 2];
         }
 #pragma unroll 4
         for (int i = lane; i < cnt; i += 32) {
             float a0 = sP[3 * i] - p00, a1 = sP[3 * i + 1] - p01, a2 = sP[3 * i + 2] - p02;
             float b0 = sQ[3 * i] - q00, b1 = sQ[3 * i + 1] - q01, b2 = sQ[3 * i + 2] - q02;
+            if constexpr (WT) {
+                const float wk = sW[i];
+                sw += wk;
+                a0 *= wk; a1 *= wk; a2 *= wk;  // a = w (p - p0) from here on
+                sq0 = fmaf(wk, b0, sq0); sq1 = fmaf(wk, b1, sq1); sq2 = fmaf(wk, b2, sq2);
+            } else {
+                sq0 += b0; sq1 += b1; sq2 += b2;
+            }
             sp0 += a0; sp1 += a1; sp2 += a2;
-            sq0 += b0; sq1 += b1; sq2 += b2;
             c00 = fmaf(b0, a0, c00); c01 = fmaf(b0, a1, c01); c02 = fmaf(b0, a2, c02);
             c10 = fmaf(b1, a0, c10); c11 = fmaf(b1, a1, c11); c12 = fmaf(b1, a2, c12);
             c20 = fmaf(b2, a0, c20); c21 = fmaf(b2, a1, c21); c22 = fmaf(b2, a2, c22);
@@ -163,8 +195,13 @@ __global__ void __launch_bounds__(kKWarps * 32, 1) kabsch_kernel(const KabschPar
             c00 = warp_sum_f(c00); c01 = warp_sum_f(c01); c02 = warp_sum_f(c02);
             c10 = warp_sum_f(c10); c11 = warp_sum_f(c11); c12 = warp_sum_f(c12);
             c20 = warp_sum_f(c20); c21 = warp_sum_f(c21); c22 = warp_sum_f(c22);
-            const float inv = 1.0f / (float)npts;
+            float inv = 1.0f / (float)npts;
+            if constexpr (WT) {
+                sw = warp_sum_f(sw);
+                inv = sw > 0.f ? 1.0f / sw : 0.f;
+            }
             if (lane == parked) {
+                kw = sw;
                 // C = sum q' p'^T - (sum q')(sum p')^T / N   (= sum (q - qbar)(p - pbar)^T)
                 keep[0] = fmaf(-sq0 * inv, sp0, c00); keep[1] = fmaf(-sq0 * inv, sp1, c01); keep[2] = fmaf(-sq0 * inv, sp2, c02);
                 keep[3] = fmaf(-sq1 * inv, sp0, c10); keep[4] = fmaf(-sq1 * inv, sp1, c11); keep[5] = fmaf(-sq1 * inv, sp2, c12);
@@ -174,7 +211,7 @@ __global__ void __launch_bounds__(kKWarps * 32, 1) kabsch_kernel(const KabschPar
                 kpair = pair;
             }
             ++parked;
-            sp0 = sp1 = sp2 = sq0 = sq1 = sq2 = 0.f;
+            sp0 = sp1 = sp2 = sq0 = sq1 = sq2 = sw = 0.f;
             c00 = c01 = c02 = c10 = c11 = c12 = c20 = c21 = c22 = 0.f;
             if (parked == 32) flush();
         }
@@ -191,6 +228,7 @@ int kabsch_launch(KabschParams prm, void* stream) {
     if (prm.b < 0 || prm.npts < 1 || prm.npts > (1 << 24)) return fail(PE_ERR_BAD_ARG, "bad cloud count or cloud size");
     if (prm.b == 0) return 0;
     if (!prm.p || !prm.q || !prm.r) return fail(PE_ERR_BAD_ARG, "null pointer");
+    const bool weighted = prm.w != nullptr;
     int dev = 0;
     cudaError_t e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return fail_cuda(e, "cudaGetDevice");
@@ -201,15 +239,20 @@ int kabsch_launch(KabschParams prm, void* stream) {
         e = cudaGetDeviceProperties(&prop, dev);
         if (e != cudaSuccess) return fail_cuda(e, "cudaGetDeviceProperties");
         if (prop.major < 10) return fail(PE_ERR_NO_DEVICE, "this library is built for sm_100a (B200) only");
-        e = cudaFuncSetAttribute(kabsch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kKSmem);
+        e = cudaFuncSetAttribute(kabsch_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, KGeo<false>::kSmem);
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(kabsch_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, KGeo<true>::kSmem);
         if (e != cudaSuccess) return fail_cuda(e, "cudaFuncSetAttribute(smem)");
         sms[dev] = prop.multiProcessorCount;
     }
     prm.use_tma = (prm.npts % 4 == 0) &&
-                  ((reinterpret_cast<uintptr_t>(prm.p) | reinterpret_cast<uintptr_t>(prm.q)) & 15u) == 0 && !force_direct();
+                  ((reinterpret_cast<uintptr_t>(prm.p) | reinterpret_cast<uintptr_t>(prm.q) |
+                    reinterpret_cast<uintptr_t>(prm.w)) & 15u) == 0 && !force_direct();
     long long grid = (prm.b + kKWarps - 1) / kKWarps;
     if (grid > sms[dev]) grid = sms[dev];
-    kabsch_kernel<<<(unsigned)grid, kKWarps * 32, kKSmem, static_cast<cudaStream_t>(stream)>>>(prm);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (weighted) kabsch_kernel<true><<<(unsigned)grid, kKWarps * 32, KGeo<true>::kSmem, st>>>(prm);
+    else kabsch_kernel<false><<<(unsigned)grid, kKWarps * 32, KGeo<false>::kSmem, st>>>(prm);
     e = cudaGetLastError();
     if (e != cudaSuccess) return fail_cuda(e, "kabsch_kernel");
     count_launch();
@@ -219,14 +262,19 @@ int kabsch_launch(KabschParams prm, void* stream) {
 
 extern "C" int pe_kabsch_fwd(const float* p, const float* q, int64_t b, int64_t npts, float* r, float* t,
                              void* stream) {
-    return kabsch_launch(KabschParams{p, q, r, t, nullptr, 0, (long long)b, (int)npts, 0}, stream);
+    return kabsch_launch(KabschParams{p, q, nullptr, r, t, nullptr, 0, (long long)b, (int)npts, 0}, stream);
 }
 extern "C" int pe_kabsch_fwd_ctx(const float* p, const float* q, int64_t b, int64_t npts, float* r, float* t,
                                  float* ctx, void* stream) {
     if (!ctx) return fail(PE_ERR_BAD_ARG, "null context pointer");
-    return kabsch_launch(KabschParams{p, q, r, t, ctx, 0, (long long)b, (int)npts, 0}, stream);
+    return kabsch_launch(KabschParams{p, q, nullptr, r, t, ctx, 0, (long long)b, (int)npts, 0}, stream);
+}
+extern "C" int pe_kabsch_weighted_fwd(const float* p, const float* q, const float* w, int64_t b, int64_t npts, float* r,
+                                      float* t, float* ctx, void* stream) {
+    if (!w && b > 0) return fail(PE_ERR_BAD_ARG, "null weight pointer");
+    return kabsch_launch(KabschParams{p, q, w, r, t, ctx, 0, (long long)b, (int)npts, 0}, stream);
 }
 extern "C" int pe_cloud_outer_sum(const float* g, const float* p, int64_t b, int64_t npts, float* m, float* gsum,
                                   void* stream) {
-    return kabsch_launch(KabschParams{p, g, m, gsum, nullptr, 1, (long long)b, (int)npts, 0}, stream);
+    return kabsch_launch(KabschParams{p, g, nullptr, m, gsum, nullptr, 1, (long long)b, (int)npts, 0}, stream);
 }

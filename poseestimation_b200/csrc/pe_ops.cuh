@@ -297,6 +297,15 @@ struct KabschBwdCoeffs {
         kabsch_bwd_coeffs(ctx, r, g, ex.inv_n, cq, cp);
     }
 };
+// weighted Kabsch: the context record carries W = sum of the pair's weights as a 16th word; 1/N becomes 1/W
+struct KabschBwdCoeffsW {
+    PE_OP_COMMON("kabsch_weighted_bwd_coeffs", 16, 9, 12, 12, 12, 0, false, 2)
+    using Extra = NoExtra;
+    __device__ static __forceinline__ void run(const float* ctx, const float* r, const float* g, float* cq, float* cp,
+                                               double*, int&, const Extra&) {
+        kabsch_bwd_coeffs(ctx, r, g, ctx[15] > 0.f ? 1.0f / ctx[15] : 0.f, cq, cp);
+    }
+};
 // ---- 8f.2 CosyPose pose update (Iterative/utility.py:90-128): (net output 12, T_init 16) -> T_pred 16 ---------------
 struct Camera {
     float inv_fx, inv_fy;

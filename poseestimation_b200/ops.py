@@ -715,6 +715,92 @@ def _kabsch_backward(ctx, g_r, g_t, _g_c):
 kabsch_ctx.register_autograd(_kabsch_backward, setup_context=_kabsch_setup)
 
 
+# weighted variant (8f.3): per-point weights w >= 0; forward 28 B per point pair, backward one pass over p, q, w that
+# writes only the gradients autograd asks for
+def _weights(w: Tensor, b: int, npts: int) -> Tensor:
+    if w.dtype != torch.float32:
+        raise TypeError("pe_b200 ops compute in float32")
+    if w.shape != (b, npts):
+        raise ValueError(f"expected ({b}, {npts}) weights, got {tuple(w.shape)}")
+    return w.contiguous()
+
+
+@torch.library.custom_op(f"{NS}::kabsch_weighted_ctx", mutates_args=(), device_types="cuda")
+def kabsch_weighted_ctx(p: Tensor, q: Tensor, w: Tensor) -> tuple[Tensor, Tensor, Tensor]:
+    p, q = _clouds(p), _clouds(q)
+    if p.shape != q.shape:
+        raise ValueError(f"expected two (B, N, 3) clouds, got {tuple(p.shape)} and {tuple(q.shape)}")
+    b, npts = p.shape[0], p.shape[1]
+    w = _weights(w, b, npts)
+    r = torch.empty((b, 3, 3), dtype=torch.float32, device=p.device)
+    t = torch.empty((b, 3), dtype=torch.float32, device=p.device)
+    c = torch.empty((b, 16), dtype=torch.float32, device=p.device)
+    if b:
+        with torch.cuda.device(p.device):
+            check(lib.pe_kabsch_weighted_fwd(p.data_ptr(), q.data_ptr(), w.data_ptr(), b, npts, r.data_ptr(),
+                                             t.data_ptr(), c.data_ptr(), _stream()), "pe_kabsch_weighted_fwd")
+    return r, t, c
+
+
+@kabsch_weighted_ctx.register_fake
+def _(p, q, w):
+    b = p.shape[0]
+    return p.new_empty((b, 3, 3)), p.new_empty((b, 3)), p.new_empty((b, 16))
+
+
+@torch.library.custom_op(f"{NS}::kabsch_weighted_bwd", mutates_args=(), device_types="cuda")
+def kabsch_weighted_bwd(p: Tensor, q: Tensor, w: Tensor, r: Tensor, c: Tensor, g_r: Tensor, g_t: Tensor, need_p: bool,
+                        need_q: bool, need_w: bool) -> tuple[Tensor, Tensor, Tensor]:
+    """Gradients that are not needed come back as empty (0,) tensors and are neither computed nor written."""
+    p, q = _clouds(p), _clouds(q)
+    b, npts = p.shape[0], p.shape[1]
+    w = _weights(w, b, npts)
+    g = torch.cat([g_r.reshape(b, 9), g_t.reshape(b, 3)], dim=1).to(torch.float32).contiguous()
+    cq = torch.empty((b, 12), dtype=torch.float32, device=p.device)
+    cp = torch.empty((b, 12), dtype=torch.float32, device=p.device)
+    none = lambda: torch.empty((0,), dtype=torch.float32, device=p.device)
+    dp = torch.empty_like(p) if need_p else none()
+    dq = torch.empty_like(q) if need_q else none()
+    dw = torch.empty_like(w) if need_w else none()
+    if b and npts and (need_p or need_q or need_w):
+        st = _stream()
+        c = c.contiguous()
+        with torch.cuda.device(p.device):
+            check(lib.pe_kabsch_weighted_bwd_coeffs(c.data_ptr(), r.contiguous().data_ptr(), g.data_ptr(), cq.data_ptr(),
+                                                    cp.data_ptr(), b, st), "pe_kabsch_weighted_bwd_coeffs")
+            check(lib.pe_kabsch_weighted_bwd_points(p.data_ptr(), q.data_ptr(), w.data_ptr(), cq.data_ptr(),
+                                                    cp.data_ptr(), c.data_ptr(), b, npts,
+                                                    dp.data_ptr() if need_p else None, dq.data_ptr() if need_q else None,
+                                                    dw.data_ptr() if need_w else None, st),
+                  "pe_kabsch_weighted_bwd_points")
+    return dp, dq, dw
+
+
+@kabsch_weighted_bwd.register_fake
+def _(p, q, w, r, c, g_r, g_t, need_p, need_q, need_w):
+    return (p.new_empty(p.shape if need_p else (0,)), q.new_empty(q.shape if need_q else (0,)),
+            w.new_empty(w.shape if need_w else (0,)))
+
+
+def _kabsch_w_setup(ctx, inputs, output):
+    ctx.save_for_backward(inputs[0], inputs[1], inputs[2], output[0], output[2])
+    ctx.mark_non_differentiable(output[2])
+
+
+def _kabsch_w_backward(ctx, g_r, g_t, _g_c):
+    p, q, w, r, c = ctx.saved_tensors
+    if g_r is None:
+        g_r = torch.zeros_like(r)
+    if g_t is None:
+        g_t = r.new_zeros((r.shape[0], 3))
+    need = ctx.needs_input_grad
+    dp, dq, dw = kabsch_weighted_bwd(p, q, w, r, c, g_r, g_t, need[0], need[1], need[2])
+    return (dp if need[0] else None, dq if need[1] else None, dw if need[2] else None)
+
+
+kabsch_weighted_ctx.register_autograd(_kabsch_w_backward, setup_context=_kabsch_w_setup)
+
+
 # ---------------------------------------------------------------------------------------------------------------------
 # 8f.4  cloud-pair rotation sampler, deterministic part            /root/reference/point_cloud/prepare.py:21-49
 @torch.library.custom_op(f"{NS}::axis_angle_matrix", mutates_args=(), device_types="cuda")

@@ -46,8 +46,14 @@ def make_cloud_pair(pc1, generator=None):
     return gt_rmat, rotate_cloud(gt_rmat, pc1)
 
 
-def kabsch(P, Q):
+def kabsch(P, Q, weights=None):
     """Closed-form alignment of cloud pairs: R (B, 3, 3), t (B, 3) with R p + t ~ q.  Differentiable w.r.t. P and Q
-    (analytic pullback through the covariance and the orthogonalisation; 48 B per point pair in the backward)."""
-    r, t, _ = _ops.kabsch_ctx(P, Q)
+    (analytic pullback through the covariance and the orthogonalisation; 48 B per point pair in the backward).
+
+    ``weights`` (B, N), >= 0: the weighted problem  min sum_k w_k |R p_k + t - q_k|^2  (weighted centroids and
+    covariance), differentiable w.r.t. P, Q and the weights - the layer a correspondence-weighting network feeds."""
+    if weights is None:
+        r, t, _ = _ops.kabsch_ctx(P, Q)
+    else:
+        r, t, _ = _ops.kabsch_weighted_ctx(P, Q, weights)
     return r, t

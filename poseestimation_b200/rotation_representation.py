@@ -186,11 +186,15 @@ def svd_frobenius_loss_and_grad(x, R_true):
     return loss, dx.reshape(x.shape)
 
 
-def kabsch(P, Q):
+def kabsch(P, Q, weights=None):
     """Rotation and translation aligning cloud P onto Q: (B, N, 3) x2 -> ((B, 3, 3), (B, 3)), R p + t ~ q.
 
     Not in the reference; the cloud pair is the (pc1, pc_out) of point_cloud/main.py:171-181.
-    Differentiable w.r.t. both clouds (poseestimation_b200.point_cloud.kabsch is the same function)."""
+    Differentiable w.r.t. both clouds (poseestimation_b200.point_cloud.kabsch is the same function); with
+    ``weights`` (B, N) >= 0 it solves the weighted problem and is differentiable w.r.t. the weights as well."""
+    if weights is not None:
+        r, t, _ = _ops.kabsch_weighted_ctx(P, Q, weights)
+        return r, t
     if torch.is_grad_enabled() and (P.requires_grad or Q.requires_grad):
         r, t, _ = _ops.kabsch_ctx(P, Q)
         return r, t

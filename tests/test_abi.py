@@ -144,6 +144,11 @@ def test_fake_kernels_of_the_8f_ops():
         assert m.shape == (2, 3, 3) and s.shape == (2, 3)
         r, t, ctx = ops.kabsch_ctx(c(2, 16, 3), c(2, 16, 3))
         assert r.shape == (2, 3, 3) and t.shape == (2, 3) and ctx.shape == (2, 15)
+        r, t, ctx = ops.kabsch_weighted_ctx(c(2, 16, 3), c(2, 16, 3), c(2, 16))
+        assert r.shape == (2, 3, 3) and t.shape == (2, 3) and ctx.shape == (2, 16)
+        dp, dq, dw = ops.kabsch_weighted_bwd(c(2, 16, 3), c(2, 16, 3), c(2, 16), r, ctx, c(2, 3, 3), c(2, 3), False,
+                                             True, True)
+        assert dp.shape == (0,) and dq.shape == (2, 16, 3) and dw.shape == (2, 16)
         assert ops.axis_angle_matrix(c(7), c(7, 3)).shape == (7, 3, 3)
         assert ops.pose_update(c(4, 12), c(4, 4, 4), 444.0, 444.0).shape == (4, 4, 4)
         assert ops.pose_update_bwd(c(4, 12), c(4, 4, 4), c(4, 4, 4), 444.0, 444.0).shape == (4, 12)

@@ -17,6 +17,12 @@ def it():
 
 
 @pytest.fixture(scope="module")
+def rr():
+    import poseestimation_b200.rotation_representation as m
+    return m
+
+
+@pytest.fixture(scope="module")
 def pc():
     import poseestimation_b200.point_cloud as m
     return m
@@ -99,6 +105,71 @@ def test_kabsch_backward_matches_oracle_autograd(pc, b, n, noise):
     p64b = p.double().requires_grad_(True)
     (O.kabsch(p64b, q.double())[0] * g_r.double()).sum().backward()
     assert _rel(pd2.grad.cpu(), p64b.grad).max() <= 2e-4
+
+
+@pytest.mark.parametrize("b,n,noise", [(64, 40, 0.05), (9, 1024, 0.01), (40, 257, 0.1), (3, 2048 + 8, 0.02)])
+def test_weighted_kabsch_forward_backward_matches_oracle_autograd(pc, b, n, noise):
+    torch.manual_seed(n + 1)
+    p = (torch.rand(b, n, 3) - 0.5).float()
+    rot = O.sample_rotations_axis_angle(b, torch.Generator().manual_seed(5)).float()
+    q = (p @ rot.transpose(1, 2) + noise * torch.randn(b, n, 3) + torch.randn(b, 1, 3)).float()
+    w = torch.rand(b, n).float()
+    w[:, 1::7] = 0.0                                                      # some correspondences switched off
+    g_r, g_t = torch.randn(b, 3, 3), torch.randn(b, 3)
+    p64, q64, w64 = (x.double().requires_grad_(True) for x in (p, q, w))
+    r64, t64 = O.kabsch_weighted(p64, q64, w64)
+    ((r64 * g_r.double()).sum() + (t64 * g_t.double()).sum()).backward()
+    pd, qd, wd = (x.cuda().requires_grad_(True) for x in (p, q, w))
+    r, t = pc.kabsch(pd, qd, weights=wd)
+    ((r * g_r.cuda()).sum() + (t * g_t.cuda()).sum()).backward()
+    assert np.abs(r.detach().cpu().numpy() - r64.detach().numpy()).max() <= 2e-5
+    assert np.abs(t.detach().cpu().numpy() - t64.detach().numpy()).max() <= 2e-5
+    assert _rel(pd.grad.cpu(), p64.grad).max() <= 2e-4
+    assert _rel(qd.grad.cpu(), q64.grad).max() <= 2e-4
+    assert _rel(wd.grad.cpu(), w64.grad).max() <= 2e-4
+    # only the weights need a gradient (the network-predicted-correspondence case): same dw, nothing else written
+    wd2 = w.cuda().requires_grad_(True)
+    r2, t2 = pc.kabsch(p.cuda(), q.cuda(), weights=wd2)
+    ((r2 * g_r.cuda()).sum() + (t2 * g_t.cuda()).sum()).backward()
+    assert torch.equal(wd2.grad, wd.grad)
+
+
+def test_weighted_kabsch_properties(pc, rr):
+    b, n = 50, 512
+    g = torch.Generator(device="cuda").manual_seed(8)
+    p = torch.rand(b, n, 3, device="cuda", generator=g) - 0.5
+    rot, q = pc.make_cloud_pair(p, generator=g)
+    q = q + torch.randn(b, 1, 3, device="cuda", generator=g)
+    # unit weights == the plain kernel; a common factor on the weights changes nothing
+    r0, t0 = pc.kabsch(p, q)
+    r1, t1 = pc.kabsch(p, q, weights=torch.ones(b, n, device="cuda"))
+    assert float((r1 - r0).abs().max()) <= 2e-6 and float((t1 - t0).abs().max()) <= 2e-6
+    w = torch.rand(b, n, device="cuda", generator=g)
+    ra, ta = pc.kabsch(p, q, weights=w)
+    rb, tb = pc.kabsch(p, q, weights=w * 8.0)
+    assert float((ra - rb).abs().max()) <= 2e-6 and float((ta - tb).abs().max()) <= 2e-6
+    assert float((ra - rot).abs().max()) <= 2e-5
+    # gross outliers with zero weight are ignored
+    qo = q.clone()
+    qo[:, ::4] += 50.0
+    wo = torch.ones(b, n, device="cuda")
+    wo[:, ::4] = 0.0
+    ro, to = rr.kabsch(p, qo, weights=wo)
+    assert float((ro - rot).abs().max()) <= 2e-5 and float((to - t0).abs().max()) <= 5e-5
+    # all-zero weights: a finite rotation, not NaN
+    rz, tz = pc.kabsch(p[:3], q[:3], weights=torch.zeros(3, n, device="cuda"))
+    assert bool(torch.isfinite(rz).all()) and bool(torch.isfinite(tz).all())
+    assert float((torch.bmm(rz, rz.transpose(1, 2)) - torch.eye(3, device="cuda")).abs().max()) <= 1e-5
+    # direct (non-TMA) kernels give the same bits as the staged ones
+    import os
+    os.environ["PE_FORCE_DIRECT"] = "1"
+    try:
+        rd, td = pc.kabsch(p, q, weights=w)
+    finally:
+        del os.environ["PE_FORCE_DIRECT"]
+    assert float((rd - ra).abs().max()) <= 2e-6 and float((td - ta).abs().max()) <= 2e-6
+    with pytest.raises((ValueError, RuntimeError)):
+        pc.kabsch(p, q, weights=torch.ones(b, n + 1, device="cuda"))
 
 
 # ---- 8f.2 CosyPose pose update and ADD-L1 ----------------------------------------------------------------------------

@@ -189,6 +189,38 @@ def test_config4_kabsch_backward_directional_derivative(rr, pc):
             assert abs(lhs - rhs) <= 3e-2 * abs(rhs), (which, lhs, rhs)
 
 
+def test_config4_weighted_kabsch(rr, pc):
+    """65 536 x 1024 with per-point weights: outliers carrying zero weight do not move the answer; the gradient w.r.t.
+    the weights is the directional derivative of the loss."""
+    b, npts = 65536, 1024
+    g = torch.Generator(device="cuda").manual_seed(9)
+    p = torch.rand(b, npts, 3, device="cuda", generator=g) - 0.5
+    rot, q = pc.make_cloud_pair(p, generator=g)
+    w = torch.rand(b, npts, device="cuda", generator=g) + 0.05
+    bad = torch.rand(b, npts, device="cuda", generator=g) < 0.1
+    q = torch.where(bad.unsqueeze(2), q + 3.0, q)
+    r, t = pc.kabsch(p, q, weights=torch.where(bad, torch.zeros_like(w), w))
+    assert float((r - rot).abs().max()) <= 2e-5 and float(t.abs().max()) <= 2e-5
+    # now let the outliers count a little: loss > 0 and it has a gradient w.r.t. the weights
+    w = torch.where(bad, 0.02 * w, w).requires_grad_(True)
+
+    def loss_of(ww):
+        r_, t_ = pc.kabsch(p, q, weights=ww)
+        return rr.loss_frobenius(r_, rot) + t_.abs().mean()
+
+    loss_of(w).backward()
+    gw = w.grad
+    assert gw.shape == w.shape and bool(torch.isfinite(gw).all())
+    # raising an outlier's weight must hurt, on average
+    assert float(gw[bad].mean()) > 0
+    with torch.no_grad():
+        v = gw / gw.norm(dim=1, keepdim=True).clamp_min(1e-30)
+        lhs = (gw.double() * v.double()).sum().item()
+        eps = 2e-3
+        rhs = (loss_of(w + eps * v).item() - loss_of(w - eps * v).item()) / (2 * eps)
+        assert abs(lhs - rhs) <= 3e-2 * abs(rhs), (lhs, rhs)
+
+
 def _reference_formula_add_l1(t_gt, t_pred, pts):
     """Iterative/loss.py:10-28 / :51-69 written with torch ops (homogeneous points times T^T, mean |.| over N and xyz)."""
     ones = torch.ones(pts.shape[0], pts.shape[1], 1, device=pts.device)

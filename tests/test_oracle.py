@@ -116,6 +116,35 @@ def test_kabsch_recovers_reference_rotation(golden):
     assert np.abs(r2.numpy() - z["gt_rmat"]).max() < 1e-5
 
 
+def test_weighted_kabsch_restatement(golden):
+    """No reference function: unit weights reduce to the plain alignment, integer weights to repeated
+    points, zero weights remove outliers, and a scaling of all weights changes nothing."""
+    z = golden("kabsch_kat")
+    p, q = T(z["pc1"]).double(), T(z["pc2"]).double()
+    b, n = p.shape[0], p.shape[1]
+    r0, t0 = O.kabsch(p, q)
+    r1, t1 = O.kabsch_weighted(p, q, torch.ones(b, n))
+    assert (r1 - r0).abs().max() < 1e-12 and (t1 - t0).abs().max() < 1e-12
+    g = torch.Generator().manual_seed(4)
+    qn = q + 0.05 * torch.randn(q.shape, generator=g, dtype=torch.float64)
+    k = torch.randint(0, 4, (b, n), generator=g)
+    k[:, 0] = 1
+    rw, tw = O.kabsch_weighted(p, qn, k.double())
+    for i in range(min(b, 4)):                                            # repeat point j k[i, j] times
+        idx = torch.repeat_interleave(torch.arange(n), k[i])
+        ri, ti = O.kabsch(p[i:i + 1, idx], qn[i:i + 1, idx])
+        assert (ri - rw[i:i + 1]).abs().max() < 1e-10 and (ti - tw[i:i + 1]).abs().max() < 1e-10
+    rs, ts = O.kabsch_weighted(p, qn, 7.5 * k.double())
+    assert (rs - rw).abs().max() < 1e-12 and (ts - tw).abs().max() < 1e-12
+    # gross outliers with zero weight do not move the answer
+    qo = q.clone()
+    qo[:, ::5] += 100.0
+    w = torch.ones(b, n, dtype=torch.float64)
+    w[:, ::5] = 0
+    ro, to = O.kabsch_weighted(p, qo, w)
+    assert np.abs(ro.numpy() - z["gt_rmat"]).max() < 1e-5 and to.abs().max() < 1e-5
+
+
 def test_sampler_gives_rotations():
     g = torch.Generator().manual_seed(0)
     r = O.sample_rotations_axis_angle(64, g).numpy()

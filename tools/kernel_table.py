@@ -99,6 +99,16 @@ def main():
         units=b * npts, unit_name="point")
     add("cloud_outer_sum (dA, dt of affine)", 24 * npts + 48, lambda: check(lib.pe_cloud_outer_sum(P(qc), P(pc), b, npts, P(rk), P(tk), st), ""),
         units=b, unit_name="pair")
+    wk = torch.rand(b, npts, device=dev, generator=g)
+    ctxw, dwk, oc2 = torch.empty(b, 16, device=dev), torch.empty(b, npts, device=dev), torch.empty(b, npts, 3, device=dev)
+    add("kabsch_weighted_fwd + context", 28 * npts + 112, lambda: check(lib.pe_kabsch_weighted_fwd(P(pc), P(qc), P(wk), b, npts, P(rk), P(tk), P(ctxw), st), ""),
+        units=b, unit_name="pair")
+    check(lib.pe_kabsch_weighted_bwd_coeffs(P(ctxw), P(rk), P(gk), P(cq), P(cp), b, st), "")
+    add("kabsch_weighted_bwd_points (dp, dq, dw)", 56, lambda: check(lib.pe_kabsch_weighted_bwd_points(P(pc), P(qc), P(wk), P(cq), P(cp), P(ctxw), b, npts, P(oc), P(oc2), P(dwk), st), ""),
+        units=b * npts, unit_name="point")
+    add("kabsch_weighted_bwd_points (dw only)", 32, lambda: check(lib.pe_kabsch_weighted_bwd_points(P(pc), P(qc), P(wk), P(cq), P(cp), P(ctxw), b, npts, None, None, P(dwk), st), ""),
+        units=b * npts, unit_name="point")
+    del wk, dwk, oc2
     tg = torch.eye(4, device=dev).repeat(b, 1, 1) + 0.1 * torch.randn(b, 4, 4, device=dev, generator=g)
     tp = torch.eye(4, device=dev).repeat(b, 1, 1) + 0.1 * torch.randn(b, 4, 4, device=dev, generator=g)
     item, gsd = torch.empty(b, device=dev), torch.empty(b, 12, device=dev)
