@@ -29,7 +29,8 @@ extern "C" {
 
 #define PE_VERSION 100 /* 0.1.0 */
 
-#define PE_ERR_BAD_ARG (-1)   /* null pointer, negative count, stride smaller than the record */
+#define PE_ERR_BAD_ARG (-1)   /* null pointer, negative count, stride smaller than the record, array not naturally
+                                 aligned (float: 4 bytes, double: 8 bytes) */
 #define PE_ERR_NO_DEVICE (-2) /* current device is not sm_100 */
 #define PE_ERR_INTERNAL (-3)
 

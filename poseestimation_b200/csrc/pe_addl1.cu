@@ -165,6 +165,7 @@ using namespace pe;
 extern "C" int pe_add_l1(const float* t_gt, const float* t_pred, const float* pts, int64_t b, int64_t npts,
                          int disentangled, float* item, double* sum, float* grad, void* stream) {
     if (b < 0 || npts < 1 || npts > (1 << 24)) return fail(PE_ERR_BAD_ARG, "bad item count or vertex count");
+    if (reinterpret_cast<uintptr_t>(sum) & 7u) return fail(PE_ERR_BAD_ARG, "float64 accumulator not aligned to 8 bytes");
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (sum) {
         cudaError_t e0 = cudaMemsetAsync(sum, 0, sizeof(double), st);

@@ -25,6 +25,11 @@ int run(const float* i0, long long stride0, const float* i1, const float* i2, fl
         double* sums, int* flag, typename Op::Extra ex, void* stream) {
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (n < 0) return fail(PE_ERR_BAD_ARG, "negative record count");
+    // natural alignment of every array (a misaligned access would be a sticky device fault, not an error code)
+    if ((reinterpret_cast<uintptr_t>(i0) | reinterpret_cast<uintptr_t>(i1) | reinterpret_cast<uintptr_t>(i2) |
+         reinterpret_cast<uintptr_t>(o0) | reinterpret_cast<uintptr_t>(o1) | reinterpret_cast<uintptr_t>(flag)) & 3u)
+        return fail(PE_ERR_BAD_ARG, "array not aligned to 4 bytes");
+    if (reinterpret_cast<uintptr_t>(sums) & 7u) return fail(PE_ERR_BAD_ARG, "float64 accumulator not aligned to 8 bytes");
     if (Op::NRED > 0) {
         if (!sums) return fail(PE_ERR_BAD_ARG, "null accumulator pointer");
         cudaError_t e = cudaMemsetAsync(sums, 0, sizeof(double) * Op::NRED, st);
@@ -139,6 +144,7 @@ int pe_geodesic_bwd(const float* m1, const float* m2, float lo, float hi, const 
 
 int pe_angle_error_fwd(const float* r1, const float* r2, double* deg, double* sum, int* flag, int64_t n,
                        void* stream) {
+    if (reinterpret_cast<uintptr_t>(deg) & 7u) return fail(PE_ERR_BAD_ARG, "float64 output not aligned to 8 bytes");
     float* d = reinterpret_cast<float*>(deg);
     if (deg && sum) return run<AngleFwd<true, true>>(r1, 9, r2, nullptr, d, nullptr, n, sum, flag, {}, stream);
     if (deg) return run<AngleFwd<true, false>>(r1, 9, r2, nullptr, d, nullptr, n, nullptr, flag, {}, stream);

@@ -73,6 +73,12 @@ def test_version_and_error_convention(built):
     with pytest.raises(RuntimeError, match="bad call -1"):
         _lib.check(rc, "pe_svd_orth_fwd")
     assert _lib.lib.pe_kabsch_fwd(None, None, 4, 0, None, None, None) == -1
+    # misaligned arrays are an error code, not a device fault (checked before any CUDA call)
+    assert _lib.lib.pe_frobenius_fwd(1024, 2048, 4096 + 4, 1, None) == -1
+    assert b"8 bytes" in _lib.lib.pe_last_error()
+    assert _lib.lib.pe_euler_fwd(1024 + 2, 3, 2048, 1, None) == -1
+    assert _lib.lib.pe_angle_error_fwd(1024, 2048, 4096 + 4, None, 8192, 1, None) == -1
+    assert _lib.lib.pe_add_l1(1024, 2048, 4096, 1, 8, 0, None, 8192 + 4, None, None) == -1
 
 
 def test_no_cpu_fallback():
