@@ -11,15 +11,26 @@
 // vertices (12 B per vertex) gives the loss and, from the same pass, the sums that make up its gradient w.r.t.
 // T_pred:  d/dR_ij = -sum_k sgn(d_ki) p_kj / (3N),  d/dt_i = -sum_k sgn(d_ki) / (3N).
 //
-// Layout: one WARP per item (pose pair + its vertices), lane 0 streams the vertices through a warp-private TMA ring,
-// lanes read vertices at a 3-word stride (conflict-free), 13 running sums per lane, butterfly reduction.
+// Layout: one WARP per item (pose pair + its vertices), lane 0 streams the vertices through a warp-private TMA ring.
+// The loop is issue-bound before it is HBM-bound (13 accumulator chains per vertex), so each lane takes TWO vertices
+// per step (v and v + 32 of a 64-vertex group, 3-word lane stride: conflict-free) and runs the whole update in packed
+// fp32x2 arithmetic: 9 FFMA2 for the residuals, |e| = sgn(e) e as one FFMA2 per row, 9 FFMA2 + 3 FADD2 for the
+// gradient sums.  The 13 sums are reduced across the warp with a transposing butterfly (16 + 8 + 4 + 2 + 1 shuffles
+// instead of 13 x 5) that leaves sum j in lane 2j, and those lanes write the outputs.
 #include "pe_common.h"
+#include "pe_lanes.cuh"
 #include "pe_stage.cuh"
 
 namespace pe {
 
-constexpr int kAWarps = 32;   // 12 B per vertex: twice the vertex rate of the Kabsch kernel for the same GB/s; the kernel
-constexpr int kAStages = 2;   // is latency-bound on its 13 accumulator chains, so it runs the full 32 warps per SM
+#ifndef PE_AWARPS
+#define PE_AWARPS 16
+#endif
+#ifndef PE_ASTAGES
+#define PE_ASTAGES 3
+#endif
+constexpr int kAWarps = PE_AWARPS;
+constexpr int kAStages = PE_ASTAGES;
 constexpr int kAChunk = 256;  // vertices per stage (3 KB)
 constexpr int kAStageWords = kAChunk * 3;
 constexpr int kASmem = 1024 + kAWarps * kAStages * kAStageWords * 4;
@@ -37,12 +48,49 @@ struct AddL1Params {
     int use_tma;
 };
 
-__device__ __forceinline__ float wsum(float v) {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    return v;
+// sign with sgn(0) = 0, as torch.sign in the backward of abs(): LOP3 + FSETP + FSEL
+__device__ __forceinline__ float sgn(float v) {
+    const float s = __int_as_float((__float_as_int(v) & 0x80000000) | 0x3f800000);
+    return v != 0.f ? s : 0.f;
 }
-__device__ __forceinline__ float sgn(float v) { return v > 0.f ? 1.f : (v < 0.f ? -1.f : 0.f); }
+
+struct AddL1Acc {
+    F2 s[9], sv[3], acc;
+};
+
+// two vertices (x, y, z hold one coordinate of each); MASKED: lanes of a ragged tail switch a vertex off through va / vb
+template <bool MASKED>
+__device__ __forceinline__ void add_l1_pair(const F2* d, const F2* dt, F2 x, F2 y, F2 z, bool va, bool vb, AddL1Acc& a) {
+    F2 e0 = t_fma(d[2], z, t_fma(d[1], y, t_fma(d[0], x, dt[0])));
+    F2 e1 = t_fma(d[5], z, t_fma(d[4], y, t_fma(d[3], x, dt[1])));
+    F2 e2 = t_fma(d[8], z, t_fma(d[7], y, t_fma(d[6], x, dt[2])));
+    F2 g0{sgn(e0.x), sgn(e0.y)}, g1{sgn(e1.x), sgn(e1.y)}, g2{sgn(e2.x), sgn(e2.y)};
+    if constexpr (MASKED) {
+        if (!va) { g0.x = 0.f; g1.x = 0.f; g2.x = 0.f; }
+        if (!vb) { g0.y = 0.f; g1.y = 0.f; g2.y = 0.f; }
+    }
+    a.acc = t_fma(g0, e0, a.acc); a.acc = t_fma(g1, e1, a.acc); a.acc = t_fma(g2, e2, a.acc);  // |e| = sgn(e) e
+    a.s[0] = t_fma(g0, x, a.s[0]); a.s[1] = t_fma(g0, y, a.s[1]); a.s[2] = t_fma(g0, z, a.s[2]);
+    a.s[3] = t_fma(g1, x, a.s[3]); a.s[4] = t_fma(g1, y, a.s[4]); a.s[5] = t_fma(g1, z, a.s[5]);
+    a.s[6] = t_fma(g2, x, a.s[6]); a.s[7] = t_fma(g2, y, a.s[7]); a.s[8] = t_fma(g2, z, a.s[8]);
+    a.sv[0] = t_add(a.sv[0], g0); a.sv[1] = t_add(a.sv[1], g1); a.sv[2] = t_add(a.sv[2], g2);
+}
+
+// v[0..15] per lane -> the warp total of v[j] in lanes 2j and 2j + 1 (returned): 31 shuffles for 16 sums
+__device__ __forceinline__ float transpose_reduce16(float* v, int lane) {
+#pragma unroll
+    for (int o = 16; o >= 2; o >>= 1) {
+        const int half = o >> 1;  // values kept after this step
+        const bool up = (lane & o) != 0;
+#pragma unroll
+        for (int i = 0; i < half; ++i) {
+            const float send = up ? v[i] : v[i + half];
+            const float keep = up ? v[i + half] : v[i];
+            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, o);
+        }
+    }
+    return v[0] + __shfl_xor_sync(0xffffffffu, v[0], 1);
+}
 
 template <bool TMA>
 __global__ void __launch_bounds__(kAWarps * 32, 1) add_l1_kernel(const AddL1Params prm) {
@@ -57,15 +105,20 @@ __global__ void __launch_bounds__(kAWarps * 32, 1) add_l1_kernel(const AddL1Para
     const int cpi = (npts + kAChunk - 1) / kAChunk;  // chunks per item
     const long long my_items = gw < prm.b ? (prm.b - gw + nwarps - 1) / nwarps : 0;
     const long long steps = my_items * cpi;
+    const float k3n = 1.0f / (3.0f * (float)npts);
     uint64_t policy = 0;
 
-    auto issue = [&](int s, long long j) {  // lane 0: chunk (j % cpi) of this warp's item number (j / cpi)
-        long long it = gw + (j / cpi) * nwarps;
-        int ch = (int)(j % cpi);
-        int cnt = min(kAChunk, npts - ch * kAChunk);
+    // lane 0: the next chunk to fetch is chunk iss_ch of item iss_it (kept incrementally: a 64-bit division per
+    // chunk costs more instructions than the chunk's arithmetic)
+    long long iss_it = gw;
+    int iss_ch = 0;
+    auto issue = [&](int s) {
+        int cnt = min(kAChunk, npts - iss_ch * kAChunk);
         uint32_t bytes = (uint32_t)cnt * 12u;
         mbar_arrive_expect_tx(&bars[s], bytes);
-        bulk_g2s(ring + s * kAStageWords, prm.pts + (it * npts + (long long)ch * kAChunk) * 3, bytes, &bars[s], policy);
+        bulk_g2s(ring + s * kAStageWords, prm.pts + (iss_it * npts + (long long)iss_ch * kAChunk) * 3, bytes, &bars[s],
+                 policy);
+        if (++iss_ch == cpi) { iss_ch = 0; iss_it += nwarps; }
     };
     if constexpr (TMA) {
         if (lane == 0) {
@@ -73,89 +126,112 @@ __global__ void __launch_bounds__(kAWarps * 32, 1) add_l1_kernel(const AddL1Para
             for (int s = 0; s < kAStages; ++s) mbar_init(&bars[s], 1);
             mbar_init_fence();
             for (int s = 0; s < kAStages; ++s)
-                if (s < steps) issue(s, s);
+                if (s < steps) issue(s);
         }
         __syncwarp();
     }
 
-    double warp_total = 0.0;  // lane 0 only
-    long long j = 0;          // running chunk counter of this warp (ring position)
-    for (long long it = gw; it < prm.b; it += nwarps) {
-        // R_gt - R_pred and t_gt - t_pred (the latter is dropped from the vertex term of the disentangled loss)
-        float d[9], dt[3], tdelta[3];
-        {
-            const float* a = prm.t_gt + it * 16;
-            const float* c = prm.t_pred + it * 16;
-#pragma unroll
-            for (int i = 0; i < 3; ++i) {
-#pragma unroll
-                for (int k = 0; k < 3; ++k) d[3 * i + k] = __ldg(a + 4 * i + k) - __ldg(c + 4 * i + k);
-                tdelta[i] = __ldg(a + 4 * i + 3) - __ldg(c + 4 * i + 3);
-                dt[i] = prm.disentangled ? 0.f : tdelta[i];
-            }
+    // lanes 0..11 fetch one entry each of (T_gt - T_pred)[:3, :4] of an item: 0..8 the rotation block row-major, 9..11
+    // the translation column.  The fetch for the NEXT item is issued at the top of the current one, so its latency
+    // hides behind a whole item of vertex work instead of stalling the warp while its ring sits full.
+    const int poff = lane < 9 ? 4 * (lane / 3) + lane % 3 : 4 * (lane - 9) + 3;
+    // (the two loaded words are only subtracted when the item starts: a subtraction at fetch time would wait for them)
+    auto fetch_pose = [&](long long item, float& a, float& c) {
+        a = c = 0.f;
+        if (lane < 12 && item < prm.b) {
+            a = __ldg(prm.t_gt + item * 16 + poff);
+            c = __ldg(prm.t_pred + item * 16 + poff);
         }
-        float acc = 0.f, S[9], sv[3];
+    };
+    float cur_a, cur_c;
+    fetch_pose(gw, cur_a, cur_c);
+
+    double warp_total = 0.0;  // lane 24 only (the lane that ends up with the loss)
+    long long j = 0;          // running chunk counter of this warp
+    int s = 0;                // ring position of chunk j (j % kAStages)
+    uint32_t phase = 0;       // its mbarrier parity ((j / kAStages) & 1)
+    for (long long it = gw; it < prm.b; it += nwarps) {
+        const float cur = cur_a - cur_c;
+        fetch_pose(it + nwarps, cur_a, cur_c);  // in flight for the whole item
+        // R_gt - R_pred and t_gt - t_pred (the latter is dropped from the vertex term of the disentangled loss)
+        F2 d[9], dt[3];
+        float tdelta[3];
 #pragma unroll
-        for (int i = 0; i < 9; ++i) S[i] = 0.f;
-        sv[0] = sv[1] = sv[2] = 0.f;
+        for (int i = 0; i < 9; ++i) {
+            const float v = __shfl_sync(0xffffffffu, cur, i);
+            d[i] = F2{v, v};
+        }
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+            tdelta[i] = __shfl_sync(0xffffffffu, cur, 9 + i);
+            const float v = prm.disentangled ? 0.f : tdelta[i];
+            dt[i] = F2{v, v};
+        }
+        AddL1Acc acc;
+#pragma unroll
+        for (int i = 0; i < 9; ++i) acc.s[i] = F2{0.f, 0.f};
+        acc.sv[0] = acc.sv[1] = acc.sv[2] = acc.acc = F2{0.f, 0.f};
 
         for (int ch = 0; ch < cpi; ++ch, ++j) {
-            const int s = (int)(j % kAStages);
             const int cnt = min(kAChunk, npts - ch * kAChunk);
             const float* sp;
             if constexpr (TMA) {
-                mbar_wait(&bars[s], (uint32_t)((j / kAStages) & 1));
+                mbar_wait(&bars[s], phase);
                 sp = ring + s * kAStageWords;
             } else {
                 sp = prm.pts + (it * npts + (long long)ch * kAChunk) * 3;
             }
-#pragma unroll 4
-            for (int k = lane; k < cnt; k += 32) {
-                float x = sp[3 * k], y = sp[3 * k + 1], z = sp[3 * k + 2];
-                float e0 = fmaf(d[2], z, fmaf(d[1], y, fmaf(d[0], x, dt[0])));
-                float e1 = fmaf(d[5], z, fmaf(d[4], y, fmaf(d[3], x, dt[1])));
-                float e2 = fmaf(d[8], z, fmaf(d[7], y, fmaf(d[6], x, dt[2])));
-                acc += fabsf(e0) + fabsf(e1) + fabsf(e2);
-                float g0 = sgn(e0), g1 = sgn(e1), g2 = sgn(e2);
-                S[0] = fmaf(g0, x, S[0]); S[1] = fmaf(g0, y, S[1]); S[2] = fmaf(g0, z, S[2]);
-                S[3] = fmaf(g1, x, S[3]); S[4] = fmaf(g1, y, S[4]); S[5] = fmaf(g1, z, S[5]);
-                S[6] = fmaf(g2, x, S[6]); S[7] = fmaf(g2, y, S[7]); S[8] = fmaf(g2, z, S[8]);
-                sv[0] += g0; sv[1] += g1; sv[2] += g2;
+            int k = 0;
+#pragma unroll 2
+            for (; k + 64 <= cnt; k += 64) {
+                const float* pa = sp + 3 * (k + lane);
+                const float* pb = pa + 96;
+                add_l1_pair<false>(d, dt, F2{pa[0], pb[0]}, F2{pa[1], pb[1]}, F2{pa[2], pb[2]}, true, true, acc);
+            }
+            if (k < cnt) {  // ragged tail of the item: fewer than 64 vertices left
+                const bool va = k + lane < cnt, vb = k + 32 + lane < cnt;
+                const float* pa = sp + 3 * (k + lane);
+                const float* pb = pa + 96;
+                F2 x{va ? pa[0] : 0.f, vb ? pb[0] : 0.f}, y{va ? pa[1] : 0.f, vb ? pb[1] : 0.f},
+                    z{va ? pa[2] : 0.f, vb ? pb[2] : 0.f};
+                add_l1_pair<true>(d, dt, x, y, z, va, vb, acc);
             }
             if constexpr (TMA) {
                 __syncwarp();
-                if (lane == 0 && j + kAStages < steps) issue(s, j + kAStages);
+                if (lane == 0 && j + kAStages < steps) issue(s);
             }
+            if (++s == kAStages) { s = 0; phase ^= 1u; }
         }
         __syncwarp();
-        acc = wsum(acc);
+        float v[16];
 #pragma unroll
-        for (int i = 0; i < 9; ++i) S[i] = wsum(S[i]);
-        sv[0] = wsum(sv[0]); sv[1] = wsum(sv[1]); sv[2] = wsum(sv[2]);
-        if (lane == 0) {
-            const float k3n = 1.0f / (3.0f * (float)npts);
-            float loss = acc * k3n;
-            float gt3[3] = {-sv[0] * k3n, -sv[1] * k3n, -sv[2] * k3n};
-            if (prm.disentangled) {
-                // transl pose: (x, y) of T_pred, depth pose: z of T_pred - constant per-vertex distances
-                loss += (fabsf(tdelta[0]) + fabsf(tdelta[1]) + fabsf(tdelta[2])) * (1.0f / 3.0f);
-                gt3[0] = -sgn(tdelta[0]) * (1.0f / 3.0f);
-                gt3[1] = -sgn(tdelta[1]) * (1.0f / 3.0f);
-                gt3[2] = -sgn(tdelta[2]) * (1.0f / 3.0f);
-            }
-            if (prm.item) prm.item[it] = loss;
-            warp_total += (double)loss;
-            if (prm.grad) {
+        for (int i = 0; i < 9; ++i) v[i] = acc.s[i].x + acc.s[i].y;
+#pragma unroll
+        for (int i = 0; i < 3; ++i) v[9 + i] = acc.sv[i].x + acc.sv[i].y;
+        v[12] = acc.acc.x + acc.acc.y;
+        v[13] = v[14] = v[15] = 0.f;
+        const float tot = transpose_reduce16(v, lane);
+        const int jv = lane >> 1;  // which sum this lane holds
+        if ((lane & 1) == 0 && jv < 13) {
+            if (jv == 12) {
+                float loss = tot * k3n;
+                if (prm.disentangled)  // transl pose: (x, y) of T_pred, depth pose: z of T_pred - constant distances
+                    loss += (fabsf(tdelta[0]) + fabsf(tdelta[1]) + fabsf(tdelta[2])) * (1.0f / 3.0f);
+                if (prm.item) prm.item[it] = loss;
+                warp_total += (double)loss;
+            } else if (prm.grad) {
                 float* gd = prm.grad + it * 12;
-#pragma unroll
-                for (int i = 0; i < 3; ++i) {
-                    gd[4 * i] = -S[3 * i] * k3n; gd[4 * i + 1] = -S[3 * i + 1] * k3n; gd[4 * i + 2] = -S[3 * i + 2] * k3n;
-                    gd[4 * i + 3] = gt3[i];
+                if (jv < 9) {
+                    gd[4 * (jv / 3) + jv % 3] = -tot * k3n;
+                } else {
+                    const int i = jv - 9;
+                    const float td = i == 0 ? tdelta[0] : (i == 1 ? tdelta[1] : tdelta[2]);
+                    gd[4 * i + 3] = prm.disentangled ? -sgn(td) * (1.0f / 3.0f) : -tot * k3n;
                 }
             }
         }
     }
-    if (prm.sum && lane == 0 && my_items > 0) atomicAdd(prm.sum, warp_total);
+    if (prm.sum && lane == 24 && my_items > 0) atomicAdd(prm.sum, warp_total);
 }
 
 }  // namespace pe

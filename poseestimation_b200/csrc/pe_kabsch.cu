@@ -73,9 +73,13 @@ __global__ void __launch_bounds__(kKWarps * 32, 1) kabsch_kernel(const KabschPar
     }
     __syncwarp();
 
-    auto issue = [&](int s, long long item) {
-        long long pair = gw + (item / cpp) * nwarps;
-        int ch = (int)(item % cpp);
+    // lane 0: the next chunk to fetch is chunk iss_ch of pair iss_pair (kept incrementally: no 64-bit divisions)
+    long long iss_pair = gw;
+    int iss_ch = 0;
+    auto issue = [&](int s) {
+        const long long pair = iss_pair;
+        const int ch = iss_ch;
+        if (++iss_ch == cpp) { iss_ch = 0; iss_pair += nwarps; }
         int cnt = min(kChunk, npts - ch * kChunk);
         uint32_t bytes = (uint32_t)cnt * 12u;
         long long off = (pair * npts + (long long)ch * kChunk) * 3;
@@ -89,7 +93,7 @@ __global__ void __launch_bounds__(kKWarps * 32, 1) kabsch_kernel(const KabschPar
     };
     if (tma && lane == 0) {
         for (int s = 0; s < kKStages; ++s)
-            if (s < items) issue(s, s);
+            if (s < items) issue(s);
     }
 
     float sp0 = 0, sp1 = 0, sp2 = 0, sq0 = 0, sq1 = 0, sq2 = 0;
@@ -140,11 +144,10 @@ __global__ void __launch_bounds__(kKWarps * 32, 1) kabsch_kernel(const KabschPar
         parked = 0;
     };
 
+    int s = 0, ch = 0;        // ring position and chunk-in-pair of item j, kept incrementally
+    uint32_t parity = 0;
+    long long pair = gw;
     for (long long j = 0; j < items; ++j) {
-        const int s = (int)(j % kKStages);
-        const uint32_t parity = (uint32_t)((j / kKStages) & 1);
-        const long long pair = gw + (j / cpp) * nwarps;
-        const int ch = (int)(j % cpp);
         const int cnt = min(kChunk, npts - ch * kChunk);
         const float* sP;
         const float* sQ;
@@ -187,9 +190,10 @@ __global__ void __launch_bounds__(kKWarps * 32, 1) kabsch_kernel(const KabschPar
             c20 = fmaf(b2, a0, c20); c21 = fmaf(b2, a1, c21); c22 = fmaf(b2, a2, c22);
         }
         __syncwarp();  // every lane is done with stage s
-        if (tma && lane == 0 && j + kKStages < items) issue(s, j + kKStages);
+        if (tma && lane == 0 && j + kKStages < items) issue(s);
+        const bool last_chunk = ch == cpp - 1;
 
-        if (ch == cpp - 1) {
+        if (last_chunk) {
             sp0 = warp_sum_f(sp0); sp1 = warp_sum_f(sp1); sp2 = warp_sum_f(sp2);
             sq0 = warp_sum_f(sq0); sq1 = warp_sum_f(sq1); sq2 = warp_sum_f(sq2);
             c00 = warp_sum_f(c00); c01 = warp_sum_f(c01); c02 = warp_sum_f(c02);
@@ -215,6 +219,8 @@ __global__ void __launch_bounds__(kKWarps * 32, 1) kabsch_kernel(const KabschPar
             c00 = c01 = c02 = c10 = c11 = c12 = c20 = c21 = c22 = 0.f;
             if (parked == 32) flush();
         }
+        if (++s == kKStages) { s = 0; parity ^= 1u; }
+        if (++ch == cpp) { ch = 0; pair += nwarps; }
     }
     if (parked > 0) flush();
 }
