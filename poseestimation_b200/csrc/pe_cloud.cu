@@ -54,6 +54,20 @@ __device__ __forceinline__ void apply(const float* m, const float* t, float x, f
     oz = fmaf(m[8], z, fmaf(m[7], y, fmaf(m[6], x, t[2])));
 }
 
+// Grid-stride walk over (cloud, position in cloud) without a 64-bit division per step (each is ~100 instructions):
+// one division when the thread starts, then cloud += step / per, pos += step % per with a carry.
+struct CloudWalk {
+    long long cloud, pos, dq, dr, per;
+    __device__ __forceinline__ CloudWalk(long long first, long long step, long long per_) : per(per_) {
+        cloud = first / per; pos = first - cloud * per;
+        dq = step / per; dr = step - dq * per;
+    }
+    __device__ __forceinline__ void next() {
+        cloud += dq; pos += dr;
+        if (pos >= per) { pos -= per; ++cloud; }
+    }
+};
+
 // npts % 4 == 0 and 16-byte aligned arrays: one thread = 4 points of one cloud
 __global__ void __launch_bounds__(256) affine_points_vec4_kernel(const AffineParams prm) {
     const long long groups = prm.b * prm.npts / 4;
@@ -61,9 +75,11 @@ __global__ void __launch_bounds__(256) affine_points_vec4_kernel(const AffinePar
     const long long step = (long long)gridDim.x * blockDim.x;
     const float4* src = reinterpret_cast<const float4*>(prm.p);
     float4* dst = reinterpret_cast<float4*>(prm.out);
-    for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < groups; g += step) {
+    const long long first = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    CloudWalk walk(first, step, gpc);
+    for (long long g = first; g < groups; g += step, walk.next()) {
         float m[9], t[3];
-        load_coeffs(prm, g / gpc, m, t);
+        load_coeffs(prm, walk.cloud, m, t);
         float4 v0 = __ldcs(src + 3 * g), v1 = __ldcs(src + 3 * g + 1), v2 = __ldcs(src + 3 * g + 2);
         float4 o0, o1, o2;
         apply(m, t, v0.x, v0.y, v0.z, o0.x, o0.y, o0.z);
@@ -78,9 +94,11 @@ __global__ void __launch_bounds__(256) affine_points_vec4_kernel(const AffinePar
 __global__ void __launch_bounds__(256) affine_points_scalar_kernel(const AffineParams prm) {
     const long long total = prm.b * prm.npts;
     const long long step = (long long)gridDim.x * blockDim.x;
-    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < total; k += step) {
+    const long long first = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    CloudWalk walk(first, step, prm.npts);
+    for (long long k = first; k < total; k += step, walk.next()) {
         float m[9], t[3];
-        load_coeffs(prm, k / prm.npts, m, t);
+        load_coeffs(prm, walk.cloud, m, t);
         float ox, oy, oz;
         apply(m, t, prm.p[3 * k], prm.p[3 * k + 1], prm.p[3 * k + 2], ox, oy, oz);
         prm.out[3 * k] = ox; prm.out[3 * k + 1] = oy; prm.out[3 * k + 2] = oz;
@@ -153,9 +171,11 @@ __global__ void __launch_bounds__(256) kabsch_weighted_bwd_vec4_kernel(const WBw
     const float4* sp = reinterpret_cast<const float4*>(prm.p);
     const float4* sq = reinterpret_cast<const float4*>(prm.q);
     const float4* swt = reinterpret_cast<const float4*>(prm.w);
-    for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < groups; g += step) {
+    const long long first = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    CloudWalk walk(first, step, gpc);
+    for (long long g = first; g < groups; g += step, walk.next()) {
         WBwdCoeffs c;
-        wbwd_load(prm, g / gpc, c);
+        wbwd_load(prm, walk.cloud, c);
         const float4 p0 = __ldcs(sp + 3 * g), p1 = __ldcs(sp + 3 * g + 1), p2 = __ldcs(sp + 3 * g + 2);
         const float4 q0 = __ldcs(sq + 3 * g), q1 = __ldcs(sq + 3 * g + 1), q2 = __ldcs(sq + 3 * g + 2);
         const float4 wv = __ldcs(swt + g);
@@ -184,9 +204,11 @@ __global__ void __launch_bounds__(256) kabsch_weighted_bwd_vec4_kernel(const WBw
 __global__ void __launch_bounds__(256) kabsch_weighted_bwd_scalar_kernel(const WBwdParams prm) {
     const long long total = prm.b * prm.npts;
     const long long step = (long long)gridDim.x * blockDim.x;
-    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < total; k += step) {
+    const long long first = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    CloudWalk walk(first, step, prm.npts);
+    for (long long k = first; k < total; k += step, walk.next()) {
         WBwdCoeffs c;
-        wbwd_load(prm, k / prm.npts, c);
+        wbwd_load(prm, walk.cloud, c);
         float dp[3], dq[3], dw;
         wbwd_point(c, prm.w[k], prm.p[3 * k], prm.p[3 * k + 1], prm.p[3 * k + 2], prm.q[3 * k], prm.q[3 * k + 1],
                    prm.q[3 * k + 2], dp, dq, dw);
