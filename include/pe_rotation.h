@@ -6,8 +6,9 @@
  * /root/reference).  INTEGRATION.md shows the ctypes stub for each.
  *
  * Conventions (all entry points):
- *   - every pointer is a DEVICE pointer into memory the caller owns (PyTorch's allocator); the library allocates
- *     nothing and keeps no state between calls;
+ *   - every pointer is a DEVICE pointer into memory the caller owns (PyTorch's allocator); the library keeps no state
+ *     between calls and owns one piece of device memory: 32 KB per device of tile-scheduler slots, allocated on the
+ *     first launch of an SVD kernel (which therefore must not happen inside a CUDA-graph capture);
  *   - a "matrix" is 9 consecutive floats, row-major: m[3*i + j] = M[i][j]  (x.view(-1, 3, 3));
  *   - `n` is the number of records (matrices / vectors); n == 0 is a no-op that still zeroes accumulators;
  *   - `*_stride` is the distance in FLOATS between consecutive input records (9 for a dense (n, 9) array, 12 for
