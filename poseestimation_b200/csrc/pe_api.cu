@@ -32,8 +32,10 @@ int run(const float* i0, long long stride0, const float* i1, const float* i2, fl
     if (reinterpret_cast<uintptr_t>(sums) & 7u) return fail(PE_ERR_BAD_ARG, "float64 accumulator not aligned to 8 bytes");
     if (Op::NRED > 0) {
         if (!sums) return fail(PE_ERR_BAD_ARG, "null accumulator pointer");
-        cudaError_t e = cudaMemsetAsync(sums, 0, sizeof(double) * Op::NRED, st);
-        if (e != cudaSuccess) return fail_cuda(e, "cudaMemsetAsync(sum)");
+        if (n == 0) {  // an empty batch still defines its sums; otherwise the kernel's last CTA writes them
+            cudaError_t e = cudaMemsetAsync(sums, 0, sizeof(double) * Op::NRED, st);
+            if (e != cudaSuccess) return fail_cuda(e, "cudaMemsetAsync(sum)");
+        }
     }
     if (Op::FLAG) {
         if (!flag) return fail(PE_ERR_BAD_ARG, "null flag pointer");
@@ -63,7 +65,7 @@ __global__ void __launch_bounds__(256) scale_by_scalar_kernel(const float4* __re
 // the upstream gradient of the loss is exactly 1 (every call site of the reference: Comparison/main.py:62,
 // UPNA/main.py:58, 3D-Pose/main.py:86).  The test is made on the device, so there is no host synchronisation; when it
 // holds the launch costs a few microseconds instead of a 72 B/matrix pass.
-__global__ void __launch_bounds__(256) scale_inplace_kernel(float4* __restrict__ x, const float* __restrict__ g,
+__global__ void __launch_bounds__(1024) scale_inplace_kernel(float4* __restrict__ x, const float* __restrict__ g,
                                                             long long n4, float* __restrict__ xt, int tail) {
     const float k = __ldg(g);
     if (k == 1.0f) return;
@@ -221,10 +223,11 @@ int pe_scale_by_scalar_inplace(float* x, const float* g, int64_t nwords, void* s
     if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     if (e != cudaSuccess) return fail_cuda(e, "cudaDeviceGetAttribute");
     const long long n4 = nwords / 4;
-    long long grid = (n4 + 255) / 256;
-    if (grid > (long long)sms * 8) grid = (long long)sms * 8;
+    // few, fat CTAs: when *g == 1 the launch is pure overhead, and that is the CTA count (2 x 1024 threads still fill an SM)
+    long long grid = (n4 + 1023) / 1024;
+    if (grid > (long long)sms * 2) grid = (long long)sms * 2;
     if (grid < 1) grid = 1;
-    scale_inplace_kernel<<<(unsigned)grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+    scale_inplace_kernel<<<(unsigned)grid, 1024, 0, static_cast<cudaStream_t>(stream)>>>(
         reinterpret_cast<float4*>(x), g, n4, x + 4 * n4, (int)(nwords - 4 * n4));
     e = cudaGetLastError();
     if (e != cudaSuccess) return fail_cuda(e, "scale_inplace");

@@ -36,9 +36,10 @@ struct Params {
     float* out[2];
     long long n;           // records
     long long in0_stride;  // words between consecutive records of in[0] (direct kernel only)
-    double* sums;          // NRED accumulators (device), added to with one atomic per CTA
+    double* sums;          // NRED results (device): written once, by the last CTA to finish
     int* flag;             // OR-ed with the per-record flags
-    unsigned int* sched;   // {next tile to hand out, CTAs finished}: the dynamic tile scheduler (set by stream_launch)
+    unsigned int* sched;   // this launch's slot (set by stream_launch): {next tile to hand out, CTAs finished, -, -,
+                           // two float64 accumulators}; all zero when idle, re-armed by the last CTA
     typename Op::Extra ex;
 };
 
@@ -53,6 +54,7 @@ struct Geometry {
     static constexpr int NOBUF = (WOTOT > 0 && !IN_PLACE) ? 2 : 0;
     static constexpr int TR = kTile * Op::RPT;  // records per tile (RPT records per thread)
     static constexpr bool DYNAMIC = Op::RPT == 2;  // tiles drawn from a global counter (see stream_tma_kernel)
+    static constexpr bool SLOT = DYNAMIC || Op::NRED > 0;  // the launch needs a slot (scheduler and / or accumulators)
     static constexpr int kBarBytes = 128;
     static constexpr int kStageBytes = TR * 4 * WITOT;
     static constexpr int kOutBytes = TR * 4 * WOTOT;
@@ -87,9 +89,15 @@ __device__ __forceinline__ void sts_pair(float* s, int t, int stride, const F2* 
     sts_record<W>(s, t + stride, b);
 }
 
+// Sums: one atomic per CTA into the slot's accumulators (zero when the launch starts), and the last CTA to finish moves
+// them to the caller's array and re-arms the slot - so a reducing launch is ONE stream operation (no memset of the
+// caller's accumulators in front of it).  Also re-arms the tile counter of the dynamic scheduler: every CTA has drawn
+// its last index before it gets here.
 template <class Op>
 __device__ __forceinline__ void block_reduce_and_publish(double* red, int flag, double* sums, int* flagp,
-                                                         double* scratch) {
+                                                         double* scratch, unsigned int* slot) {
+    static_assert(Op::NRED <= 2, "a slot holds two accumulators");
+    double* acc = reinterpret_cast<double*>(slot + 4);
     if constexpr (Op::NRED > 0) {
         const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
@@ -103,13 +111,29 @@ __device__ __forceinline__ void block_reduce_and_publish(double* red, int flag, 
             for (int k = 0; k < Op::NRED; ++k) {
                 double v = 0.0;
                 for (int w = 0; w < (int)(blockDim.x >> 5); ++w) v += scratch[w * Op::NRED + k];
-                atomicAdd(sums + k, v);
+                atomicAdd(acc + k, v);
             }
         }
     }
     if constexpr (Op::FLAG) {
         int any = __syncthreads_or(flag);
         if (threadIdx.x == 0 && any) atomicOr(flagp, any);
+    }
+    if constexpr (Geometry<Op>::SLOT) {
+        if (threadIdx.x == 0) {
+            __threadfence();  // this CTA's adds are visible before its ticket
+            if (atomicAdd(slot + 1, 1u) == gridDim.x - 1) {
+                __threadfence();
+#pragma unroll
+                for (int k = 0; k < Op::NRED; ++k) {
+                    sums[k] = __ldcg(acc + k);  // L2: where the other CTAs' atomics landed
+                    acc[k] = 0.0;
+                }
+                slot[0] = 0u;
+                slot[1] = 0u;
+                __threadfence();
+            }
+        }
     }
 }
 
@@ -313,16 +337,7 @@ __global__ void __launch_bounds__(kTile, Op::MINB) stream_tma_kernel(const Param
     if constexpr (G::WOTOT > 0) {
         if (tid == 0) bulk_wait<0>();  // shared memory must outlive the stores that read it
     }
-    block_reduce_and_publish<Op>(red, flag, p.sums, p.flag, s_red);
-    // every CTA has drawn its last index before it gets here; the last one re-arms the scheduler slot
-    if (DYN && tid == 0) {
-        __threadfence();
-        if (atomicAdd(p.sched + 1, 1u) == gridDim.x - 1) {
-            p.sched[0] = 0u;
-            p.sched[1] = 0u;
-            __threadfence();
-        }
-    }
+    block_reduce_and_publish<Op>(red, flag, p.sums, p.flag, s_red, p.sched);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -353,7 +368,7 @@ __global__ void __launch_bounds__(kTile) stream_direct_kernel(const Params<Op> p
 #pragma unroll
         for (int w = 0; w < Op::WO1; ++w) p.out[1][i * Op::WO1 + w] = o1.v[w];
     }
-    block_reduce_and_publish<Op>(red, flag, p.sums, p.flag, s_red);
+    block_reduce_and_publish<Op>(red, flag, p.sums, p.flag, s_red, p.sched);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -392,8 +407,8 @@ int stream_config(LaunchCfg* out) {
 
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
-// Scheduler slots: {next tile, finished CTAs} pairs in device memory, 32 bytes apart, zero when idle (the last CTA of
-// a launch re-arms its slot).  Successive launches take successive slots of a ring, so launches that overlap on
+// Launch slots: {next tile, finished CTAs, -, -, two float64 accumulators} in device memory, 32 bytes each, zero when idle
+// (the last CTA of a launch re-arms its slot).  Successive launches take successive slots of a ring, so launches that overlap on
 // different streams never share one (the ring is far longer than any realistic number of launches in flight).
 // This is the one piece of device memory the library owns: 32 KB per device, allocated on the first launch (which
 // therefore must not happen inside a CUDA-graph capture).
@@ -441,13 +456,16 @@ int stream_launch(Params<Op> p, cudaStream_t stream) {
     if (tma) {
         long long grid = (long long)cfg.sms * cfg.ctas_per_sm;
         if (grid > ntiles) grid = ntiles;
-        if constexpr (G::DYNAMIC) {
+        if constexpr (G::SLOT) {
             if (int rc = sched_slot(&p.sched)) return rc;
         }
         stream_tma_kernel<Op><<<(unsigned)grid, kTile, G::kSmemBytes, stream>>>(p);
     } else {
         long long grid = (long long)cfg.sms * 8;
         if (grid > ntiles) grid = ntiles;
+        if constexpr (G::SLOT) {
+            if (int rc = sched_slot(&p.sched)) return rc;
+        }
         stream_direct_kernel<Op><<<(unsigned)grid, kTile, 0, stream>>>(p);
     }
     cudaError_t e = cudaGetLastError();
