@@ -14,7 +14,9 @@
  *   - `*_stride` is the distance in FLOATS between consecutive input records (9 for a dense (n, 9) array, 12 for
  *     the out[:, :9] view of a (n, 12) network output); outputs are always dense;
  *   - `stream` is a cudaStream_t passed as void*; all work is enqueued on it, nothing synchronises;
- *   - accumulators (`double* sum`, `int* flag`) are zeroed by the call on `stream`, then added to;
+ *   - accumulators: `double* sum` is WRITTEN by the call (its previous content is ignored; the partial sums meet in
+ *     library-owned scratch and the last thread block to finish stores the total), `int* flag` is zeroed by the call
+ *     on `stream` and then OR-ed into;
  *   - return value: 0 = success, > 0 = a cudaError_t from the launch, < 0 = PE_ERR_* below;
  *     pe_last_error() gives a message for the calling thread's last non-zero return;
  *   - there is no CPU path: without an sm_100 device every compute entry point fails.
