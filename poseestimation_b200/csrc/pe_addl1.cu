@@ -46,6 +46,7 @@ struct AddL1Params {
     int npts;
     int disentangled;
     int use_tma;
+    int lg_split;         // each item is shared by 2^lg_split warps (small batches); outputs are then added atomically
 };
 
 // sign with sgn(0) = 0, as torch.sign in the backward of abs(): LOP3 + FSETP + FSEL
@@ -103,22 +104,30 @@ __global__ void __launch_bounds__(kAWarps * 32, 1) add_l1_kernel(const AddL1Para
     const long long gw = (long long)blockIdx.x * kAWarps + warp;
     const int npts = prm.npts;
     const int cpi = (npts + kAChunk - 1) / kAChunk;  // chunks per item
-    const long long my_items = gw < prm.b ? (prm.b - gw + nwarps - 1) / nwarps : 0;
-    const long long steps = my_items * cpi;
+    // Work units: (item, part).  A small batch (fewer items than warps on the device) is split 2^lg ways, part p of an
+    // item being its chunks [p cpi / 2^lg, (p + 1) cpi / 2^lg).  The number of warps is a multiple of 2^lg, so a warp
+    // keeps the same part for all of its units: unit u = gw + k nwarps -> item u >> lg, part gw & (2^lg - 1).
+    const int lg = prm.lg_split;
+    const int part = (int)(gw & ((1 << lg) - 1));
+    const int ch0 = (part * cpi) >> lg, ch1 = ((part + 1) * cpi) >> lg;
+    const long long units = prm.b << lg;
+    const long long my_units = gw < units ? (units - gw + nwarps - 1) / nwarps : 0;
+    const long long steps = my_units * (ch1 - ch0);
     const float k3n = 1.0f / (3.0f * (float)npts);
     uint64_t policy = 0;
 
     // lane 0: the next chunk to fetch is chunk iss_ch of item iss_it (kept incrementally: a 64-bit division per
     // chunk costs more instructions than the chunk's arithmetic)
-    long long iss_it = gw;
-    int iss_ch = 0;
+    const long long item_step = nwarps >> lg;
+    long long iss_it = gw >> lg;
+    int iss_ch = ch0;
     auto issue = [&](int s) {
         int cnt = min(kAChunk, npts - iss_ch * kAChunk);
         uint32_t bytes = (uint32_t)cnt * 12u;
         mbar_arrive_expect_tx(&bars[s], bytes);
         bulk_g2s(ring + s * kAStageWords, prm.pts + (iss_it * npts + (long long)iss_ch * kAChunk) * 3, bytes, &bars[s],
                  policy);
-        if (++iss_ch == cpi) { iss_ch = 0; iss_it += nwarps; }
+        if (++iss_ch == ch1) { iss_ch = ch0; iss_it += item_step; }
     };
     if constexpr (TMA) {
         if (lane == 0) {
@@ -144,15 +153,15 @@ __global__ void __launch_bounds__(kAWarps * 32, 1) add_l1_kernel(const AddL1Para
         }
     };
     float cur_a, cur_c;
-    fetch_pose(gw, cur_a, cur_c);
+    fetch_pose(gw >> lg, cur_a, cur_c);
 
     double warp_total = 0.0;  // lane 24 only (the lane that ends up with the loss)
     long long j = 0;          // running chunk counter of this warp
     int s = 0;                // ring position of chunk j (j % kAStages)
     uint32_t phase = 0;       // its mbarrier parity ((j / kAStages) & 1)
-    for (long long it = gw; it < prm.b; it += nwarps) {
+    for (long long it = gw >> lg; it < prm.b && ch0 < ch1; it += item_step) {
         const float cur = cur_a - cur_c;
-        fetch_pose(it + nwarps, cur_a, cur_c);  // in flight for the whole item
+        fetch_pose(it + item_step, cur_a, cur_c);  // in flight for the whole item
         // R_gt - R_pred and t_gt - t_pred (the latter is dropped from the vertex term of the disentangled loss)
         F2 d[9], dt[3];
         float tdelta[3];
@@ -172,7 +181,7 @@ __global__ void __launch_bounds__(kAWarps * 32, 1) add_l1_kernel(const AddL1Para
         for (int i = 0; i < 9; ++i) acc.s[i] = F2{0.f, 0.f};
         acc.sv[0] = acc.sv[1] = acc.sv[2] = acc.acc = F2{0.f, 0.f};
 
-        for (int ch = 0; ch < cpi; ++ch, ++j) {
+        for (int ch = ch0; ch < ch1; ++ch, ++j) {
             const int cnt = min(kAChunk, npts - ch * kAChunk);
             const float* sp;
             if constexpr (TMA) {
@@ -213,25 +222,37 @@ __global__ void __launch_bounds__(kAWarps * 32, 1) add_l1_kernel(const AddL1Para
         const float tot = transpose_reduce16(v, lane);
         const int jv = lane >> 1;  // which sum this lane holds
         if ((lane & 1) == 0 && jv < 13) {
+            // a split item: every part adds its share (the outputs were zeroed by the host side); the terms that do not
+            // depend on the vertices come from part 0 only
+            const bool first = part == 0;
             if (jv == 12) {
                 float loss = tot * k3n;
-                if (prm.disentangled)  // transl pose: (x, y) of T_pred, depth pose: z of T_pred - constant distances
+                if (prm.disentangled && first)  // transl pose: (x, y) of T_pred, depth pose: z of T_pred - constants
                     loss += (fabsf(tdelta[0]) + fabsf(tdelta[1]) + fabsf(tdelta[2])) * (1.0f / 3.0f);
-                if (prm.item) prm.item[it] = loss;
+                if (prm.item) {
+                    if (lg == 0) prm.item[it] = loss;
+                    else atomicAdd(prm.item + it, loss);
+                }
                 warp_total += (double)loss;
             } else if (prm.grad) {
                 float* gd = prm.grad + it * 12;
+                float val;
+                int off;
                 if (jv < 9) {
-                    gd[4 * (jv / 3) + jv % 3] = -tot * k3n;
+                    off = 4 * (jv / 3) + jv % 3;
+                    val = -tot * k3n;
                 } else {
                     const int i = jv - 9;
                     const float td = i == 0 ? tdelta[0] : (i == 1 ? tdelta[1] : tdelta[2]);
-                    gd[4 * i + 3] = prm.disentangled ? -sgn(td) * (1.0f / 3.0f) : -tot * k3n;
+                    off = 4 * i + 3;
+                    val = prm.disentangled ? (first ? -sgn(td) * (1.0f / 3.0f) : 0.f) : -tot * k3n;
                 }
+                if (lg == 0) gd[off] = val;
+                else atomicAdd(gd + off, val);
             }
         }
     }
-    if (prm.sum && lane == 24 && my_items > 0) atomicAdd(prm.sum, warp_total);
+    if (prm.sum && lane == 24 && my_units > 0) atomicAdd(prm.sum, warp_total);
 }
 
 }  // namespace pe
@@ -264,9 +285,20 @@ extern "C" int pe_add_l1(const float* t_gt, const float* t_pred, const float* pt
         if (e != cudaSuccess) return fail_cuda(e, "cudaFuncSetAttribute(smem)");
         sms[dev] = prop.multiProcessorCount;
     }
-    AddL1Params prm{t_gt, t_pred, pts, item, sum, grad, (long long)b, (int)npts, disentangled, 0};
+    AddL1Params prm{t_gt, t_pred, pts, item, sum, grad, (long long)b, (int)npts, disentangled, 0, 0};
     prm.use_tma = (npts % 4 == 0) && (reinterpret_cast<uintptr_t>(pts) & 15u) == 0 && !force_direct();
-    long long grid = (b + kAWarps - 1) / kAWarps;
+    // small batches (the reference trains with 64 meshes per step): share an item among up to 16 warps
+    const long long all_warps = (long long)sms[dev] * kAWarps;
+    const long long cpi = (npts + kAChunk - 1) / kAChunk;
+    // (each part keeps at least four chunks: below that the two extra memsets and the atomics cost more than the split saves)
+    while (prm.lg_split < 4 && (b << (prm.lg_split + 1)) <= all_warps && (cpi >> (prm.lg_split + 1)) >= 4) ++prm.lg_split;
+    if (prm.lg_split > 0) {
+        cudaError_t e1 = cudaSuccess;
+        if (item) e1 = cudaMemsetAsync(item, 0, sizeof(float) * (size_t)b, st);
+        if (e1 == cudaSuccess && grad) e1 = cudaMemsetAsync(grad, 0, sizeof(float) * 12 * (size_t)b, st);
+        if (e1 != cudaSuccess) return fail_cuda(e1, "cudaMemsetAsync(split outputs)");
+    }
+    long long grid = ((b << prm.lg_split) + kAWarps - 1) / kAWarps;
     if (grid > sms[dev]) grid = sms[dev];
     if (prm.use_tma) add_l1_kernel<true><<<(unsigned)grid, kAWarps * 32, kASmem, st>>>(prm);
     else add_l1_kernel<false><<<(unsigned)grid, kAWarps * 32, 0, st>>>(prm);

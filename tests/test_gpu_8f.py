@@ -219,7 +219,9 @@ def test_add_l1_losses_match_reference_golden(it, golden):
     assert np.abs(tp3.grad.cpu().numpy() - a64.grad.numpy()).max() <= 1e-5
 
 
-@pytest.mark.parametrize("b,n", [(1, 1), (5, 3), (19, 512), (8, 1500), (150, 2048 + 4), (3, 5000)])
+# (the last three are small batches of large meshes: each item is shared by 4 / 16 / 8 warps and added atomically)
+@pytest.mark.parametrize("b,n", [(1, 1), (5, 3), (19, 512), (8, 1500), (150, 2048 + 4), (3, 5000), (5, 32768 + 4),
+                                 (64, 8192)])
 def test_add_l1_shapes_and_ragged_sizes(it, b, n):
     torch.manual_seed(b + n)
     def poses(k):
