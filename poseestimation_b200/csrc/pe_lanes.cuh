@@ -97,8 +97,17 @@ PE_DEV void hestenes_t(T& p0, T& p1, T& p2, T& q0, T& q1, T& q2, T& np, T& nq) {
 // `fetch(T* dst)` delivers the nine entries of M.  It is called twice (three times for a degenerate lane): once for
 // the Jacobi iteration and once more, afterwards, for the recovery of V - so M does not sit in registers while the
 // rotations run (the kernels re-read it from shared memory; see PairSrc in pe_stream.cuh).
+// What the decomposition leaves for a pullback in the same thread (12 registers per lane pair): the symmetric matrix
+// A = (tr(P) I - P)^-1 (regularised, see svd_orth_pullback_ctx) as a00, a01, a02, a11, a12, a22, and a bit mask of lanes
+// that took the scalar route (their A is not valid).
+template <class T>
+struct SvdCtx {
+    T a[6];
+    int deg;
+};
+
 template <class T, class Fetch>
-PE_DEV void svd_orth_f(const Fetch& fetch, T* r, T& dsign) {
+PE_DEV void svd_orth_f(const Fetch& fetch, T* r, T& dsign, SvdCtx<T>* ctx = nullptr) {
     T a[9];
     fetch(a);
     const T z = a[0];
@@ -130,6 +139,25 @@ PE_DEV void svd_orth_f(const Fetch& fetch, T* r, T& dsign) {
     T u22 = t_fma(u00, u11, t_neg(t_mul(u10, u01)));
     T dd = t_fma(c02, u02, t_fma(c12, u12, t_mul(c22, u22)));
     dsign = t_sel(t_ltz(dd), t_set(z, -1.f), t_set(z, 1.f));
+    T l2 = z, e0 = z, e1 = z;  // ctx only: regularised inverse eigenvalues of tr(P) I - P (see svd_orth_pullback_ctx)
+    if (ctx) {
+        // singular values of the prescaled matrix, the sign of det(M) on the third: P = R^T M = V diag(s0, s1, s2) V^T
+        const T s0 = t_mul(al0, k0), s1 = t_mul(al1, k1), s2 = dd;
+        T a = t_add(s1, s2), b = t_add(s0, s2), cc = t_add(s0, s1);
+        T ab = t_mul(a, b), bc = t_mul(b, cc), ac = t_mul(a, cc);
+        T det = t_mul(ab, cc);
+        T tr3 = t_mul(t_add(t_add(a, b), cc), t_set(z, 1.0f / 3.0f));
+        T fl = t_mul(t_set(z, kDetFloor), t_abs(t_mul(t_mul(tr3, tr3), tr3)));
+        det = t_max(det, fl);
+        T inv = z;
+#pragma unroll
+        for (int k = 0; k < LaneCount<T>::value; ++k) {
+            float d = lane_get(det, k);
+            lane_put(inv, k, d > 1e-30f ? lane_get(sc, k) * rcp_fast(d) : 0.f);
+        }
+        l2 = t_mul(ab, inv);
+        e0 = t_sub(t_mul(bc, inv), l2); e1 = t_sub(t_mul(ac, inv), l2);
+    }
     // right vectors from the left ones: w_j = (sc M)^T u_j, Gram-Schmidt, cross product
     fetch(a);
 #pragma unroll
@@ -160,6 +188,19 @@ PE_DEV void svd_orth_f(const Fetch& fetch, T* r, T& dsign) {
     r[6] = t_fma(u22, v02, t_fma(u21, v01, t_mul(u20, v00)));
     r[7] = t_fma(u22, v12, t_fma(u21, v11, t_mul(u20, v10)));
     r[8] = t_fma(u22, v22, t_fma(u21, v21, t_mul(u20, v20)));
+    if (ctx) {
+        // A = V diag(l0, l1, l2) V^T with (l0, l1, l2) = (bc, ac, ab) / max(abc, floor); since sum_j v_j v_j^T = I,
+        // A = l2 I + (l0 - l2) v0 v0^T + (l1 - l2) v1 v1^T
+        const T p00 = t_mul(e0, v00), p10 = t_mul(e0, v10), p20 = t_mul(e0, v20);
+        const T p01 = t_mul(e1, v01), p11 = t_mul(e1, v11), p21 = t_mul(e1, v21);
+        ctx->a[0] = t_fma(p01, v01, t_fma(p00, v00, l2));
+        ctx->a[1] = t_fma(p01, v11, t_mul(p00, v10));
+        ctx->a[2] = t_fma(p01, v21, t_mul(p00, v20));
+        ctx->a[3] = t_fma(p11, v11, t_fma(p10, v10, l2));
+        ctx->a[4] = t_fma(p11, v21, t_mul(p10, v20));
+        ctx->a[5] = t_fma(p21, v21, t_fma(p20, v20, l2));
+        ctx->deg = 0;
+    }
     // degenerate lanes: hand them to the scalar routine (rare: rank <= 1, all-zero, non-finite)
 #pragma unroll
     for (int k = 0; k < LaneCount<T>::value; ++k) {
@@ -173,6 +214,7 @@ PE_DEV void svd_orth_f(const Fetch& fetch, T* r, T& dsign) {
 #pragma unroll
             for (int i = 0; i < 9; ++i) lane_put(r[i], k, rs[i]);
             lane_put(dsign, k, ds);
+            if (ctx) ctx->deg |= 1 << k;
         }
     }
 }
@@ -225,6 +267,42 @@ PE_DEV void svd_orth_pullback_solve(const T* m, const T* r, T z0, T z1, T z2, T*
         dm[3 * i + 0] = t_fma(r1, y2, t_mul(r2, ny1));
         dm[3 * i + 1] = t_fma(r2, y0, t_mul(r0, ny2));
         dm[3 * i + 2] = t_fma(r0, y1, t_mul(r1, ny0));
+    }
+}
+
+// The same solve from the decomposition itself (SvdCtx), for kernels that have just computed it: with
+// P = R^T M = V diag(s0, s1, s2) V^T the matrix tr(P) I - P is V diag(a, b, c) V^T, a = s1 + s2, b = s0 + s2, c = s0 + s1,
+// so y = V diag(bc, ac, ab) V^T z / max(abc, floor) - the adjugate form, i.e. exactly the regularisation of the
+// cofactor solve above - built once, next to the decomposition, as the symmetric A (6 words); the pullback is then
+// y = A z and dM = R [y]_x: 61 packed instructions in all instead of 89, and M is not read again.
+// Lanes flagged in ctx.deg (scalar route, no valid V) are redone by the generic solve from M.
+template <class T, class Fetch>
+PE_DEV void svd_orth_pullback_ctx(const SvdCtx<T>& c, const Fetch& fetch, const T* r, T z0, T z1, T z2, T* dm) {
+    T y0 = t_fma(c.a[2], z2, t_fma(c.a[1], z1, t_mul(c.a[0], z0)));
+    T y1 = t_fma(c.a[4], z2, t_fma(c.a[3], z1, t_mul(c.a[1], z0)));
+    T y2 = t_fma(c.a[5], z2, t_fma(c.a[4], z1, t_mul(c.a[2], z0)));
+    T ny0 = t_neg(y0), ny1 = t_neg(y1), ny2 = t_neg(y2);
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        T r0 = r[3 * i], r1 = r[3 * i + 1], r2 = r[3 * i + 2];
+        dm[3 * i + 0] = t_fma(r1, y2, t_mul(r2, ny1));
+        dm[3 * i + 1] = t_fma(r2, y0, t_mul(r0, ny2));
+        dm[3 * i + 2] = t_fma(r0, y1, t_mul(r1, ny0));
+    }
+    if (__builtin_expect(c.deg != 0, 0)) {
+        T m[9];
+        fetch(m);
+#pragma unroll
+        for (int k = 0; k < LaneCount<T>::value; ++k) {
+            if (c.deg & (1 << k)) {
+                float ms[9], rs[9], ds[9];
+#pragma unroll
+                for (int i = 0; i < 9; ++i) { ms[i] = lane_get(m[i], k); rs[i] = lane_get(r[i], k); }
+                svd_orth_pullback_solve<float>(ms, rs, lane_get(z0, k), lane_get(z1, k), lane_get(z2, k), ds);
+#pragma unroll
+                for (int i = 0; i < 9; ++i) lane_put(dm[i], k, ds[i]);
+            }
+        }
     }
 }
 

@@ -44,6 +44,16 @@ template <class T, class Src>
 __device__ __forceinline__ void svd_from(const Src& src, T* r, T& ds) {
     svd_orth_f<T>([&src](T* dst) { src.load(dst); }, r, ds);
 }
+// decomposition that keeps (V, singular values) for the pullback in the same thread, and that pullback
+template <class T, class Src>
+__device__ __forceinline__ void svd_from_ctx(const Src& src, T* r, SvdCtx<T>& ctx) {
+    T ds;
+    svd_orth_f<T>([&src](T* dst) { src.load(dst); }, r, ds, &ctx);
+}
+template <class T, class Src>
+__device__ __forceinline__ void pullback_ctx(const SvdCtx<T>& ctx, const Src& src, const T* r, T z0, T z1, T z2, T* dm) {
+    svd_orth_pullback_ctx<T>(ctx, [&src](T* dst) { src.load(dst); }, r, z0, z1, z2, dm);
+}
 
 template <bool DET>
 struct SvdFwd {
@@ -79,10 +89,13 @@ struct SvdBwdRecompute {
     using Extra = NoExtra;
     template <class T, class S0, class S1>
     __device__ static __forceinline__ void body(const S0& ms, const S1& gs, T* dm) {
-        T r[9], m[9], g[9], ds;
-        svd_from<T>(ms, r, ds);
-        ms.load(m); gs.load(g);
-        svd_orth_pullback_t(m, r, g, dm);
+        T r[9], g[9];
+        SvdCtx<T> ctx;
+        svd_from_ctx<T>(ms, r, ctx);
+        gs.load(g);
+        T z0, z1, z2;
+        skew_axial_rtg(r, g, z0, z1, z2);
+        pullback_ctx<T>(ctx, ms, r, z0, z1, z2, dm);
     }
     __device__ static __forceinline__ void run(const float* m, const float* g, const float*, float* dm, float*,
                                                double*, int&, const Extra&) {
@@ -259,14 +272,14 @@ struct SvdFrobBwd {
     using Extra = GradScale;
     template <class T, class S0, class S1>
     __device__ static __forceinline__ void body(const S0& ms, const S1& rts, T* dm, float gs) {
-        T r[9], m[9], ds;
-        svd_from<T>(ms, r, ds);
-        rts.load(m);  // R_true, in the registers that will hold M next
+        T r[9], m[9];
+        SvdCtx<T> ctx;
+        svd_from_ctx<T>(ms, r, ctx);
+        rts.load(m);  // R_true
         T f;
         T z0, z1, z2;
         frob_seed(r, m, gs, f, z0, z1, z2);
-        ms.load(m);
-        svd_orth_pullback_solve(m, r, z0, z1, z2, dm);
+        pullback_ctx<T>(ctx, ms, r, z0, z1, z2, dm);
     }
     __device__ static __forceinline__ void run(const float* m, const float* rt, const float*, float* dm, float*,
                                                double*, int&, const Extra& ex) {
@@ -337,14 +350,14 @@ struct SvdFrobStep {
     using Extra = StepScale;
     template <class T, class S0, class S1>
     __device__ static __forceinline__ T body(const S0& ms, const S1& rts, T* dm, float gs) {
-        T r[9], m[9], ds;
-        svd_from<T>(ms, r, ds);
-        rts.load(m);
+        T r[9], m[9];
+        SvdCtx<T> ctx;
+        svd_from_ctx<T>(ms, r, ctx);
+        rts.load(m);  // R_true
         T f;
         T z0, z1, z2;
         frob_seed(r, m, gs, f, z0, z1, z2);
-        ms.load(m);
-        svd_orth_pullback_solve(m, r, z0, z1, z2, dm);
+        pullback_ctx<T>(ctx, ms, r, z0, z1, z2, dm);
         return f;
     }
     __device__ static __forceinline__ void run(const float* m, const float* rt, const float*, float* dm, float*,

@@ -43,6 +43,24 @@ void hm_svd_orth_x2(const float* m, float* r, float* d, long n) {
         d[i] = ds.x; d[i + h] = ds.y;
     }
 }
+// pullback from the decomposition's own (V, singular values), as the recompute / fused kernels run it
+void hm_svd_orth_bwd_ctx_x2(const float* m, const float* g, float* dm, long n) {
+    long h = n / 2;
+    for (long i = 0; i < h; ++i) {
+        pe::F2 mm[9], rr[9], gg[9], dd[9], ds;
+        for (int k = 0; k < 9; ++k) {
+            mm[k] = pe::F2{m[9 * i + k], m[9 * (i + h) + k]};
+            gg[k] = pe::F2{g[9 * i + k], g[9 * (i + h) + k]};
+        }
+        pe::SvdCtx<pe::F2> ctx;
+        auto fetch = [&mm](pe::F2* dst) { for (int k = 0; k < 9; ++k) dst[k] = mm[k]; };
+        pe::svd_orth_f<pe::F2>(fetch, rr, ds, &ctx);
+        pe::F2 z0, z1, z2;
+        pe::skew_axial_rtg(rr, gg, z0, z1, z2);
+        pe::svd_orth_pullback_ctx<pe::F2>(ctx, fetch, rr, z0, z1, z2, dd);
+        for (int k = 0; k < 9; ++k) { dm[9 * i + k] = dd[k].x; dm[9 * (i + h) + k] = dd[k].y; }
+    }
+}
 void hm_svd_orth_bwd_x2(const float* m, const float* r, const float* g, float* dm, long n) {
     long h = n / 2;
     for (long i = 0; i < h; ++i) {

@@ -148,6 +148,16 @@ def test_packed_two_lane_instantiation_matches_scalar(hm):
     assert np.isfinite(b2).all()
     scale = np.abs(b1).max(1)
     assert (np.abs(b1 - b2).max(1) / np.maximum(scale, 0.1 * np.median(scale))).max() <= 1e-5
+    # the pullback the recompute / fused kernels run: from the decomposition's own V and singular values (no second
+    # read of M, adjugate form of the same regularised solve); degenerate lanes fall back to the generic solve
+    b3 = hostmath.call(hm, "hm_svd_orth_bwd_ctx_x2", x.numpy(), g.numpy(), (n, 9))
+    assert np.isfinite(b3).all()
+    e3 = np.abs(b1 - b3).max(1) / np.maximum(scale, 0.1 * np.median(scale))
+    assert np.quantile(e3, 0.999) <= 1e-5
+    ref_b = O.svd_orth_pullback(x, g).numpy().reshape(n, 9)
+    rel3, rel1 = _rel(b3, ref_b), _rel(b1, ref_b)
+    assert rel3[ok & (cond > 0.1)].max() <= 1e-4                # north_star: 1e-4 away from degenerate spectra
+    assert (rel3 * cond)[ok].max() <= max(2e-5, 1.5 * (rel1 * cond)[ok].max())
 
 
 # ---- SURVEY 8(f) rows ------------------------------------------------------------------------------------------------
