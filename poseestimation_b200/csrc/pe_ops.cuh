@@ -222,12 +222,15 @@ struct AngleFwd {
 // ---- fused: loss_frobenius(symmetric_orthogonalization(x), R_true) ------------------------------------------------
 // Seed of the pullback for G = gs (R - R_t)/|R - R_t|_F without forming G:  R^T G = k (R^T R - R^T R_t) and R^T R is
 // symmetric, so axial(R^T G - G^T R) = -k axial(S - S^T) with S = R^T R_t.  f = |R - R_t|_F, k = gs / f (0 if f = 0).
+// axial(S - S^T) = -sum_k r_k x rt_k over the rows, and with D = R - R_t that is sum_k r_k x d_k: the difference is
+// formed anyway for f, and the cross products of the small d do not cancel when R is close to R_t.
 template <class T>
 __device__ __forceinline__ void frob_seed(const T* r, const T* rt, float gs, T& f, T& z0, T& z1, T& z2) {
-    T d = t_sub(r[0], rt[0]);
-    T s = t_mul(d, d);
+    T d[9];
+    d[0] = t_sub(r[0], rt[0]);
+    T s = t_mul(d[0], d[0]);
 #pragma unroll
-    for (int i = 1; i < 9; ++i) { d = t_sub(r[i], rt[i]); s = t_fma(d, d, s); }
+    for (int i = 1; i < 9; ++i) { d[i] = t_sub(r[i], rt[i]); s = t_fma(d[i], d[i], s); }
     T nk = s;
     f = s;
 #pragma unroll
@@ -237,7 +240,15 @@ __device__ __forceinline__ void frob_seed(const T* r, const T* rt, float gs, T& 
         lane_put(nk, l, -gs * inv);
         lane_put(f, l, sl * inv);
     }
-    skew_axial_rtg(r, rt, z0, z1, z2);
+    z0 = t_mul(r[1], d[2]); z1 = t_mul(r[2], d[0]); z2 = t_mul(r[0], d[1]);
+    z0 = t_fma(t_neg(r[2]), d[1], z0); z1 = t_fma(t_neg(r[0]), d[2], z1); z2 = t_fma(t_neg(r[1]), d[0], z2);
+#pragma unroll
+    for (int k = 1; k < 3; ++k) {
+        const T a0 = r[3 * k], a1 = r[3 * k + 1], a2 = r[3 * k + 2];
+        const T b0 = d[3 * k], b1 = d[3 * k + 1], b2 = d[3 * k + 2];
+        z0 = t_fma(a1, b2, z0); z1 = t_fma(a2, b0, z1); z2 = t_fma(a0, b1, z2);
+        z0 = t_fma(t_neg(a2), b1, z0); z1 = t_fma(t_neg(a0), b2, z1); z2 = t_fma(t_neg(a1), b0, z2);
+    }
     z0 = t_mul(z0, nk); z1 = t_mul(z1, nk); z2 = t_mul(z2, nk);
 }
 
