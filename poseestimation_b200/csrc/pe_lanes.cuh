@@ -168,11 +168,13 @@ PE_DEV void svd_orth_f(const Fetch& fetch, T* r, T& dsign, SvdCtx<T>* ctx = null
     T w01 = t_fma(a[6], u21, t_fma(a[3], u11, t_mul(a[0], u01)));
     T w11 = t_fma(a[7], u21, t_fma(a[4], u11, t_mul(a[1], u01)));
     T w21 = t_fma(a[8], u21, t_fma(a[5], u11, t_mul(a[2], u01)));
+    // Gram-Schmidt without waiting for the first normalisation: n0 w1 - (w1 . w0) w0 has the direction of
+    // w1 - (w1 . v0) v0, so the two reciprocal square roots are independent (this tail is latency-bound)
     T n0 = t_fma(w20, w20, t_fma(w10, w10, t_mul(w00, w00)));
+    T pr = t_neg(t_fma(w21, w20, t_fma(w11, w10, t_mul(w01, w00))));
     T j0 = t_rsq(n0);
+    w01 = t_fma(pr, w00, t_mul(n0, w01)); w11 = t_fma(pr, w10, t_mul(n0, w11)); w21 = t_fma(pr, w20, t_mul(n0, w21));
     T v00 = t_mul(w00, j0), v10 = t_mul(w10, j0), v20 = t_mul(w20, j0);
-    T pr = t_neg(t_fma(w21, v20, t_fma(w11, v10, t_mul(w01, v00))));
-    w01 = t_fma(pr, v00, w01); w11 = t_fma(pr, v10, w11); w21 = t_fma(pr, v20, w21);
     T n1 = t_fma(w21, w21, t_fma(w11, w11, t_mul(w01, w01)));
     T j1 = t_rsq(n1);
     T v01 = t_mul(w01, j1), v11 = t_mul(w11, j1), v21 = t_mul(w21, j1);
