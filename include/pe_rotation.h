@@ -119,6 +119,25 @@ int pe_scale_by_scalar(const float* x, const float* g, float* y, int64_t nwords,
  * single-pass step under `loss.backward()`, whose upstream gradient is exactly 1 at every call site of the reference. */
 int pe_scale_by_scalar_inplace(float* x, const float* g, int64_t nwords, void* stream);
 
+/* ---- fused map + metric: sum_b metric(map(x_b), r_true_b), the rotation is never written ---
+ * What the evaluation loops of the reference compute in two steps - R = transform_output[rot_rep](out), then
+ * angle_error(R, R_true).mean() (UPNA/main.py:93-96, 3D-Pose/main.py:116-120) or a loss of R - in one pass of
+ * 4 W + 36 bytes per record.  `map` selects the representation (x has W = 9, 6, 4, 3, 5, 3 words per record, read with
+ * x_stride), `metric` the distance: Frobenius norm of the difference, geodesic angle in radians (fp32 acos, the cosine
+ * clamped to [lo, hi]: -1, 1 for a6, -+(1 - 1e-7) for a8), or angle_error in degrees (float64; *flag, required, gets
+ * bit 0 if a cosine left [-1.1, 1.1]; lo, hi unused).  Divide *sum by n for the mean. */
+#define PE_MAP_SVD 0
+#define PE_MAP_ORTHO6D 1
+#define PE_MAP_QUAT 2
+#define PE_MAP_EULER 3
+#define PE_MAP_ORTHO5D 4
+#define PE_MAP_EXPMAP 5
+#define PE_METRIC_FROBENIUS 0
+#define PE_METRIC_GEODESIC 1
+#define PE_METRIC_ANGLE_DEG 2
+int pe_map_metric_fwd(int map, int metric, const float* x, int64_t x_stride, const float* r_true, float lo, float hi,
+                      double* sum, int* flag, int64_t n, void* stream);
+
 /* ---- a9  Kabsch alignment - no reference function (site: point_cloud/main.py:171-181) --------------------------
  * p, q: (b, npts, 3) dense.  r[b][9] = the rotation minimising sum_k |R p_k + t - q_k|^2, i.e.
  * pe_svd_orth of sum_k (q_k - qbar)(p_k - pbar)^T;  t (nullable, b x 3) = qbar - R pbar. */

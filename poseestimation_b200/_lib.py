@@ -41,6 +41,7 @@ SIGNATURES = {
     "pe_svd_orth_frobenius_step": [_f, _i64, _f, _flt, _f, _f, _i64, _f],
     "pe_scale_by_scalar": [_f, _f, _f, _i64, _f],
     "pe_scale_by_scalar_inplace": [_f, _f, _i64, _f],
+    "pe_map_metric_fwd": [_int, _int, _f, _i64, _f, _flt, _flt, _f, _f, _i64, _f],
     "pe_kabsch_fwd": [_f, _f, _i64, _i64, _f, _f, _f],
     "pe_kabsch_fwd_ctx": [_f, _f, _i64, _i64, _f, _f, _f, _f],
     "pe_kabsch_bwd_coeffs": [_f, _f, _f, _i64, _f, _f, _i64, _f],

@@ -382,4 +382,69 @@ struct SvdFrobStep {
     }
 };
 
+// ---- fused map + metric: metric(map(x), R_true) summed over the batch, R never written ------
+// The evaluation loops of the reference compute R = transform_output(out) and then angle_error(R, R_true).mean()
+// (UPNA/main.py:93-96, 3D-Pose/main.py:116-120, Comparison/main.py:70-75): 4W + 36 bytes written, then 72 read.
+// Fused: 4W + 36 bytes per record in all.  METRIC 0: |R - R_t|_F (loss_frobenius), 1: geodesic angle in radians, fp32
+// acos, clamp from Extra (a6 / a8), 2: angle_error in degrees, float64, with its range flag (a7).
+template <int METRIC>
+__device__ __forceinline__ void metric_accumulate(const float* r, const float* rt, double* red, int& flag,
+                                                  const Clamp& ex) {
+    if constexpr (METRIC == 0) {
+        red[0] += (double)frob_dist(rt, r);
+    } else if constexpr (METRIC == 1) {
+        float c = 0.5f * (dot9(r, rt) - 1.0f);
+        red[0] += (double)acosf(fminf(fmaxf(c, ex.lo), ex.hi));
+    } else {
+        double c = 0.5 * (dot9_f64(r, rt) - 1.0);
+        if (c < -1.1 || c > 1.1) flag |= 1;
+        red[0] += acos(fmin(fmax(c, -1.0), 1.0)) * 57.295779513082320876798154814105;
+    }
+}
+#define PE_MAP_METRIC(Tag, W, FWD, LABEL)                                                                     \
+    template <int METRIC>                                                                                     \
+    struct Tag##Metric {                                                                                      \
+        PE_OP_COMMON(LABEL "_metric", W, 9, 0, 0, 0, 1, METRIC == 2, 4)                                       \
+        using Extra = Clamp;                                                                                  \
+        __device__ static __forceinline__ void run(const float* x, const float* rt, const float*, float*,    \
+                                                   float*, double* red, int& flag, const Extra& ex) {        \
+            float r[9];                                                                                       \
+            FWD(x, r);                                                                                        \
+            metric_accumulate<METRIC>(r, rt, red, flag, ex);                                                  \
+        }                                                                                                     \
+    };
+PE_MAP_METRIC(Ortho6d, 6, ortho6d, "ortho6d")
+PE_MAP_METRIC(Quat, 4, quat_map, "quat")
+PE_MAP_METRIC(Euler, 3, euler_map, "euler")
+PE_MAP_METRIC(Ortho5d, 5, ortho5d, "ortho5d")
+PE_MAP_METRIC(Expmap, 3, expmap, "expmap")
+template <int METRIC>
+struct SvdMetric {
+    PE_OP_COMMON2("svd_orth_metric", 9, 9, 0, 0, 0, 1, METRIC == 2, 3)
+    using Extra = Clamp;
+    __device__ static __forceinline__ void run(const float* m, const float* rt, const float*, float*, float*,
+                                               double* red, int& flag, const Extra& ex) {
+        float r[9], ds;
+        svd_from<float>(RegSrc<9>{m}, r, ds);
+        metric_accumulate<METRIC>(r, rt, red, flag, ex);
+    }
+    __device__ static __forceinline__ void run2(const PairSrc<9>& m, const PairSrc<9>& rts, const PairSrc<0>&, F2*, F2*,
+                                                double* red, int& flag, bool v0, bool v1, const Extra& ex) {
+        F2 r[9], rt[9], ds;
+        svd_from<F2>(m, r, ds);
+        rts.load(rt);
+        float a[9], b[9];
+        if (v0) {
+#pragma unroll
+            for (int i = 0; i < 9; ++i) { a[i] = r[i].x; b[i] = rt[i].x; }
+            metric_accumulate<METRIC>(a, b, red, flag, ex);
+        }
+        if (v1) {
+#pragma unroll
+            for (int i = 0; i < 9; ++i) { a[i] = r[i].y; b[i] = rt[i].y; }
+            metric_accumulate<METRIC>(a, b, red, flag, ex);
+        }
+    }
+};
+
 }  // namespace pe

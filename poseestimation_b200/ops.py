@@ -389,6 +389,36 @@ def _(r1, r2):
 
 
 # ---------------------------------------------------------------------------------------------------------------------
+# fused map + metric: sum_b metric(map(x_b), r_true_b) without writing the rotations.
+# The reference's evaluation loops: R = transform_output[rot_rep](out); angle_error(R, R_true).mean()
+# (/root/reference/UPNA/main.py:93-96, 3D-Pose/main.py:116-120, Comparison/main.py:70-75)
+MAP_IDS = {"svd": (0, 9), "ortho6d": (1, 6), "quat": (2, 4), "euler": (3, 3), "ortho5d": (4, 5), "expmap": (5, 3)}
+METRIC_IDS = {"frobenius": 0, "geodesic": 1, "angle_error": 2}
+
+
+@torch.library.custom_op(f"{NS}::map_metric_sum", mutates_args=(), device_types="cuda")
+def map_metric_sum(x: Tensor, r_true: Tensor, map_id: int, width: int, metric_id: int, lo: float,
+                   hi: float) -> tuple[Tensor, Tensor]:
+    """(sum (1,) float64, flag (1,) int32: bit 0 = an angle_error cosine out of range; 0 for the other metrics)."""
+    x, stride = _rec(x, width)
+    rt = _mat(r_true)
+    n = x.shape[0]
+    if rt.shape[0] != n:
+        raise ValueError(f"{n} records but {rt.shape[0]} target rotations")
+    s = torch.empty((1,), dtype=torch.float64, device=x.device)
+    flag = torch.zeros((1,), dtype=torch.int32, device=x.device)
+    with torch.cuda.device(x.device):
+        check(lib.pe_map_metric_fwd(map_id, metric_id, x.data_ptr(), stride, rt.data_ptr(), lo, hi, s.data_ptr(),
+                                    flag.data_ptr(), n, _stream()), "pe_map_metric_fwd")
+    return s, flag
+
+
+@map_metric_sum.register_fake
+def _(x, r_true, map_id, width, metric_id, lo, hi):
+    return x.new_empty((1,), dtype=torch.float64), x.new_empty((1,), dtype=torch.int32)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
 # fused training step: loss_frobenius(symmetric_orthogonalization(x), R_true)
 # (/root/reference/Comparison/main.py:59-62, UPNA/main.py:54-58, 3D-Pose/main.py:60,85-86)
 @torch.library.custom_op(f"{NS}::svd_orth_frobenius_sum", mutates_args=(), device_types="cuda")

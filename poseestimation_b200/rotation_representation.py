@@ -31,7 +31,7 @@ __all__ = [
     "compute_rotation_matrix_from_quaternion", "symmetric_orthogonalization",
     "compute_geodesic_distance_from_two_matrices", "angle_error", "so3_exp_map", "hat", "vec_3d_to_SO3",
     "transform_output", "get_scene_parameters", "parametrization",
-    "loss_frobenius", "geodesic", "kabsch", "svd_frobenius_loss", "svd_frobenius_loss_and_grad", "mean_angle_error", "install",
+    "loss_frobenius", "geodesic", "kabsch", "svd_frobenius_loss", "svd_frobenius_loss_and_grad", "mean_angle_error", "map_metric", "install",
 ]
 
 
@@ -159,6 +159,39 @@ def mean_angle_error(R1, R2, check: bool = True):
         raise ValueError("angle out of range, input probably not proper rotation matrices")
     n = R1.reshape(-1, 9).shape[0]
     return (s / n).reshape(())
+
+
+_MAP_KEYS = {"SVD": "svd", "6D": "ortho6d", "5D": "ortho5d", "3D": "expmap", "Quat": "quat", "quat": "quat",
+             "Euler": "euler", "euler": "euler"}
+
+
+def map_metric(rot_rep, x, R_true, metric="angle_error", reduction="mean", check: bool = True):
+    """``metric(transform(x), R_true)`` reduced over the batch in ONE pass, the rotations never written.
+
+    ``rot_rep``: a key of the reference's dispatch dicts (``'SVD'``, ``'6D'``, ``'5D'``, ``'3D'``, ``'Quat'``,
+    ``'Euler'``: rotation_representation.py:323-324, Comparison/models.py:18-19, 3D-Pose/main.py:46).
+    ``metric``: ``'angle_error'`` (degrees, float64, as :230-242 and its ``.mean()`` at the call sites; raises
+    ``ValueError`` like the reference unless ``check=False``), ``'geodesic'`` (radians, clamp of
+    point_cloud/main.py:61-73), ``'geodesic_a6'`` (clamp +-1 of :209-227) or ``'frobenius'`` (loss_frobenius).
+    Returns a 0-d tensor on the device (float64 for angle_error, float32 otherwise).  Not differentiable: it is the
+    evaluation path (the reference runs it under ``torch.no_grad()``)."""
+    if rot_rep not in _MAP_KEYS:
+        raise KeyError(rot_rep)
+    map_id, width = _ops.MAP_IDS[_MAP_KEYS[rot_rep]]
+    lo, hi = -1.0, 1.0
+    if metric == "geodesic":
+        lo, hi = -1.0 + 1e-7, 1.0 - 1e-7
+    mkey = "geodesic" if metric in ("geodesic", "geodesic_a6") else metric
+    if mkey not in _ops.METRIC_IDS:
+        raise ValueError(f"unknown metric {metric!r}")
+    if reduction not in ("mean", "sum"):
+        raise ValueError("reduction must be 'mean' or 'sum'")
+    rec = x.detach().reshape(-1, width)
+    s, flag = _ops.map_metric_sum(rec, R_true.detach(), map_id, width, _ops.METRIC_IDS[mkey], lo, hi)
+    if mkey == "angle_error" and check and int(flag.item()) & 1:
+        raise ValueError("angle out of range, input probably not proper rotation matrices")
+    out = s / rec.shape[0] if reduction == "mean" else s
+    return out.reshape(()) if mkey == "angle_error" else out.reshape(()).to(torch.float32)
 
 
 def loss_frobenius(R_pred, R_true):

@@ -73,6 +73,9 @@ def test_version_and_error_convention(built):
     with pytest.raises(RuntimeError, match="bad call -1"):
         _lib.check(rc, "pe_svd_orth_fwd")
     assert _lib.lib.pe_kabsch_fwd(None, None, 4, 0, None, None, None) == -1
+    assert _lib.lib.pe_map_metric_fwd(9, 0, 1024, 6, 2048, -1.0, 1.0, 4096, None, 1, None) == -1
+    assert b"unknown map" in _lib.lib.pe_last_error()
+    assert _lib.lib.pe_map_metric_fwd(1, 7, 1024, 6, 2048, -1.0, 1.0, 4096, None, 1, None) == -1
     # misaligned arrays are an error code, not a device fault (checked before any CUDA call)
     assert _lib.lib.pe_frobenius_fwd(1024, 2048, 4096 + 4, 1, None) == -1
     assert b"8 bytes" in _lib.lib.pe_last_error()
@@ -160,6 +163,8 @@ def test_fake_kernels_of_the_8f_ops():
         assert ops.pose_update_bwd(c(4, 12), c(4, 4, 4), c(4, 4, 4), 444.0, 444.0).shape == (4, 12)
         item, tot, g = ops.add_l1(c(4, 4, 4), c(4, 4, 4), c(4, 32, 3), True)
         assert item.shape == (4,) and tot.dtype == torch.float64 and g.shape == (4, 3, 4)
+        sm, fl = ops.map_metric_sum(c(5, 6), c(5, 3, 3), 1, 6, 2, -1.0, 1.0)
+        assert sm.shape == (1,) and sm.dtype == torch.float64 and fl.dtype == torch.int32
         loss, dx = ops.svd_orth_frobenius_step(c(5, 9), c(5, 3, 3))
         assert loss.shape == () and dx.shape == (5, 9)
 

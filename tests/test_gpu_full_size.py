@@ -135,6 +135,26 @@ def test_config3_fused_means_equal_per_record_kernels(rr):
     assert float((rows - 2 * math.sqrt(2) * torch.sin(torch.deg2rad(deg) / 2))[sel].abs().max()) <= 1e-4
 
 
+@pytest.mark.parametrize("fname,w,key", MAPS + [("symmetric_orthogonalization", 9, "svd")])
+def test_config3_fused_map_metric_equals_map_then_metric(rr, fname, w, key):
+    """2^24 records: the fused kernels (nothing written) against map kernel -> metric kernel, every metric."""
+    rot_rep = {"ortho6d": "6D", "quaternion": "Quat", "euler": "Euler", "ortho5d": "5D", "expmap": "3D", "svd": "SVD"}[key]
+    torch.manual_seed(20 + w)
+    x = torch.randn(N3, w, device="cuda")
+    rt = rr.compute_rotation_matrix_from_quaternion(torch.randn(N3, 4, device="cuda"))
+    r = getattr(rr, fname)(x)
+    assert abs(rr.map_metric(rot_rep, x, rt, "angle_error").item() - rr.mean_angle_error(r, rt).item()) <= 1e-9 * 180
+    assert abs(rr.map_metric(rot_rep, x, rt, "geodesic").item() - rr.geodesic(r, rt, "mean").item()) <= 1e-6
+    assert abs(rr.map_metric(rot_rep, x, rt, "frobenius").item() - rr.loss_frobenius(r, rt).item()) <= 1e-6
+    # the map of a rotation's own parameters has zero distance to it (up to the acos floor of a float cosine)
+    if key == "ortho6d":
+        own = torch.cat([rt[:, :, 0], rt[:, :, 1]], dim=1).contiguous()
+        assert rr.map_metric("6D", own, rt, "frobenius").item() <= 2e-6
+        assert rr.map_metric("6D", own, rt, "angle_error").item() <= 0.05
+    if key == "svd":
+        assert rr.map_metric("SVD", rt.reshape(N3, 9), rt, "frobenius").item() <= 2e-6
+
+
 def test_config4_sampler_rotate_kabsch_round_trip(rr, pc):
     b, npts = 65536, 1024
     g = torch.Generator(device="cuda").manual_seed(5)

@@ -128,3 +128,57 @@ def test_direct_kernel_path_matches_tma_path(rr):
     a = rr.symmetric_orthogonalization(aligned)
     b = rr.symmetric_orthogonalization(shifted)
     assert torch.equal(a, b)
+
+
+# ---- fused map + metric -------------------------------------------------------------------------
+_FUSED = [("SVD", 9, "symmetric_orthogonalization"), ("6D", 6, "compute_rotation_matrix_from_ortho6d"),
+          ("Quat", 4, "compute_rotation_matrix_from_quaternion"), ("Euler", 3, "compute_rotation_matrix_from_euler"),
+          ("5D", 5, "compute_rotation_matrix_from_ortho5d"), ("3D", 3, "vec_3d_to_SO3")]
+
+
+@pytest.mark.parametrize("key,w,fname", _FUSED)
+@pytest.mark.parametrize("n", [1, 257, 100003])
+def test_fused_map_metric_matches_oracle_and_unfused(rr, key, w, fname, n):
+    g = torch.Generator().manual_seed(n + w)
+    x = torch.randn(n, w, generator=g)
+    rt = O.symmetric_orthogonalization(torch.randn(n, 9, generator=g).double())
+    r64 = getattr(O, fname)(x.double())
+    xd, rtd = x.cuda(), rt.float().cuda()
+    # angle_error: degrees, float64 (rotation_representation.py:230-242 and the .mean() of its call sites)
+    want = O.angle_error(r64, rt).mean().item()
+    got = rr.map_metric(key, xd, rtd, "angle_error")
+    assert got.dtype == torch.float64 and got.dim() == 0
+    assert abs(got.item() - want) <= 1e-4 * max(1.0, 30.0 / n ** 0.5)        # north_star: 1e-4 degrees on the mean
+    unfused = rr.mean_angle_error(getattr(rr, fname)(xd), rtd).item()
+    assert abs(got.item() - unfused) <= 1e-9 * 180
+    assert abs(rr.map_metric(key, xd, rtd, "angle_error", reduction="sum").item() / n - got.item()) <= 1e-9 * 180
+    # geodesic with the clamp of point_cloud/main.py:61-73 and of rotation_representation.py:209-227
+    for metric, fn in (("geodesic", lambda a, b: O.geodesic(a, b, "mean")),
+                       ("geodesic_a6", lambda a, b: O.compute_geodesic_distance_from_two_matrices(a, b).mean())):
+        got = rr.map_metric(key, xd, rtd, metric)
+        assert got.dtype == torch.float32
+        assert abs(got.item() - fn(r64, rt).item()) <= 1e-5 + 2e-4 / n ** 0.5
+    got = rr.map_metric(key, xd, rtd, "frobenius")
+    assert abs(got.item() - O.loss_frobenius(r64, rt).item()) <= 2e-6
+    assert abs(got.item() - rr.loss_frobenius(getattr(rr, fname)(xd), rtd).item()) <= 1e-6
+
+
+def test_fused_map_metric_interface(rr):
+    x = torch.randn(64, 12, device="cuda")
+    rt = rr.symmetric_orthogonalization(torch.randn(64, 9, device="cuda"))
+    # a (B, 12) network output read in place through its first columns
+    a = rr.map_metric("SVD", x[:, :9], rt)
+    b = rr.mean_angle_error(rr.symmetric_orthogonalization(x[:, :9]), rt)
+    assert abs(a.item() - b.item()) <= 1e-9
+    with pytest.raises(KeyError):
+        rr.map_metric("7D", x[:, :7], rt)
+    with pytest.raises(ValueError):
+        rr.map_metric("6D", x[:, :6], rt, metric="chordal")
+    with pytest.raises(ValueError):
+        rr.map_metric("6D", x[:, :6], rt[:10])
+    # non-rotations as the target: the range flag of angle_error raises, as in the reference
+    with pytest.raises(ValueError):
+        rr.map_metric("6D", x[:, :6], 3.0 * rt)
+    assert rr.map_metric("6D", x[:, :6], 3.0 * rt, check=False).dim() == 0
+    with pytest.raises(NotImplementedError):
+        rr.map_metric("6D", x[:, :6].cpu(), rt.cpu())

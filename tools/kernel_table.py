@@ -80,6 +80,15 @@ def main():
     add("geodesic_bwd (one grad)", 112, lambda: check(lib.pe_geodesic_bwd(P(r1), P(r2), -1.0, 1.0, P(th), 0, 1.0, P(o9), None, n, st), ""))
     add("angle_error_fwd (deg, f64)", 80, lambda: check(lib.pe_angle_error_fwd(P(r1), P(r2), P(deg), None, P(flag), n, st), ""))
     add("angle_error_fwd (fused mean)", 72, lambda: check(lib.pe_angle_error_fwd(P(r1), P(r2), None, P(sums), P(flag), n, st), ""))
+    # fused map + metric (config 3): nothing written
+    for name, mid, w in (("svd", 0, 9), ("ortho6d", 1, 6), ("quat", 2, 4), ("euler", 3, 3)):
+        xi = x9 if w == 9 else rnd(n, w)
+        add(f"{name} + angle_error mean (fused, f64)", 4 * w + 36,
+            lambda mid=mid, xi=xi, w=w: check(lib.pe_map_metric_fwd(mid, 2, P(xi), w, P(r1), -1.0, 1.0, P(sums), P(flag), n, st), ""))
+    x6 = rnd(n, 6)
+    add("ortho6d + geodesic mean (fused)", 60, lambda: check(lib.pe_map_metric_fwd(1, 1, P(x6), 6, P(r1), -1.0, 1.0, P(sums), None, n, st), ""))
+    add("ortho6d + frobenius mean (fused)", 60, lambda: check(lib.pe_map_metric_fwd(1, 0, P(x6), 6, P(r1), -1.0, 1.0, P(sums), None, n, st), ""))
+    del x6
     del x9, g9, r1, r2, o9, o9b
     b, npts = 65536, 1024
     pc = torch.rand(b, npts, 3, device=dev, generator=g) - 0.5
