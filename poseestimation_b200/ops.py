@@ -2,7 +2,10 @@
 
 Each op is CUDA-only (``device_types="cuda"``): a CPU tensor raises ``NotImplementedError`` from the dispatcher, there is
 no CPU or PyTorch fallback.  Every differentiable op has ``register_fake`` (so ``torch.compile`` can trace it) and
-``register_autograd`` whose backward is itself a custom op.
+``register_autograd`` whose backward is itself a custom op.  The names exported from this module are thin eager wrappers
+around those registrations (``_Eager`` below): with ordinary CUDA tensors in eager mode they run the op's body and its
+autograd functions directly, which takes the dispatcher's 30-40 us per call off the small-batch path; ``<name>.op`` and
+``torch.ops.pe_b200.<name>`` are the registered ops themselves.
 
 Record convention: the ops take 2-D ``(n, w)`` float32 tensors ("records": w = 9 for a row-major 3x3 matrix) whose
 inner stride is 1; the row stride may exceed ``w`` (``out[:, :9]`` of a ``(B, 12)`` network output,
@@ -16,6 +19,67 @@ from torch import Tensor
 from ._lib import check, lib
 
 NS = "pe_b200"
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# Eager fast path.  A call of a ``torch.library.custom_op`` costs 30-40 us of Python dispatch, and ~150 us with its
+# generated autograd node - more than the kernel itself at the batch sizes the reference trains with (32-128 matrices
+# per step; measured: tools/latency.py).  Every op object exported by this module is therefore an ``_Eager`` wrapper:
+#   * ordinary CUDA tensors, eager mode  -> the op's own Python body is called directly (same C-ABI call, same checks),
+#     under a plain ``torch.autograd.Function`` built from the SAME setup / backward functions that are registered with
+#     ``register_autograd`` when an input needs a gradient;
+#   * anything else (torch.compile tracing, FakeTensor / functorch subclasses, CPU tensors, keyword arguments)
+#     -> the registered ``pe_b200::<op>`` through the dispatcher (``.op`` is the CustomOpDef; ``torch.ops.pe_b200`` sees
+#     the same registrations), which is also what rejects CPU tensors with NotImplementedError.
+# Double backward raises (``once_differentiable``), as it does for the registered ops.
+_AUTOGRAD: dict = {}
+
+
+def _register(op, backward, setup):
+    op.register_autograd(backward, setup_context=setup)
+    _AUTOGRAD[op] = (setup, backward)
+
+
+class _Eager:
+    __slots__ = ("op", "raw", "fn", "nargs", "__name__", "__doc__")
+
+    def __init__(self, op, setup=None, backward=None):
+        import inspect
+        from torch.autograd.function import once_differentiable
+        self.op, self.raw = op, op._init_fn
+        self.nargs = len(inspect.signature(self.raw).parameters)
+        self.__name__, self.__doc__ = op._name, self.raw.__doc__
+        self.fn = None
+        if backward is not None:
+            raw = self.raw
+
+            def forward(ctx, *args):
+                out = raw(*args)
+                setup(ctx, args, out)
+                return out
+
+            def backward_(ctx, *grads):
+                return backward(ctx, *grads)
+
+            # created through type() so that the node shows up as pe_b200_<op>Backward in autograd graphs / profiles
+            self.fn = type(f"pe_b200_{self.__name__}", (torch.autograd.Function,),
+                           {"forward": staticmethod(forward), "backward": staticmethod(once_differentiable(backward_))})
+
+    def __call__(self, *args, **kwargs):
+        if kwargs or len(args) != self.nargs or torch.compiler.is_compiling():
+            return self.op(*args, **kwargs)
+        needs_grad = False
+        for a in args:
+            if isinstance(a, Tensor):
+                if not a.is_cuda or (type(a) is not Tensor and type(a) is not torch.nn.Parameter):
+                    return self.op(*args)
+                needs_grad = needs_grad or a.requires_grad
+        if needs_grad and self.fn is not None and torch.is_grad_enabled():
+            return self.fn.apply(*args)
+        return self.raw(*args)
+
+    def register_fake(self, fn):          # so that decorators written against the CustomOpDef keep working
+        return self.op.register_fake(fn)
 
 
 # ---------------------------------------------------------------------------------------------------------------------
@@ -39,6 +103,13 @@ def _mat(x: Tensor) -> Tensor:
     if x.dim() == 3 and x.shape[1:] == (3, 3) or x.dim() == 2 and x.shape[1] == 9:
         return x.contiguous().view(-1, 9)
     raise ValueError(f"expected (n, 3, 3) matrices, got {tuple(x.shape)}")
+
+
+def _mean32(s: Tensor, n: int) -> Tensor:
+    """0-d float32 mean from the (1,) float64 sum a kernel wrote: ONE small launch (the float32 ``out=`` does the cast)."""
+    out = torch.empty((1,), dtype=torch.float32, device=s.device)
+    torch.div(s, n, out=out)
+    return out.reshape(())
 
 
 def _stream() -> int:
@@ -114,7 +185,7 @@ def _svd_orth_backward(ctx, g):
     return svd_orth_bwd_recompute(x, g)
 
 
-svd_orth.register_autograd(_svd_orth_backward, setup_context=_svd_orth_setup)
+_register(svd_orth, _svd_orth_backward, _svd_orth_setup)
 
 
 @torch.library.custom_op(f"{NS}::svd_orth_det", mutates_args=(), device_types="cuda")
@@ -170,12 +241,14 @@ def _make_map(name: str, w: int):
     def setup(ctx, inputs, output):
         ctx.save_for_backward(inputs[0])
 
+    bwd_e = _Eager(bwd)
+
     def backward(ctx, g):
         (x,) = ctx.saved_tensors
-        return bwd(x, g)
+        return bwd_e(x, g)
 
-    fwd.register_autograd(backward, setup_context=setup)
-    return fwd, bwd
+    _register(fwd, backward, setup)
+    return _Eager(fwd, setup, backward), bwd_e
 
 
 ortho6d, ortho6d_bwd = _make_map("ortho6d", 6)     # rotation_representation.py:21-36
@@ -209,7 +282,7 @@ def _(a, b):
 def frobenius_mean(a: Tensor, b: Tensor) -> Tensor:
     """mean_b |a_b - b_b|_F, 0-d float32."""
     n = _mat(a).shape[0]
-    return (frobenius_sum(a, b) / max(n, 1)).to(torch.float32).reshape(()) if n else \
+    return _mean32(frobenius_sum(a, b), n) if n else \
         torch.full((), float("nan"), dtype=torch.float32, device=a.device)
 
 
@@ -250,7 +323,7 @@ def _frob_backward(ctx, g):
     return (da.view(a.shape) if na else None), (db.view(b.shape) if nb else None)
 
 
-frobenius_mean.register_autograd(_frob_backward, setup_context=_frob_setup)
+_register(frobenius_mean, _frob_backward, _frob_setup)
 
 
 # ---------------------------------------------------------------------------------------------------------------------
@@ -347,8 +420,8 @@ def _geo_reduce_backward(ctx, g):
     return (d1.view(m1.shape) if n1 else None), (d2.view(m2.shape) if n2 else None), None, None, None
 
 
-geodesic_theta.register_autograd(_geo_theta_backward, setup_context=_geo_setup)
-geodesic_reduce.register_autograd(_geo_reduce_backward, setup_context=_geo_setup)
+_register(geodesic_theta, _geo_theta_backward, _geo_setup)
+_register(geodesic_reduce, _geo_reduce_backward, _geo_setup)
 
 
 # ---------------------------------------------------------------------------------------------------------------------
@@ -448,7 +521,7 @@ def svd_orth_frobenius(x: Tensor, r_true: Tensor) -> Tensor:
     """0-d float32 loss; differentiable w.r.t. x (r_true is a target)."""
     n = x.shape[0]
     s, _ = svd_orth_frobenius_sum(x, r_true, False)
-    return (s / n).to(torch.float32).reshape(()) if n else s.to(torch.float32).reshape(()) * float("nan")
+    return _mean32(s, n) if n else s.to(torch.float32).reshape(()) * float("nan")
 
 
 @svd_orth_frobenius.register_fake
@@ -484,7 +557,7 @@ def _sof_backward(ctx, g):
     return svd_orth_frobenius_bwd(x, rt, g), None
 
 
-svd_orth_frobenius.register_autograd(_sof_backward, setup_context=_sof_setup)
+_register(svd_orth_frobenius, _sof_backward, _sof_setup)
 
 
 # single pass: one decomposition per matrix gives the loss and the gradient for a unit upstream gradient (108 B/matrix);
@@ -497,13 +570,14 @@ def svd_orth_frobenius_step(x: Tensor, r_true: Tensor) -> tuple[Tensor, Tensor]:
     rt = _mat(r_true)
     if rt.shape[0] != n:
         raise ValueError("batch mismatch")
-    s = torch.zeros((1,), dtype=torch.float64, device=x.device)
+    # the kernel WRITES the sum (include/pe_rotation.h: accumulators); only the empty batch needs a defined value
+    s = (torch.empty if n else torch.zeros)((1,), dtype=torch.float64, device=x.device)
     dx = torch.empty((n, 9), dtype=torch.float32, device=x.device)
     if n:
         with torch.cuda.device(x.device):
             check(lib.pe_svd_orth_frobenius_step(x.data_ptr(), stride, rt.data_ptr(), 1.0 / n, dx.data_ptr(),
                                                  s.data_ptr(), n, _stream()), "pe_svd_orth_frobenius_step")
-        loss = (s / n).to(torch.float32).reshape(())
+        loss = _mean32(s, n)
     else:
         loss = s.to(torch.float32).reshape(()) * float("nan")
     return loss, dx
@@ -564,7 +638,7 @@ def _step_backward(ctx, g_loss, _g_dx):
     return dx, None
 
 
-svd_orth_frobenius_step.register_autograd(_step_backward, setup_context=_step_setup)
+_register(svd_orth_frobenius_step, _step_backward, _step_setup)
 
 
 # ---------------------------------------------------------------------------------------------------------------------
@@ -678,7 +752,7 @@ def _affine_backward(ctx, g):
     return da, dt, dp, None
 
 
-affine_points.register_autograd(_affine_backward, setup_context=_affine_setup)
+_register(affine_points, _affine_backward, _affine_setup)
 
 
 # ---------------------------------------------------------------------------------------------------------------------
@@ -745,7 +819,7 @@ def _kabsch_backward(ctx, g_r, g_t, _g_c):
     return kabsch_bwd(p, q, r, c, g_r, g_t)
 
 
-kabsch_ctx.register_autograd(_kabsch_backward, setup_context=_kabsch_setup)
+_register(kabsch_ctx, _kabsch_backward, _kabsch_setup)
 
 
 # weighted variant (8f.3): per-point weights w >= 0; forward 28 B per point pair, backward one pass over p, q, w that
@@ -831,7 +905,7 @@ def _kabsch_w_backward(ctx, g_r, g_t, _g_c):
     return (dp if need[0] else None, dq if need[1] else None, dw if need[2] else None)
 
 
-kabsch_weighted_ctx.register_autograd(_kabsch_w_backward, setup_context=_kabsch_w_setup)
+_register(kabsch_weighted_ctx, _kabsch_w_backward, _kabsch_w_setup)
 
 
 # ---------------------------------------------------------------------------------------------------------------------
@@ -915,7 +989,7 @@ def _pose_backward(ctx, g):
     return pose_update_bwd(out, ti, g, ctx.fx, ctx.fy), None, None, None
 
 
-pose_update.register_autograd(_pose_backward, setup_context=_pose_setup)
+_register(pose_update, _pose_backward, _pose_setup)
 
 
 # ---------------------------------------------------------------------------------------------------------------------
@@ -964,4 +1038,18 @@ def _addl1_backward(ctx, g_item, g_sum, _g_grad):
     return None, d, None, None
 
 
-add_l1.register_autograd(_addl1_backward, setup_context=_addl1_setup)
+_register(add_l1, _addl1_backward, _addl1_setup)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# every op object of this module becomes its eager wrapper (see _Eager); calls between ops resolve these names at call
+# time, so the backward functions above take the fast path as well
+def _wrap_all():
+    from torch._library.custom_ops import CustomOpDef
+    g = globals()
+    for name, obj in list(g.items()):
+        if isinstance(obj, CustomOpDef):
+            g[name] = _Eager(obj, *_AUTOGRAD.get(obj, (None, None)))
+
+
+_wrap_all()

@@ -250,9 +250,12 @@ def get_scene_parameters():
 
 def parametrization(output, T_init, fx, fy, vx, vy, rot_rep):
     """CosyPose pose update (rotation_representation.py:346-373; the reference body uses undefined names and cannot
-    run - this follows its formulas and the working twin Iterative/utility.py:90-128).  The rotation goes through the
-    native map; the 4x4 assembly is a SURVEY 8(f) "next" row and still plain torch."""
+    run - this follows its formulas and the working twin Iterative/utility.py:90-128).  ``'SVD'`` is ONE native kernel
+    (orthogonalisation, dR R_k, translation update, 4x4 assembly; differentiable w.r.t. ``output``); for the other keys
+    the rotation goes through its native map and only the 12-number assembly is torch indexing."""
     vector_length, representation_func = transform_output[rot_rep]
+    if rot_rep == 'SVD' and output.shape[1] >= 12:
+        return _ops.pose_update(output[:, :12], T_init.float(), float(fx), float(fy))
     R = representation_func(output[:, 0:vector_length])
     v = output[:, vector_length:vector_length + 3]
     xk, yk, zk = T_init[:, 0, 3], T_init[:, 1, 3], T_init[:, 2, 3]

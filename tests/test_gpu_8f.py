@@ -194,6 +194,22 @@ def test_pose_update_matches_reference_golden(it, golden):
         it.calculate_T_pred(T(z["out"]).cuda(), T(z["T_init"]).cuda(), "cuda", rot_repr="6D")
 
 
+def test_parametrization_svd_is_the_pose_update_kernel(rr, it, golden):
+    """rotation_representation.py:346-373 (cannot run in the reference): same formulas as Iterative/utility.py:90-128,
+    so with the 'SVD' key it must reproduce the golden poses; the '6D' key goes through the native 6D map."""
+    z = golden("iterative")
+    out, ti = T(z["out"]).cuda(), T(z["T_init"]).cuda()
+    fx, fy = it.get_scene_parameters()
+    tp = rr.parametrization(out, ti, fx, fy, 160.0, 160.0, "SVD")
+    assert np.abs(tp.cpu().numpy() - z["T_pred_ref_fp32"]).max() <= 2e-5
+    x6 = torch.randn(len(out), 9, device="cuda")
+    t6 = rr.parametrization(x6, ti, fx, fy, 160.0, 160.0, "6D")
+    r6 = rr.compute_rotation_matrix_from_ortho6d(x6[:, :6])
+    assert float((t6[:, :3, :3] - r6 @ ti[:, :3, :3]).abs().max()) <= 1e-6
+    assert float((t6[:, 2, 3] - x6[:, 8] * ti[:, 2, 3]).abs().max()) <= 1e-6
+    assert (t6[:, 3] == torch.tensor([0.0, 0.0, 0.0, 1.0], device="cuda")).all()
+
+
 def test_add_l1_losses_match_reference_golden(it, golden):
     z = golden("iterative")
     tg, v = T(z["T_gt"]).cuda(), T(z["verts"]).cuda()

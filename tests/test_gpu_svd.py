@@ -319,12 +319,71 @@ def test_degenerate_inputs_are_finite_rotations(rr):
 
 def test_opcheck(ops):
     x = torch.randn(33, 9, device="cuda", requires_grad=True)
-    torch.library.opcheck(ops.svd_orth, (x,), test_utils=("test_schema", "test_faketensor", "test_autograd_registration"))
+    torch.library.opcheck(ops.svd_orth.op, (x,), test_utils=("test_schema", "test_faketensor", "test_autograd_registration"))
     a = torch.randn(33, 3, 3, device="cuda", requires_grad=True)
     b = torch.randn(33, 3, 3, device="cuda")
-    torch.library.opcheck(ops.frobenius_mean, (a, b),
+    torch.library.opcheck(ops.frobenius_mean.op, (a, b),
                           test_utils=("test_schema", "test_faketensor", "test_autograd_registration"))
-    torch.library.opcheck(ops.svd_orth_frobenius_step, (x, b),
+    torch.library.opcheck(ops.svd_orth_frobenius_step.op, (x, b),
                           test_utils=("test_schema", "test_faketensor", "test_autograd_registration"))
-    torch.library.opcheck(ops.ortho6d, (torch.randn(33, 6, device="cuda", requires_grad=True),),
+    torch.library.opcheck(ops.ortho6d.op, (torch.randn(33, 6, device="cuda", requires_grad=True),),
                           test_utils=("test_schema", "test_faketensor", "test_autograd_registration"))
+
+
+def test_eager_fast_path_equals_dispatcher_route(ops, rr):
+    """ops.X(...) calls the op body directly (plain autograd.Function) for ordinary CUDA tensors; ops.X.op(...) is the
+    registered pe_b200::X through the dispatcher.  Same kernels, same autograd formulas: results are bit-identical."""
+    g = torch.Generator(device="cuda").manual_seed(7)
+    rt = rr.symmetric_orthogonalization(torch.randn(257, 9, device="cuda", generator=g)).detach()
+    up = torch.randn(257, 3, 3, device="cuda", generator=g)
+    for name, w in (("svd_orth", 9), ("ortho6d", 6), ("quat", 4), ("euler", 3)):
+        x = torch.randn(257, w, device="cuda", generator=g)
+        res = []
+        for route in (getattr(ops, name), getattr(ops, name).op):
+            xi = x.clone().requires_grad_(True)
+            r = route(xi)
+            r.backward(up)
+            res.append((r.detach(), xi.grad))
+        assert torch.equal(res[0][0], res[1][0]) and torch.equal(res[0][1], res[1][1])
+        assert type(getattr(ops, name)(x).grad_fn) is type(None)
+        assert "pe_b200_" + name in type(getattr(ops, name)(x.clone().requires_grad_(True)).grad_fn).__name__
+    x = torch.randn(257, 9, device="cuda", generator=g)
+    out = []
+    for route in (ops.svd_orth_frobenius_step, ops.svd_orth_frobenius_step.op):
+        xi = x.clone().requires_grad_(True)
+        loss, _ = route(xi, rt)
+        (loss * 3.0).backward()
+        out.append((loss.detach(), xi.grad))
+    # the loss sum is accumulated with float64 atomics in an order that varies from launch to launch
+    assert abs(float(out[0][0]) - float(out[1][0])) <= 1e-6 and torch.equal(out[0][1], out[1][1])
+    a = torch.randn(64, 3, 3, device="cuda", generator=g)
+    ga = []
+    for route in (ops.frobenius_mean, ops.frobenius_mean.op):
+        ai = a.clone().requires_grad_(True)
+        route(ai, rt[:64]).backward()
+        ga.append(ai.grad)
+    assert torch.equal(ga[0], ga[1])
+    # double backward is refused on the fast path as on the registered one
+    xi = x.clone().requires_grad_(True)
+    (gx,) = torch.autograd.grad(ops.svd_orth(xi).sum(), xi, create_graph=True)
+    with pytest.raises(RuntimeError):
+        gx.sum().backward()
+
+
+def test_registered_ops_trace_under_torch_compile(rr):
+    """torch.compile sees pe_b200::* through register_fake / register_autograd (the wrapper steps aside while
+    compiling); aot_eager runs the traced graph with the same kernels."""
+    g = torch.Generator(device="cuda").manual_seed(11)
+    x = torch.randn(130, 9, device="cuda", generator=g)
+    rt = rr.symmetric_orthogonalization(torch.randn(130, 9, device="cuda", generator=g)).detach()
+
+    def step(x, rt):
+        return rr.loss_frobenius(rr.symmetric_orthogonalization(x), rt)
+
+    xe = x.clone().requires_grad_(True)
+    le = step(xe, rt)
+    le.backward()
+    xc = x.clone().requires_grad_(True)
+    lc = torch.compile(step, backend="aot_eager", fullgraph=True)(xc, rt)
+    lc.backward()
+    assert abs(float(le) - float(lc)) <= 1e-6 and torch.equal(xe.grad, xc.grad)

@@ -1,0 +1,107 @@
+#!/usr/bin/env python
+"""Per-call latency of the public API at the batch sizes the reference trains with (32-128 matrices per step:
+Comparison/main.py:100, UPNA/main.py:149, 3D-Pose configs, Iterative/main.py:216), where a call is launch- and
+host-bound, not HBM-bound.  Prints one JSON object: microseconds per call (wall clock over `reps` back-to-back calls,
+synchronised at both ends) for
+
+  * svd_frobenius_loss(x, R_true).backward()         the fused training step (2 launches), on the eager fast path
+    (ops._Eager) and through the registered torch.library op (the route torch.compile traces)
+  * symmetric_orthogonalization(x) -> loss_frobenius -> backward   the unfused drop-in route (4 launches)
+  * the same with the whole step captured in a CUDA graph and replayed
+  * stock torch on the same GPU (torch.svd + det + matmul + matrix_norm, the calls of rotation_representation.py:192-206
+    and Comparison/main.py:12-16) for scale
+
+Usage: python tools/latency.py [--reps 300] [--batches 32,64,128,4096]"""
+import argparse
+import json
+import os
+import sys
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import poseestimation_b200.rotation_representation as rr  # noqa: E402
+from poseestimation_b200 import ops  # noqa: E402
+
+
+def stock_torch_step(x, rt):
+    m = x.view(-1, 3, 3)
+    u, s, v = torch.svd(m)
+    vt = v.transpose(1, 2)
+    det = torch.det(torch.matmul(u, vt)).view(-1, 1, 1)
+    vt = torch.cat((vt[:, :2, :], vt[:, -1:, :] * det), 1)
+    r = torch.matmul(u, vt)
+    loss = torch.linalg.matrix_norm(rt - r, ord="fro").mean()
+    loss.backward()
+    return loss
+
+
+def timed(fn, reps):
+    for _ in range(10):
+        fn()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        fn()
+    torch.cuda.synchronize()
+    return (time.perf_counter() - t0) / reps * 1e6
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--reps", type=int, default=300)
+    ap.add_argument("--batches", default="32,64,128,4096")
+    args = ap.parse_args()
+    dev = torch.device("cuda", 0)
+    res = {}
+    for b in [int(v) for v in args.batches.split(",")]:
+        x = torch.randn(b, 9, device=dev, requires_grad=True)
+        rt = rr.symmetric_orthogonalization(torch.randn(b, 9, device=dev)).detach()
+
+        def fused():
+            x.grad = None
+            rr.svd_frobenius_loss(x, rt).backward()
+
+        def unfused():
+            x.grad = None
+            rr.loss_frobenius(rr.symmetric_orthogonalization(x), rt).backward()
+
+        def no_autograd():
+            rr.svd_frobenius_loss_and_grad(x, rt)
+
+        def dispatcher():
+            x.grad = None
+            ops.svd_orth_frobenius_step.op(x, rt)[0].backward()
+
+        def stock():
+            x.grad = None
+            stock_torch_step(x, rt)
+
+        row = {"fused_step_us": timed(fused, args.reps), "fused_step_via_dispatcher_us": timed(dispatcher, args.reps),
+               "unfused_dropin_us": timed(unfused, args.reps),
+               "loss_and_grad_no_autograd_us": timed(no_autograd, args.reps),
+               "stock_torch_gpu_us": timed(stock, max(20, args.reps // 10))}
+        # the whole fused step as one CUDA graph (static input buffers, as a training loop would hold them)
+        xs = x.detach().clone()
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(3):
+                rr.svd_frobenius_loss_and_grad(xs, rt)
+        torch.cuda.current_stream().wait_stream(side)
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            loss, grad = rr.svd_frobenius_loss_and_grad(xs, rt)
+        ref_loss, ref_grad = rr.svd_frobenius_loss_and_grad(xs, rt)
+        graph.replay()
+        torch.cuda.synchronize()
+        assert torch.equal(grad, ref_grad) and abs(float(loss) - float(ref_loss)) <= 1e-6
+        row["loss_and_grad_cuda_graph_us"] = timed(graph.replay, args.reps)
+        res[str(b)] = {k: round(v, 2) for k, v in row.items()}
+    print(json.dumps({"what": "microseconds per call, wall clock, 1 B200", "reps": args.reps, "batch": res}))
+
+
+if __name__ == "__main__":
+    main()
