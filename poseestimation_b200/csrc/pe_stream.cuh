@@ -29,6 +29,15 @@
 namespace pe {
 
 constexpr int kTile = 256;  // records per tile = threads per CTA
+// Output tiles of the ops that do not store in place wait in a ring of kOutBufs shared-memory buffers for their bulk
+// stores.  With THREE buffers a tile needs ONE __syncthreads: the barrier that says "everyone is done with the input
+// stage" also publishes the output tile, because the buffer written in iteration i+1 was last read by the store of
+// iteration i-2, which thread 0 has waited for before it arrived at the barrier of iteration i.  (With two buffers the
+// write has to sit between two barriers; ncu showed the write-heavy maps stalled 5-11 cycles per issue on them.)
+#ifndef PE_OUT_BUFS
+#define PE_OUT_BUFS 3
+#endif
+constexpr int kOutBufs = PE_OUT_BUFS;
 
 template <class Op>
 struct Params {
@@ -51,7 +60,7 @@ struct Geometry {
     static constexpr int WOTOT = Op::WO0 + Op::WO1;
     // in-place output: the op's single output record has the width of in[0] and replaces it inside the stage
     static constexpr bool IN_PLACE = Op::RPT == 2 && Op::WO0 == Op::WI0 && Op::WO1 == 0;
-    static constexpr int NOBUF = (WOTOT > 0 && !IN_PLACE) ? 2 : 0;
+    static constexpr int NOBUF = (WOTOT > 0 && !IN_PLACE) ? Op::OUTBUFS : 0;
     static constexpr int TR = kTile * Op::RPT;  // records per tile (RPT records per thread)
     static constexpr bool DYNAMIC = Op::RPT == 2;  // tiles drawn from a global counter (see stream_tma_kernel)
     static constexpr bool SLOT = DYNAMIC || Op::NRED > 0;  // the launch needs a slot (scheduler and / or accumulators)
@@ -287,6 +296,39 @@ __global__ void __launch_bounds__(kTile, Op::MINB) stream_tma_kernel(const Param
             for (int w = 0; w < Op::WO1; ++w) { o1.v[w] = q1.v[w].x; o1.v[Op::WO1 + w] = q1.v[w].y; }
         }
 
+        if constexpr (!IP && G::NOBUF == 3) {
+            // ONE barrier per tile (see kOutBufs): write the output tile, then the barrier, then thread 0 refills the
+            // input stage and sends the output tile on its way
+#pragma unroll
+            for (int rr = 0; rr < Op::RPT; ++rr) {
+                if constexpr (Op::WO0 > 0) sts_record<Op::WO0>(so, tid + rr * T, o0.v + rr * Op::WO0);
+                if constexpr (Op::WO1 > 0) sts_record<Op::WO1>(so + TR * Op::WO0, tid + rr * T, o1.v + rr * Op::WO1);
+            }
+            fence_async_smem();
+            if (tid == 0) bulk_wait_read<1>();  // all stores but the latest have finished reading their buffers
+            __syncthreads();  // every thread is done with stage s (and has read s_tile[s]); `so` is complete
+            if (tid == 0) {
+                if constexpr (DYN) s_tile[s] = drawn;
+                if (drawn < nfull) issue(s, drawn);
+                if (full) {
+                    if constexpr (Op::WO0 > 0) bulk_s2g(p.out[0] + base * Op::WO0, so, (uint32_t)(TR * 4 * Op::WO0));
+                    if constexpr (Op::WO1 > 0)
+                        bulk_s2g(p.out[1] + base * Op::WO1, so + TR * Op::WO0, (uint32_t)(TR * 4 * Op::WO1));
+                    bulk_commit();
+                }
+            }
+            if (!full) {  // ragged last tile: plain coalesced word copies (no later tile reuses `so`)
+                if constexpr (Op::WO0 > 0) {
+                    float* dst = p.out[0] + base * Op::WO0;
+                    for (int w = tid; w < cnt * Op::WO0; w += T) dst[w] = so[w];
+                }
+                if constexpr (Op::WO1 > 0) {
+                    float* dst = p.out[1] + base * Op::WO1;
+                    for (int w = tid; w < cnt * Op::WO1; w += T) dst[w] = so[TR * Op::WO0 + w];
+                }
+            }
+            if (++obuf == 3) obuf = 0;
+        } else {
         if constexpr (!IP) {
             if constexpr (G::NOBUF > 0) {
                 if (tid == 0) bulk_wait_read<1>();  // the store issued two tiles ago has finished reading `so`
@@ -326,6 +368,7 @@ __global__ void __launch_bounds__(kTile, Op::MINB) stream_tma_kernel(const Param
                 }
             }
             obuf ^= 1;
+        }
         }
         if constexpr (IP) {
             refill = true;
