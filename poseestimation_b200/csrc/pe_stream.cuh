@@ -384,32 +384,75 @@ __global__ void __launch_bounds__(kTile, Op::MINB) stream_tma_kernel(const Param
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-// Non-TMA path: arbitrary alignment and arbitrary row stride on in[0].  One record per thread, grid-stride.
+// Non-TMA path: arbitrary alignment and arbitrary row stride on in[0] (the `out[:, :9]` view of a (B, 12) network
+// output, /root/reference/3D-Pose/main2.py:94).  Grid-stride, plain loads through L1.  The two-records-per-thread ops
+// (the SVD family) keep their packed fp32x2 arithmetic here too: a thread takes records i and i + ceil(n/2), holds them
+// in registers and hands them to the op's `run2` through the same lazy-source interface the TMA kernel uses (a PairSrc
+// over a thread-local array; after inlining its loads are register moves).  Measured at 2^24 matrices: svd_orth on a
+// stride-12 view 0.516 ms with one record per thread (scalar SVD), 0.347 ms packed; unaligned dense input 0.440 -> 0.334.
+// Occupancy of the packed variant (measured on a stride-12 view of 2^24 matrices): the forward is fastest at 3 CTAs/SM
+// (80 registers, a few spills: 0.346 ms against 0.400 at 2 CTAs), the ops that also hold a second input at 2 CTAs/SM
+// (128 registers: the step 0.457 ms against 0.508 at 3 CTAs and 0.613 at 1).
 template <class Op>
-__global__ void __launch_bounds__(kTile) stream_direct_kernel(const Params<Op> p) {
+constexpr int direct_min_blocks() { return Op::RPT == 2 ? (Op::WI1 == 0 ? 3 : 2) : 1; }
+template <class Op>
+__global__ void __launch_bounds__(kTile, direct_min_blocks<Op>()) stream_direct_kernel(const Params<Op> p) {
     __shared__ double s_red[32 * (Op::NRED > 0 ? Op::NRED : 1)];
     double red[Op::NRED > 0 ? Op::NRED : 1];
 #pragma unroll
     for (int k = 0; k < (Op::NRED > 0 ? Op::NRED : 1); ++k) red[k] = 0.0;
     int flag = 0;
     const long long step = (long long)gridDim.x * blockDim.x;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < p.n; i += step) {
-        RegArr<Op::WI0> i0;
-        RegArr<Op::WI1> i1;
-        RegArr<Op::WI2> i2;
-        RegArr<Op::WO0> o0;
-        RegArr<Op::WO1> o1;
+    if constexpr (Op::RPT == 2) {
+        constexpr int W0 = Op::WI0, W1 = Op::WI1, W2 = Op::WI2;
+        const long long half = (p.n + 1) / 2;
+        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < half; i += step) {
+            const bool v1 = i + half < p.n;
+            const long long j = v1 ? i + half : i;  // an odd batch: the last thread's second lane repeats its first
+            __align__(16) float l0[2 * (W0 > 0 ? W0 : 1)], l1[2 * (W1 > 0 ? W1 : 1)], l2[2 * (W2 > 0 ? W2 : 1)];
 #pragma unroll
-        for (int w = 0; w < Op::WI0; ++w) i0.v[w] = __ldg(p.in[0] + i * p.in0_stride + w);
+            for (int w = 0; w < W0; ++w) {
+                l0[w] = __ldg(p.in[0] + i * p.in0_stride + w);
+                l0[W0 + w] = __ldg(p.in[0] + j * p.in0_stride + w);
+            }
 #pragma unroll
-        for (int w = 0; w < Op::WI1; ++w) i1.v[w] = __ldg(p.in[1] + i * Op::WI1 + w);
+            for (int w = 0; w < W1; ++w) { l1[w] = __ldg(p.in[1] + i * W1 + w); l1[W1 + w] = __ldg(p.in[1] + j * W1 + w); }
 #pragma unroll
-        for (int w = 0; w < Op::WI2; ++w) i2.v[w] = __ldg(p.in[2] + i * Op::WI2 + w);
-        Op::run(i0.v, i1.v, i2.v, o0.v, o1.v, red, flag, p.ex);
+            for (int w = 0; w < W2; ++w) { l2[w] = __ldg(p.in[2] + i * W2 + w); l2[W2 + w] = __ldg(p.in[2] + j * W2 + w); }
+            PairArr<Op::WO0> q0;
+            PairArr<Op::WO1> q1;
+            Op::run2(PairSrc<W0>{l0, 0, 1}, PairSrc<W1>{l1, 0, 1}, PairSrc<W2>{l2, 0, 1}, q0.v, q1.v, red, flag, true, v1,
+                     p.ex);
 #pragma unroll
-        for (int w = 0; w < Op::WO0; ++w) p.out[0][i * Op::WO0 + w] = o0.v[w];
+            for (int w = 0; w < Op::WO0; ++w) p.out[0][i * Op::WO0 + w] = q0.v[w].x;
 #pragma unroll
-        for (int w = 0; w < Op::WO1; ++w) p.out[1][i * Op::WO1 + w] = o1.v[w];
+            for (int w = 0; w < Op::WO1; ++w) p.out[1][i * Op::WO1 + w] = q1.v[w].x;
+            if (v1) {
+#pragma unroll
+                for (int w = 0; w < Op::WO0; ++w) p.out[0][j * Op::WO0 + w] = q0.v[w].y;
+#pragma unroll
+                for (int w = 0; w < Op::WO1; ++w) p.out[1][j * Op::WO1 + w] = q1.v[w].y;
+            }
+        }
+    } else {
+        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < p.n; i += step) {
+            RegArr<Op::WI0> i0;
+            RegArr<Op::WI1> i1;
+            RegArr<Op::WI2> i2;
+            RegArr<Op::WO0> o0;
+            RegArr<Op::WO1> o1;
+#pragma unroll
+            for (int w = 0; w < Op::WI0; ++w) i0.v[w] = __ldg(p.in[0] + i * p.in0_stride + w);
+#pragma unroll
+            for (int w = 0; w < Op::WI1; ++w) i1.v[w] = __ldg(p.in[1] + i * Op::WI1 + w);
+#pragma unroll
+            for (int w = 0; w < Op::WI2; ++w) i2.v[w] = __ldg(p.in[2] + i * Op::WI2 + w);
+            Op::run(i0.v, i1.v, i2.v, o0.v, o1.v, red, flag, p.ex);
+#pragma unroll
+            for (int w = 0; w < Op::WO0; ++w) p.out[0][i * Op::WO0 + w] = o0.v[w];
+#pragma unroll
+            for (int w = 0; w < Op::WO1; ++w) p.out[1][i * Op::WO1 + w] = o1.v[w];
+        }
     }
     block_reduce_and_publish<Op>(red, flag, p.sums, p.flag, s_red, p.sched);
 }
@@ -492,6 +535,9 @@ int stream_launch(Params<Op> p, cudaStream_t stream) {
     if (p.in0_stride < G::wi(0)) return fail(PE_ERR_BAD_ARG, "row stride smaller than the record");
     LaunchCfg cfg;
     if (int rc = stream_config<Op>(&cfg)) return rc;
+    // Strided or unaligned arrays take the direct kernel.  (Tried: keeping the TMA kernel and gathering a strided in[0]
+    // tile by tile with plain coalesced loads - slower than the direct kernel, 0.49 vs 0.40 ms for svd_orth on a
+    // stride-12 view of 2^24 matrices: the gather is not prefetched and costs a barrier per tile.)
     bool tma = (p.in0_stride == G::wi(0)) && !force_direct();
     for (int k = 0; k < 3; ++k) tma = tma && (G::wi(k) == 0 || aligned16(p.in[k]));
     for (int k = 0; k < 2; ++k) tma = tma && (G::wo(k) == 0 || aligned16(p.out[k]));

@@ -387,3 +387,24 @@ def test_registered_ops_trace_under_torch_compile(rr):
     lc = torch.compile(step, backend="aot_eager", fullgraph=True)(xc, rt)
     lc.backward()
     assert abs(float(le) - float(lc)) <= 1e-6 and torch.equal(xe.grad, xc.grad)
+
+
+@pytest.mark.parametrize("n", [1, 2, 3, 512, 1001, 70001])
+def test_strided_view_runs_the_packed_direct_kernels(ops, rr, n):
+    """A stride-12 view goes through the non-TMA kernels, which keep two matrices per thread (records i and
+    i + ceil(n/2)): forward, recompute backward and the single-pass step must equal the dense TMA route bit for bit,
+    for odd and even batch sizes."""
+    g = torch.Generator(device="cuda").manual_seed(n)
+    wide = torch.randn(n, 12, device="cuda", generator=g)
+    view, dense = wide[:, :9], wide[:, :9].contiguous()
+    up = torch.randn(n, 3, 3, device="cuda", generator=g)
+    rt = rr.symmetric_orthogonalization(torch.randn(n, 9, device="cuda", generator=g))
+    r_v, d_v = ops.svd_orth_det(view)
+    r_d, d_d = ops.svd_orth_det(dense)
+    assert torch.equal(r_v, r_d) and torch.equal(d_v, d_d)
+    assert torch.equal(ops.svd_orth(view), r_d)
+    assert torch.equal(ops.svd_orth_bwd_recompute(view, up), ops.svd_orth_bwd_recompute(dense, up))
+    l_v, g_v = ops.svd_orth_frobenius_step(view, rt)
+    l_d, g_d = ops.svd_orth_frobenius_step(dense, rt)
+    assert torch.equal(g_v, g_d) and abs(float(l_v) - float(l_d)) <= 1e-6
+    assert abs(float(rr.map_metric("SVD", view, rt)) - float(rr.map_metric("SVD", dense, rt))) <= 1e-9 * 180
