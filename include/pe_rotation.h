@@ -74,6 +74,9 @@ int pe_expmap_bwd(const float* v, int64_t v_stride, const float* g, float* dv, i
 /* ---- a5  loss_frobenius(R_pred, R_true)                 Comparison/main.py:12-16 (+ 7 copies) ----------------
  * *sum = sum_b |a_b - b_b|_F (the caller divides by n: the mean of line 16; across ranks the sums all-reduce). */
 int pe_frobenius_fwd(const float* a, const float* b, double* sum, int64_t n, void* stream);
+/* the same, and *mean = (float)(*sum / n) written by the same launch: the 0-d float32 tensor loss_frobenius returns
+ * (line 16), without a second launch that divides and casts.  n == 0: *sum = 0, *mean = NaN (torch's empty mean). */
+int pe_frobenius_mean_fwd(const float* a, const float* b, double* sum, float* mean, int64_t n, void* stream);
 /* da = gscale * (a - b)/|a - b|_F, db = -da, with gscale = (*gout) * inv_n; 0 where the norm is 0.
  * gout is a device scalar (the upstream gradient of the 0-d loss); da or db may be NULL. */
 int pe_frobenius_bwd(const float* a, const float* b, const float* gout, float inv_n, float* da, float* db,
@@ -113,6 +116,9 @@ int pe_svd_orth_frobenius_bwd(const float* m, int64_t m_stride, const float* r_t
  * batch-mean loss for an upstream gradient of 1.  The autograd backward is then pe_scale_by_scalar(dm, gout). */
 int pe_svd_orth_frobenius_step(const float* m, int64_t m_stride, const float* r_true, float inv_n, float* dm,
                                double* sum, int64_t n, void* stream);
+/* the same, and *mean = (float)(*sum / n): the loss tensor itself, written by the launch's last CTA. */
+int pe_svd_orth_frobenius_step_mean(const float* m, int64_t m_stride, const float* r_true, float inv_n, float* dm,
+                                    double* sum, float* mean, int64_t n, void* stream);
 /* y[i] = x[i] * (*g) for nwords floats; g is a DEVICE scalar (no host sync); x, y 16-byte aligned, y may alias x. */
 int pe_scale_by_scalar(const float* x, const float* g, float* y, int64_t nwords, void* stream);
 /* x[i] *= (*g) in place; does nothing when *g == 1 (tested on the device, no host sync): the backward of the

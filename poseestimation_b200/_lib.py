@@ -32,6 +32,7 @@ SIGNATURES = {
     "pe_expmap_fwd": [_f, _i64, _f, _i64, _f],
     "pe_expmap_bwd": [_f, _i64, _f, _f, _i64, _f],
     "pe_frobenius_fwd": [_f, _f, _f, _i64, _f],
+    "pe_frobenius_mean_fwd": [_f, _f, _f, _f, _i64, _f],
     "pe_frobenius_bwd": [_f, _f, _f, _flt, _f, _f, _i64, _f],
     "pe_geodesic_fwd": [_f, _f, _flt, _flt, _f, _f, _i64, _f],
     "pe_geodesic_bwd": [_f, _f, _flt, _flt, _f, _int, _flt, _f, _f, _i64, _f],
@@ -39,6 +40,7 @@ SIGNATURES = {
     "pe_svd_orth_frobenius_fwd": [_f, _i64, _f, _f, _f, _i64, _f],
     "pe_svd_orth_frobenius_bwd": [_f, _i64, _f, _f, _flt, _f, _i64, _f],
     "pe_svd_orth_frobenius_step": [_f, _i64, _f, _flt, _f, _f, _i64, _f],
+    "pe_svd_orth_frobenius_step_mean": [_f, _i64, _f, _flt, _f, _f, _f, _i64, _f],
     "pe_scale_by_scalar": [_f, _f, _f, _i64, _f],
     "pe_scale_by_scalar_inplace": [_f, _f, _i64, _f],
     "pe_map_metric_fwd": [_int, _int, _f, _i64, _f, _flt, _flt, _f, _f, _i64, _f],

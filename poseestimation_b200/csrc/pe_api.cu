@@ -14,6 +14,8 @@ Params<Op> make_params(const float* i0, long long stride0, const float* i1, cons
     p.n = n;
     p.in0_stride = stride0;
     p.sums = sums;
+    p.mean32 = nullptr;
+    p.mean_scale = 0.0;
     p.flag = flag;
     p.sched = nullptr;  // assigned by stream_launch
     p.ex = ex;
@@ -22,7 +24,7 @@ Params<Op> make_params(const float* i0, long long stride0, const float* i1, cons
 
 template <class Op>
 int run(const float* i0, long long stride0, const float* i1, const float* i2, float* o0, float* o1, long long n,
-        double* sums, int* flag, typename Op::Extra ex, void* stream) {
+        double* sums, int* flag, typename Op::Extra ex, void* stream, float* mean32 = nullptr, double mean_scale = 0.0) {
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (n < 0) return fail(PE_ERR_BAD_ARG, "negative record count");
     // natural alignment of every array (a misaligned access would be a sticky device fault, not an error code)
@@ -42,7 +44,17 @@ int run(const float* i0, long long stride0, const float* i1, const float* i2, fl
         cudaError_t e = cudaMemsetAsync(flag, 0, sizeof(int), st);
         if (e != cudaSuccess) return fail_cuda(e, "cudaMemsetAsync(flag)");
     }
-    return stream_launch<Op>(make_params<Op>(i0, stride0, i1, i2, o0, o1, n, sums, flag, ex), st);
+    Params<Op> p = make_params<Op>(i0, stride0, i1, i2, o0, o1, n, sums, flag, ex);
+    if (mean32) {
+        if (reinterpret_cast<uintptr_t>(mean32) & 3u) return fail(PE_ERR_BAD_ARG, "array not aligned to 4 bytes");
+        if (n == 0) {  // the mean of an empty batch is NaN, as torch's (all-ones bits are a quiet NaN)
+            cudaError_t e = cudaMemsetAsync(mean32, 0xFF, sizeof(float) * Op::NRED, st);
+            if (e != cudaSuccess) return fail_cuda(e, "cudaMemsetAsync(mean)");
+        }
+        p.mean32 = mean32;
+        p.mean_scale = mean_scale;
+    }
+    return stream_launch<Op>(p, st);
 }
 
 // y = x * (*g): the backward of a single-pass step (the gradient for a unit upstream gradient times the upstream
@@ -128,6 +140,11 @@ PE_MAP_API(expmap, Expmap)
 int pe_frobenius_fwd(const float* a, const float* b, double* sum, int64_t n, void* stream) {
     return run<FrobFwd>(a, 9, b, nullptr, nullptr, nullptr, n, sum, nullptr, {}, stream);
 }
+int pe_frobenius_mean_fwd(const float* a, const float* b, double* sum, float* mean, int64_t n, void* stream) {
+    if (!mean) return fail(PE_ERR_BAD_ARG, "null mean pointer");
+    return run<FrobFwd>(a, 9, b, nullptr, nullptr, nullptr, n, sum, nullptr, {}, stream, mean,
+                        n > 0 ? 1.0 / (double)n : 0.0);
+}
 int pe_frobenius_bwd(const float* a, const float* b, const float* gout, float inv_n, float* da, float* db,
                      int64_t n, void* stream) {
     if (!gout) return fail(PE_ERR_BAD_ARG, "null upstream-gradient pointer");
@@ -184,6 +201,12 @@ int pe_svd_orth_frobenius_bwd(const float* m, int64_t m_stride, const float* r_t
 int pe_svd_orth_frobenius_step(const float* m, int64_t m_stride, const float* r_true, float inv_n, float* dm,
                                double* sum, int64_t n, void* stream) {
     return run<SvdFrobStep>(m, m_stride, r_true, nullptr, dm, nullptr, n, sum, nullptr, {inv_n}, stream);
+}
+int pe_svd_orth_frobenius_step_mean(const float* m, int64_t m_stride, const float* r_true, float inv_n, float* dm,
+                                    double* sum, float* mean, int64_t n, void* stream) {
+    if (!mean) return fail(PE_ERR_BAD_ARG, "null mean pointer");
+    return run<SvdFrobStep>(m, m_stride, r_true, nullptr, dm, nullptr, n, sum, nullptr, {inv_n}, stream, mean,
+                            n > 0 ? 1.0 / (double)n : 0.0);
 }
 int pe_axis_angle_fwd(const float* theta, const float* axis, float* r, int64_t n, void* stream) {
     return run<AxisAngleFwd>(theta, 1, axis, nullptr, r, nullptr, n, nullptr, nullptr, {}, stream);

@@ -46,6 +46,8 @@ struct Params {
     long long n;           // records
     long long in0_stride;  // words between consecutive records of in[0] (direct kernel only)
     double* sums;          // NRED results (device): written once, by the last CTA to finish
+    float* mean32;         // optional: (float)(sums[k] * mean_scale) next to them, written by the same CTA - the float32
+    double mean_scale;     // batch mean a loss function returns, without a follow-up launch that divides and casts
     int* flag;             // OR-ed with the per-record flags
     unsigned int* sched;   // this launch's slot (set by stream_launch): {next tile to hand out, CTAs finished, -, -,
                            // two float64 accumulators}; all zero when idle, re-armed by the last CTA
@@ -104,7 +106,8 @@ __device__ __forceinline__ void sts_pair(float* s, int t, int stride, const F2* 
 // its last index before it gets here.
 template <class Op>
 __device__ __forceinline__ void block_reduce_and_publish(double* red, int flag, double* sums, int* flagp,
-                                                         double* scratch, unsigned int* slot) {
+                                                         double* scratch, unsigned int* slot, float* mean32 = nullptr,
+                                                         double mean_scale = 0.0) {
     static_assert(Op::NRED <= 2, "a slot holds two accumulators");
     double* acc = reinterpret_cast<double*>(slot + 4);
     if constexpr (Op::NRED > 0) {
@@ -135,7 +138,9 @@ __device__ __forceinline__ void block_reduce_and_publish(double* red, int flag, 
                 __threadfence();
 #pragma unroll
                 for (int k = 0; k < Op::NRED; ++k) {
-                    sums[k] = __ldcg(acc + k);  // L2: where the other CTAs' atomics landed
+                    const double v = __ldcg(acc + k);  // L2: where the other CTAs' atomics landed
+                    sums[k] = v;
+                    if (mean32) mean32[k] = (float)(v * mean_scale);
                     acc[k] = 0.0;
                 }
                 slot[0] = 0u;
@@ -380,7 +385,7 @@ __global__ void __launch_bounds__(kTile, Op::MINB) stream_tma_kernel(const Param
     if constexpr (G::WOTOT > 0) {
         if (tid == 0) bulk_wait<0>();  // shared memory must outlive the stores that read it
     }
-    block_reduce_and_publish<Op>(red, flag, p.sums, p.flag, s_red, p.sched);
+    block_reduce_and_publish<Op>(red, flag, p.sums, p.flag, s_red, p.sched, p.mean32, p.mean_scale);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -454,7 +459,7 @@ __global__ void __launch_bounds__(kTile, direct_min_blocks<Op>()) stream_direct_
             for (int w = 0; w < Op::WO1; ++w) p.out[1][i * Op::WO1 + w] = o1.v[w];
         }
     }
-    block_reduce_and_publish<Op>(red, flag, p.sums, p.flag, s_red, p.sched);
+    block_reduce_and_publish<Op>(red, flag, p.sums, p.flag, s_red, p.sched, p.mean32, p.mean_scale);
 }
 
 // ---------------------------------------------------------------------------------------------------------------

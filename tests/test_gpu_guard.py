@@ -104,6 +104,12 @@ def test_record_kernels_stay_inside_their_outputs(abi, n, off):
     s = out(2, f64=True)
     _call(abi, "pe_frobenius_fwd", rot.ptr, rot2.ptr, s.ptr, n, st)
     done("pe_frobenius_fwd")
+    s, mean = out(2, f64=True), out(1)
+    _call(abi, "pe_frobenius_mean_fwd", rot.ptr, rot2.ptr, s.ptr, mean.ptr, n, st)
+    torch.cuda.synchronize()
+    ref = float(s.words().view(torch.float64)[0]) / n
+    assert abs(float(mean.f32(1)[0]) - ref) <= 1.2e-7 * abs(ref)           # (float)(sum * (1/n)): one rounding
+    done("pe_frobenius_mean_fwd")
     da, db = out(9 * n), out(9 * n)
     _call(abi, "pe_frobenius_bwd", rot.ptr, rot2.ptr, one.ptr, 1.0 / n, da.ptr, db.ptr, n, st)
     done("pe_frobenius_bwd")
@@ -130,6 +136,14 @@ def test_record_kernels_stay_inside_their_outputs(abi, n, off):
     dm, s = out(9 * n), out(2, f64=True)
     _call(abi, "pe_svd_orth_frobenius_step", m.ptr, 9, rot2.ptr, 1.0 / n, dm.ptr, s.ptr, n, st)
     done("pe_svd_orth_frobenius_step")
+    dm2, s2, mean = out(9 * n), out(2, f64=True), out(1)
+    _call(abi, "pe_svd_orth_frobenius_step_mean", m.ptr, 9, rot2.ptr, 1.0 / n, dm2.ptr, s2.ptr, mean.ptr, n, st)
+    torch.cuda.synchronize()
+    ref = float(s2.words().view(torch.float64)[0]) / n
+    assert abs(float(mean.f32(1)[0]) - ref) <= 1.2e-7 * abs(ref)
+    assert abs(float(s2.words().view(torch.float64)[0]) - float(s.words().view(torch.float64)[0])) <= 1e-9 * n
+    assert torch.equal(dm2.words(), dm.words())
+    done("pe_svd_orth_frobenius_step_mean")
     if off == 0:                                                    # documented: 16-byte aligned arrays only
         y = out(9 * n)
         _call(abi, "pe_scale_by_scalar", m.ptr, one.ptr, y.ptr, 9 * n, st)
