@@ -218,7 +218,10 @@ PE_DEV F2 f2_mul(F2 a, F2 b) {
 // mean +- rho of its 2x2 Gram matrix, which the angle computation has already formed, so a TRACKED rotation needs one
 // dot product (3 FMA-pipe instructions) instead of three (9).  FRESH recomputes both norms from the columns; the last
 // kFreshTail rotations are fresh, so rounding drift of the tracked values cannot reach the result.
-constexpr int kFreshTail = 1;
+#ifndef PE_FRESH_TAIL
+#define PE_FRESH_TAIL 1
+#endif
+constexpr int kFreshTail = PE_FRESH_TAIL;
 template <bool FRESH>
 PE_DEV void hestenes_a(F2& p01, float& p2, F2& q01, float& q2, float& np, float& nq) {
     float al = FRESH ? fmaf(p2, p2, fmaf(p01.y, p01.y, p01.x * p01.x)) : np;
