@@ -20,8 +20,16 @@ constexpr int stages_for(int witot, int wotot, int budget = 54 * 1024, int nbuf 
 // (measured: pose_update_bwd, 45 KB per stage, 0.077 ms with two buffers, 0.093 ms with three; every other op is as fast
 // or up to 8 % faster with three).
 constexpr int outbufs_for(int witot, int wotot) {
-    return wotot == 0 ? 0 : (kOutBufs == 3 && kTile * 4 * witot <= 32 * 1024 ? 3 : 2);
+    return wotot == 0 ? 0 : (kOutBufs >= 3 && kTile * 4 * witot <= 32 * 1024 ? kOutBufs : 2);
 }
+
+// Shared-memory budget of a one-record-per-thread CTA.  54 KB = 4 CTAs/SM.  Measured alternatives (r1m, 2^24 records):
+// 36 KB (6 CTAs/SM) gains 5-6 % on euler_bwd / expmap_bwd, 0-1 % on the write-heavy forward maps and loses 1 % on the
+// float64 angle-error kernels; a four-buffer output ring (-DPE_OUT_BUFS=4) gains 3.6 % on ortho6d_fwd and nothing
+// elsewhere.  Neither is a clear win, so the defaults stay; the forward maps are not limited by stores in flight.
+#ifndef PE_LIGHT_BUDGET
+#define PE_LIGHT_BUDGET (54 * 1024)
+#endif
 
 struct NoExtra {};
 
@@ -30,10 +38,10 @@ struct NoExtra {};
     static constexpr bool FLAG = (FL);                                                       \
     static constexpr int RPT = (R);                                                          \
     static constexpr bool kInPlace = (R) == 2 && WO0 == WI0 && WO1 == 0;                     \
-    static constexpr int kBudget = (R) == 2 && (MB) < 4 ? 75 * 1024 : 54 * 1024;                 \
+    static constexpr int kBudget = (R) == 2 && (MB) < 4 ? 75 * 1024 : PE_LIGHT_BUDGET;           \
     static constexpr int OUTBUFS = outbufs_for((R) * (WI0 + WI1 + WI2), kInPlace ? 0 : (R) * (WO0 + WO1)); \
     static constexpr int STAGES = stages_for((R) * (WI0 + WI1 + WI2), kInPlace ? 0 : (R) * (WO0 + WO1), kBudget, \
-                                             OUTBUFS == 3 ? 3 : 2);                              \
+                                             OUTBUFS >= 3 ? OUTBUFS : 2);                              \
     static constexpr int MINB = (MB);                                                        \
     static const char* name() { return NAME; }
 // one record per thread

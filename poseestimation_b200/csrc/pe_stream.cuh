@@ -301,7 +301,7 @@ __global__ void __launch_bounds__(kTile, Op::MINB) stream_tma_kernel(const Param
             for (int w = 0; w < Op::WO1; ++w) { o1.v[w] = q1.v[w].x; o1.v[Op::WO1 + w] = q1.v[w].y; }
         }
 
-        if constexpr (!IP && G::NOBUF == 3) {
+        if constexpr (!IP && G::NOBUF >= 3) {
             // ONE barrier per tile (see kOutBufs): write the output tile, then the barrier, then thread 0 refills the
             // input stage and sends the output tile on its way
 #pragma unroll
@@ -310,7 +310,7 @@ __global__ void __launch_bounds__(kTile, Op::MINB) stream_tma_kernel(const Param
                 if constexpr (Op::WO1 > 0) sts_record<Op::WO1>(so + TR * Op::WO0, tid + rr * T, o1.v + rr * Op::WO1);
             }
             fence_async_smem();
-            if (tid == 0) bulk_wait_read<1>();  // all stores but the latest have finished reading their buffers
+            if (tid == 0) bulk_wait_read<G::NOBUF - 2>();  // all stores but the latest NOBUF-2 have finished reading their buffers
             __syncthreads();  // every thread is done with stage s (and has read s_tile[s]); `so` is complete
             if (tid == 0) {
                 if constexpr (DYN) s_tile[s] = drawn;
@@ -332,7 +332,7 @@ __global__ void __launch_bounds__(kTile, Op::MINB) stream_tma_kernel(const Param
                     for (int w = tid; w < cnt * Op::WO1; w += T) dst[w] = so[TR * Op::WO0 + w];
                 }
             }
-            if (++obuf == 3) obuf = 0;
+            if (++obuf == G::NOBUF) obuf = 0;
         } else {
         if constexpr (!IP) {
             if constexpr (G::NOBUF > 0) {
