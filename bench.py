@@ -17,7 +17,8 @@ under "also".
 
   value        whole-job matrices/s with x, R_true resident in HBM (CUDA events, max over ranks)
   e2e          same step through the public API (rotation_representation.svd_frobenius_loss + autograd) with HOST
-               pinned inputs: H2D of x and R_true and D2H of the loss inside the timed region
+               pinned inputs: H2D of x and R_true and D2H of the loss inside the timed region (the copies of step
+               i+1 are issued on a copy stream while step i computes, as a data loader would)
   roofline     dominant kernel (the step kernel): algorithmic bytes / event-timed duration vs MEASURED_PEAKS.json
   cpu_baseline the oracle port (= the reference's torch code) in fp32 on this box's host cores, bounded sample
   --impl reference   times that CPU implementation as the headline instead (rank 0 only)
