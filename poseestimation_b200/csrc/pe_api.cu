@@ -63,6 +63,8 @@ __global__ void __launch_bounds__(256) scale_by_scalar_kernel(const float4* __re
                                                               float4* __restrict__ y, long long n4,
                                                               const float* __restrict__ xt, float* __restrict__ yt,
                                                               int tail) {
+    pdl_wait();
+    pdl_launch_dependents();
     const float k = __ldg(g);
     const long long step = (long long)gridDim.x * blockDim.x;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += step) {
@@ -79,6 +81,8 @@ __global__ void __launch_bounds__(256) scale_by_scalar_kernel(const float4* __re
 // holds the launch costs a few microseconds instead of a 72 B/matrix pass.
 __global__ void __launch_bounds__(1024) scale_inplace_kernel(float4* __restrict__ x, const float* __restrict__ g,
                                                             long long n4, float* __restrict__ xt, int tail) {
+    pdl_wait();
+    pdl_launch_dependents();
     const float k = __ldg(g);
     if (k == 1.0f) return;
     const long long step = (long long)gridDim.x * blockDim.x;
@@ -279,9 +283,9 @@ int pe_scale_by_scalar_inplace(float* x, const float* g, int64_t nwords, void* s
     long long grid = (n4 + 1023) / 1024;
     if (grid > (long long)sms * 2) grid = (long long)sms * 2;
     if (grid < 1) grid = 1;
-    scale_inplace_kernel<<<(unsigned)grid, 1024, 0, static_cast<cudaStream_t>(stream)>>>(
-        reinterpret_cast<float4*>(x), g, n4, x + 4 * n4, (int)(nwords - 4 * n4));
-    e = cudaGetLastError();
+    e = launch_pdl(scale_inplace_kernel, (unsigned)grid, 1024u, 0, static_cast<cudaStream_t>(stream),
+                   reinterpret_cast<float4*>(x), g, (long long)n4, x + 4 * n4, (int)(nwords - 4 * n4));
+    if (e == cudaSuccess) e = cudaGetLastError();
     if (e != cudaSuccess) return fail_cuda(e, "scale_inplace");
     count_launch();
     return 0;

@@ -35,4 +35,33 @@ inline bool force_direct() {
     return v && v[0] == '1';
 }
 
+// Programmatic dependent launch.  The streaming kernels and the scaling kernels are launched with
+// cudaLaunchAttributeProgrammaticStreamSerialization: their CTAs may be scheduled while the previous kernel of the
+// stream is still draining, and block in `griddepcontrol.wait` (first statement of the kernel, before any global
+// access) until that kernel has completed and its writes are visible - so the launch latency and the CTA start-up hide
+// behind the predecessor's tail, whatever the predecessor is.  PE_NO_PDL=1 switches the attribute off (A/B runs).
+inline bool pdl_enabled() {
+    static const bool on = [] { const char* v = getenv("PE_NO_PDL"); return !(v && v[0] == '1'); }();
+    return on;
+}
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+template <class... KArgs, class... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), unsigned grid, unsigned block, size_t smem, cudaStream_t st,
+                              Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(block);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, args...);
+}
+#endif
+
 }  // namespace pe

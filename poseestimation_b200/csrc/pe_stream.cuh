@@ -176,6 +176,8 @@ __global__ void __launch_bounds__(kTile, Op::MINB) stream_tma_kernel(const Param
     using G = Geometry<Op>;
     constexpr int T = kTile, TR = G::TR, S = Op::STAGES;
     constexpr bool IP = G::IN_PLACE;  // the output record overwrites the thread's own in[0] record in the stage
+    pdl_wait();               // programmatic dependent launch (pe_common.h): the predecessor is complete from here on
+    pdl_launch_dependents();  // and the successor may be scheduled as soon as CTAs of this grid retire
     extern __shared__ __align__(128) unsigned char smem_raw[];
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw);
     float* s_in = reinterpret_cast<float*>(smem_raw + G::kBarBytes);
@@ -586,7 +588,8 @@ int stream_launch(Params<Op> p, cudaStream_t stream) {
         if constexpr (G::SLOT) {
             if (int rc = sched_slot(&p.sched)) return rc;
         }
-        stream_tma_kernel<Op><<<(unsigned)grid, kTile, G::kSmemBytes, stream>>>(p);
+        cudaError_t le = launch_pdl(stream_tma_kernel<Op>, (unsigned)grid, (unsigned)kTile, (size_t)G::kSmemBytes, stream, p);
+        if (le != cudaSuccess) return fail_cuda(le, Op::name());
     } else {
         long long grid = (long long)cfg.sms * 8;
         if (grid > ntiles) grid = ntiles;
