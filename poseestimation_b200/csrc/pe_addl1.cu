@@ -95,6 +95,8 @@ __device__ __forceinline__ float transpose_reduce16(float* v, int lane) {
 
 template <bool TMA>
 __global__ void __launch_bounds__(kAWarps * 32, 1) add_l1_kernel(const AddL1Params prm) {
+    pdl_wait();               // programmatic dependent launch (pe_common.h)
+    pdl_launch_dependents();
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw) + warp * kAStages;
@@ -300,8 +302,8 @@ extern "C" int pe_add_l1(const float* t_gt, const float* t_pred, const float* pt
     }
     long long grid = ((b << prm.lg_split) + kAWarps - 1) / kAWarps;
     if (grid > sms[dev]) grid = sms[dev];
-    if (prm.use_tma) add_l1_kernel<true><<<(unsigned)grid, kAWarps * 32, kASmem, st>>>(prm);
-    else add_l1_kernel<false><<<(unsigned)grid, kAWarps * 32, 0, st>>>(prm);
+    if (prm.use_tma) launch_pdl(add_l1_kernel<true>, (unsigned)grid, (unsigned)(kAWarps * 32), (size_t)kASmem, st, prm);
+    else launch_pdl(add_l1_kernel<false>, (unsigned)grid, (unsigned)(kAWarps * 32), (size_t)0, st, prm);
     e = cudaGetLastError();
     if (e != cudaSuccess) return fail_cuda(e, "add_l1_kernel");
     count_launch();

@@ -70,6 +70,8 @@ struct CloudWalk {
 
 // npts % 4 == 0 and 16-byte aligned arrays: one thread = 4 points of one cloud
 __global__ void __launch_bounds__(256) affine_points_vec4_kernel(const AffineParams prm) {
+    pdl_wait();               // programmatic dependent launch (pe_common.h)
+    pdl_launch_dependents();
     const long long groups = prm.b * prm.npts / 4;
     const long long gpc = prm.npts / 4;  // groups per cloud
     const long long step = (long long)gridDim.x * blockDim.x;
@@ -92,6 +94,8 @@ __global__ void __launch_bounds__(256) affine_points_vec4_kernel(const AffinePar
 
 // any npts / alignment: one thread = one point
 __global__ void __launch_bounds__(256) affine_points_scalar_kernel(const AffineParams prm) {
+    pdl_wait();               // programmatic dependent launch (pe_common.h)
+    pdl_launch_dependents();
     const long long total = prm.b * prm.npts;
     const long long step = (long long)gridDim.x * blockDim.x;
     const long long first = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -165,6 +169,8 @@ __device__ __forceinline__ void wbwd_point(const WBwdCoeffs& c, float w, float p
 
 // npts % 4 == 0 and 16-byte aligned arrays: one thread = 4 points of one cloud (7 LDG.128, up to 7 STG.128)
 __global__ void __launch_bounds__(256) kabsch_weighted_bwd_vec4_kernel(const WBwdParams prm) {
+    pdl_wait();               // programmatic dependent launch (pe_common.h)
+    pdl_launch_dependents();
     const long long groups = prm.b * prm.npts / 4;
     const long long gpc = prm.npts / 4;
     const long long step = (long long)gridDim.x * blockDim.x;
@@ -202,6 +208,8 @@ __global__ void __launch_bounds__(256) kabsch_weighted_bwd_vec4_kernel(const WBw
 
 // any npts / alignment: one thread = one point
 __global__ void __launch_bounds__(256) kabsch_weighted_bwd_scalar_kernel(const WBwdParams prm) {
+    pdl_wait();               // programmatic dependent launch (pe_common.h)
+    pdl_launch_dependents();
     const long long total = prm.b * prm.npts;
     const long long step = (long long)gridDim.x * blockDim.x;
     const long long first = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -242,8 +250,8 @@ extern "C" int pe_kabsch_weighted_bwd_points(const float* p, const float* q, con
     long long grid = (work + 255) / 256;
     if (grid > (long long)sms * 8) grid = (long long)sms * 8;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    if (vec) kabsch_weighted_bwd_vec4_kernel<<<(unsigned)grid, 256, 0, st>>>(prm);
-    else kabsch_weighted_bwd_scalar_kernel<<<(unsigned)grid, 256, 0, st>>>(prm);
+    if (vec) launch_pdl(kabsch_weighted_bwd_vec4_kernel, (unsigned)grid, 256u, (size_t)0, st, prm);
+    else launch_pdl(kabsch_weighted_bwd_scalar_kernel, (unsigned)grid, 256u, (size_t)0, st, prm);
     e = cudaGetLastError();
     if (e != cudaSuccess) return fail_cuda(e, "kabsch_weighted_bwd_points");
     count_launch();
@@ -270,8 +278,8 @@ extern "C" int pe_affine_points(const float* a, int64_t a_stride, int a_row, int
     long long grid = (work + 255) / 256;
     if (grid > (long long)sms * 8) grid = (long long)sms * 8;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    if (vec) affine_points_vec4_kernel<<<(unsigned)grid, 256, 0, st>>>(prm);
-    else affine_points_scalar_kernel<<<(unsigned)grid, 256, 0, st>>>(prm);
+    if (vec) launch_pdl(affine_points_vec4_kernel, (unsigned)grid, 256u, (size_t)0, st, prm);
+    else launch_pdl(affine_points_scalar_kernel, (unsigned)grid, 256u, (size_t)0, st, prm);
     e = cudaGetLastError();
     if (e != cudaSuccess) return fail_cuda(e, "affine_points");
     count_launch();

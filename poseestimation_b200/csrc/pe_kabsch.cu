@@ -51,6 +51,8 @@ __device__ __forceinline__ float warp_sum_f(float v) {
 
 template <bool WT>
 __global__ void __launch_bounds__(kKWarps * 32, 1) kabsch_kernel(const KabschParams prm) {
+    pdl_wait();               // programmatic dependent launch (pe_common.h)
+    pdl_launch_dependents();
     constexpr int kKStageWords = KGeo<WT>::kStageWords;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -257,8 +259,8 @@ int kabsch_launch(KabschParams prm, void* stream) {
     long long grid = (prm.b + kKWarps - 1) / kKWarps;
     if (grid > sms[dev]) grid = sms[dev];
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    if (weighted) kabsch_kernel<true><<<(unsigned)grid, kKWarps * 32, KGeo<true>::kSmem, st>>>(prm);
-    else kabsch_kernel<false><<<(unsigned)grid, kKWarps * 32, KGeo<false>::kSmem, st>>>(prm);
+    if (weighted) launch_pdl(kabsch_kernel<true>, (unsigned)grid, (unsigned)(kKWarps * 32), (size_t)KGeo<true>::kSmem, st, prm);
+    else launch_pdl(kabsch_kernel<false>, (unsigned)grid, (unsigned)(kKWarps * 32), (size_t)KGeo<false>::kSmem, st, prm);
     e = cudaGetLastError();
     if (e != cudaSuccess) return fail_cuda(e, "kabsch_kernel");
     count_launch();
