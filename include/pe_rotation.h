@@ -6,9 +6,14 @@
  * /root/reference).  INTEGRATION.md shows the ctypes stub for each.
  *
  * Conventions (all entry points):
- *   - every pointer is a DEVICE pointer into memory the caller owns (PyTorch's allocator); the library keeps no state
- *     between calls and owns one piece of device memory: 32 KB per device of tile-scheduler slots, allocated on the
- *     first launch of an SVD kernel (which therefore must not happen inside a CUDA-graph capture);
+ *   - every pointer is a DEVICE pointer into memory the caller owns (PyTorch's allocator).  The library owns one piece of
+ *     device memory: 128 KB per device of 32-byte launch slots (tile counter + two float64 accumulators), allocated and
+ *     zeroed by pe_init(device).  An eager launch uses the slot of its (device, stream) - launches on one stream never
+ *     overlap, so they can share it for ever; a launch recorded by a stream capture gets a slot of its own that no eager
+ *     launch and no other captured launch ever uses, so graphs may replay next to eager work.  Call pe_init before
+ *     capturing (an un-initialised device is initialised by its first eager launch; inside a capture that is refused
+ *     with PE_ERR_BAD_ARG because it would allocate).  pe_svd_orth_frobenius_step_metrics also takes caller-owned
+ *     scratch instead of a slot;
  *   - a "matrix" is 9 consecutive floats, row-major: m[3*i + j] = M[i][j]  (x.view(-1, 3, 3));
  *   - `n` is the number of records (matrices / vectors); n == 0 is a no-op that still zeroes accumulators;
  *   - `*_stride` is the distance in FLOATS between consecutive input records (9 for a dense (n, 9) array, 12 for
@@ -30,7 +35,7 @@
 extern "C" {
 #endif
 
-#define PE_VERSION 100 /* 0.1.0 */
+#define PE_VERSION 200 /* 0.2.0 */
 
 #define PE_ERR_BAD_ARG (-1)   /* null pointer, negative count, stride smaller than the record, array not naturally
                                  aligned (float: 4 bytes, double: 8 bytes) */
@@ -41,6 +46,9 @@ int pe_version(void);
 const char* pe_last_error(void);
 /* kernels launched by this process through the library so far (bench.py's gpu_launches) */
 long long pe_launch_count(void);
+/* Allocate and zero the launch slots of `device` (a CUDA device ordinal; < 0 = the current device).  Idempotent,
+ * thread-safe, synchronises the device once.  Nothing else in the library allocates. */
+int pe_init(int device);
 
 /* ---- a1  symmetric_orthogonalization(x)                 rotation_representation.py:192-206 ------------------
  * r[n][9] = U diag(1, 1, det(U V^T)) V^T with m = U S V^T.  det_sign (nullable, n floats) receives the factor
@@ -119,6 +127,19 @@ int pe_svd_orth_frobenius_step(const float* m, int64_t m_stride, const float* r_
 /* the same, and *mean = (float)(*sum / n): the loss tensor itself, written by the launch's last CTA. */
 int pe_svd_orth_frobenius_step_mean(const float* m, int64_t m_stride, const float* r_true, float inv_n, float* dm,
                                     double* sum, float* mean, int64_t n, void* stream);
+/* The training step with its metric (Comparison/main.py:59-70, 3D-Pose/main.py:60-62,85-91: loss_frobenius(outR, R)
+ * and angle_error(outR, R) from the same outR):  as pe_svd_orth_frobenius_step, and additionally
+ *   sums[0] = sum_b |r_true_b - r_b|_F,  sums[1] = sum_b angle_error(r_b, r_true_b) in degrees (float64 trace and acos
+ *   of the fp32 r the step would have written, rotation_representation.py:230-242),
+ *   *flag |= 1 if a cosine left [-1.1, 1.1] (:237; the binding raises ValueError),
+ *   *loss_mean (nullable) = (float)(sums[0] / n),  *angle_mean (nullable) = sums[1] / n.
+ * [sums[0], sums[1], n] is the vector the ranks all-reduce.
+ * scratch: NULL, or 32 bytes of caller-owned device memory, 8-byte aligned, zero before its first use (the launch
+ * leaves it zero again): then the launch touches no library-owned memory at all - one scratch per launch that can be
+ * in flight at a time (e.g. per captured graph node). */
+int pe_svd_orth_frobenius_step_metrics(const float* m, int64_t m_stride, const float* r_true, float inv_n, float* dm,
+                                       double* sums, float* loss_mean, double* angle_mean, int* flag, void* scratch,
+                                       int64_t n, void* stream);
 /* y[i] = x[i] * (*g) for nwords floats; g is a DEVICE scalar (no host sync); x, y 16-byte aligned, y may alias x. */
 int pe_scale_by_scalar(const float* x, const float* g, float* y, int64_t nwords, void* stream);
 /* x[i] *= (*g) in place; does nothing when *g == 1 (tested on the device, no host sync): the backward of the

@@ -41,6 +41,7 @@ SIGNATURES = {
     "pe_svd_orth_frobenius_bwd": [_f, _i64, _f, _f, _flt, _f, _i64, _f],
     "pe_svd_orth_frobenius_step": [_f, _i64, _f, _flt, _f, _f, _i64, _f],
     "pe_svd_orth_frobenius_step_mean": [_f, _i64, _f, _flt, _f, _f, _f, _i64, _f],
+    "pe_svd_orth_frobenius_step_metrics": [_f, _i64, _f, _flt, _f, _f, _f, _f, _f, _f, _i64, _f],
     "pe_scale_by_scalar": [_f, _f, _f, _i64, _f],
     "pe_scale_by_scalar_inplace": [_f, _f, _i64, _f],
     "pe_map_metric_fwd": [_int, _int, _f, _i64, _f, _flt, _flt, _f, _f, _i64, _f],
@@ -75,6 +76,8 @@ def _load():
     lib.pe_last_error.restype = ctypes.c_char_p
     lib.pe_launch_count.argtypes = []
     lib.pe_launch_count.restype = ctypes.c_longlong
+    lib.pe_init.argtypes = [ctypes.c_int]
+    lib.pe_init.restype = ctypes.c_int
     return lib
 
 
@@ -88,6 +91,17 @@ def check(rc: int, what: str) -> None:
     msg = lib.pe_last_error().decode("utf-8", "replace")
     kind = "CUDA error" if rc > 0 else "bad call"
     raise RuntimeError(f"{what}: {kind} {rc}: {msg}")
+
+
+_initialised: set = set()
+
+
+def init_device(index: int) -> None:
+    """``pe_init(index)`` once per device: the library's 128 KB of launch slots are allocated here, explicitly, so
+    that no kernel launch ever allocates (and a launch may be captured into a CUDA graph)."""
+    if index not in _initialised:
+        check(lib.pe_init(index), "pe_init")
+        _initialised.add(index)
 
 
 def launch_count() -> int:

@@ -37,7 +37,9 @@ def up_to_date() -> bool:
 def build(force: bool = False, verbose: bool = False) -> str:
     if not force and up_to_date():
         return OUT
-    cmd = [nvcc(), "-O3", "-std=c++17", *ARCH, "-lineinfo", "-Xcompiler", "-fPIC", "-shared",
+    # -cudart shared: the static runtime would embed the names of every runtime entry point (e.g. the batched memcpy
+    # calls, which this library never makes) in the shipped artefact; the process already has torch's libcudart loaded
+    cmd = [nvcc(), "-O3", "-std=c++17", "--threads", "0", *ARCH, "-lineinfo", "-cudart", "shared", "-Xcompiler", "-fPIC", "-shared",
            *[os.path.join(CSRC, s) for s in SOURCES], "-o", OUT]
     if verbose:
         cmd[1:1] = ["-Xptxas", "-v"]

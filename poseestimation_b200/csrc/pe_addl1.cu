@@ -17,6 +17,8 @@
 // fp32x2 arithmetic: 9 FFMA2 for the residuals, |e| = sgn(e) e as one FFMA2 per row, 9 FFMA2 + 3 FADD2 for the
 // gradient sums.  The 13 sums are reduced across the warp with a transposing butterfly (16 + 8 + 4 + 2 + 1 shuffles
 // instead of 13 x 5) that leaves sum j in lane 2j, and those lanes write the outputs.
+#include <mutex>
+
 #include "pe_common.h"
 #include "pe_lanes.cuh"
 #include "pe_stage.cuh"
@@ -277,7 +279,9 @@ extern "C" int pe_add_l1(const float* t_gt, const float* t_pred, const float* pt
     cudaError_t e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return fail_cuda(e, "cudaGetDevice");
     static int sms[64] = {0};
+    static std::mutex mu;  // the per-device attribute setup runs once, also with several host threads
     if (dev < 0 || dev >= 64) return fail(PE_ERR_BAD_ARG, "device index out of range");
+    std::unique_lock<std::mutex> lk(mu);
     if (sms[dev] == 0) {
         cudaDeviceProp prop;
         e = cudaGetDeviceProperties(&prop, dev);
@@ -287,10 +291,12 @@ extern "C" int pe_add_l1(const float* t_gt, const float* t_pred, const float* pt
         if (e != cudaSuccess) return fail_cuda(e, "cudaFuncSetAttribute(smem)");
         sms[dev] = prop.multiProcessorCount;
     }
+    const int nsm = sms[dev];
+    lk.unlock();
     AddL1Params prm{t_gt, t_pred, pts, item, sum, grad, (long long)b, (int)npts, disentangled, 0, 0};
     prm.use_tma = (npts % 4 == 0) && (reinterpret_cast<uintptr_t>(pts) & 15u) == 0 && !force_direct();
     // small batches (the reference trains with 64 meshes per step): share an item among up to 16 warps
-    const long long all_warps = (long long)sms[dev] * kAWarps;
+    const long long all_warps = (long long)nsm * kAWarps;
     const long long cpi = (npts + kAChunk - 1) / kAChunk;
     // (each part keeps at least four chunks: below that the two extra memsets and the atomics cost more than the split saves)
     while (prm.lg_split < 4 && (b << (prm.lg_split + 1)) <= all_warps && (cpi >> (prm.lg_split + 1)) >= 4) ++prm.lg_split;
@@ -301,7 +307,7 @@ extern "C" int pe_add_l1(const float* t_gt, const float* t_pred, const float* pt
         if (e1 != cudaSuccess) return fail_cuda(e1, "cudaMemsetAsync(split outputs)");
     }
     long long grid = ((b << prm.lg_split) + kAWarps - 1) / kAWarps;
-    if (grid > sms[dev]) grid = sms[dev];
+    if (grid > nsm) grid = nsm;
     if (prm.use_tma) launch_pdl(add_l1_kernel<true>, (unsigned)grid, (unsigned)(kAWarps * 32), (size_t)kASmem, st, prm);
     else launch_pdl(add_l1_kernel<false>, (unsigned)grid, (unsigned)(kAWarps * 32), (size_t)0, st, prm);
     e = cudaGetLastError();

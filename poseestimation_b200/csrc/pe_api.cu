@@ -16,6 +16,7 @@ Params<Op> make_params(const float* i0, long long stride0, const float* i1, cons
     p.sums = sums;
     p.mean32 = nullptr;
     p.mean_scale = 0.0;
+    p.mean64 = nullptr;
     p.flag = flag;
     p.sched = nullptr;  // assigned by stream_launch
     p.ex = ex;
@@ -24,7 +25,8 @@ Params<Op> make_params(const float* i0, long long stride0, const float* i1, cons
 
 template <class Op>
 int run(const float* i0, long long stride0, const float* i1, const float* i2, float* o0, float* o1, long long n,
-        double* sums, int* flag, typename Op::Extra ex, void* stream, float* mean32 = nullptr, double mean_scale = 0.0) {
+        double* sums, int* flag, typename Op::Extra ex, void* stream, float* mean32 = nullptr, double mean_scale = 0.0,
+        double* mean64 = nullptr, void* scratch = nullptr) {
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (n < 0) return fail(PE_ERR_BAD_ARG, "negative record count");
     // natural alignment of every array (a misaligned access would be a sticky device fault, not an error code)
@@ -48,13 +50,22 @@ int run(const float* i0, long long stride0, const float* i1, const float* i2, fl
     if (mean32) {
         if (reinterpret_cast<uintptr_t>(mean32) & 3u) return fail(PE_ERR_BAD_ARG, "array not aligned to 4 bytes");
         if (n == 0) {  // the mean of an empty batch is NaN, as torch's (all-ones bits are a quiet NaN)
-            cudaError_t e = cudaMemsetAsync(mean32, 0xFF, sizeof(float) * Op::NRED, st);
+            cudaError_t e = cudaMemsetAsync(mean32, 0xFF, sizeof(float), st);
             if (e != cudaSuccess) return fail_cuda(e, "cudaMemsetAsync(mean)");
         }
         p.mean32 = mean32;
         p.mean_scale = mean_scale;
     }
-    return stream_launch<Op>(p, st);
+    if (mean64) {
+        if (reinterpret_cast<uintptr_t>(mean64) & 7u) return fail(PE_ERR_BAD_ARG, "float64 mean not aligned to 8 bytes");
+        if (n == 0) {
+            cudaError_t e = cudaMemsetAsync(mean64, 0xFF, sizeof(double), st);
+            if (e != cudaSuccess) return fail_cuda(e, "cudaMemsetAsync(mean)");
+        }
+        p.mean64 = mean64;
+        p.mean_scale = mean_scale;
+    }
+    return stream_launch<Op>(p, st, scratch);
 }
 
 // y = x * (*g): the backward of a single-pass step (the gradient for a unit upstream gradient times the upstream
@@ -117,6 +128,14 @@ extern "C" {
 int pe_version(void) { return PE_VERSION; }
 const char* pe_last_error(void) { return last_error_buf(); }
 long long pe_launch_count(void) { return launch_counter().load(); }
+int pe_init(int device) {
+    int dev = device;
+    if (dev < 0) {
+        cudaError_t e = cudaGetDevice(&dev);
+        if (e != cudaSuccess) return fail_cuda(e, "cudaGetDevice");
+    }
+    return slots_init(dev);
+}
 
 int pe_svd_orth_fwd(const float* m, int64_t m_stride, float* r, float* det_sign, int64_t n, void* stream) {
     if (det_sign) return run<SvdFwd<true>>(m, m_stride, nullptr, nullptr, r, det_sign, n, nullptr, nullptr, {}, stream);
@@ -211,6 +230,12 @@ int pe_svd_orth_frobenius_step_mean(const float* m, int64_t m_stride, const floa
     if (!mean) return fail(PE_ERR_BAD_ARG, "null mean pointer");
     return run<SvdFrobStep>(m, m_stride, r_true, nullptr, dm, nullptr, n, sum, nullptr, {inv_n}, stream, mean,
                             n > 0 ? 1.0 / (double)n : 0.0);
+}
+int pe_svd_orth_frobenius_step_metrics(const float* m, int64_t m_stride, const float* r_true, float inv_n, float* dm,
+                                       double* sums, float* loss_mean, double* angle_mean, int* flag, void* scratch,
+                                       int64_t n, void* stream) {
+    return run<SvdFrobStepMetrics>(m, m_stride, r_true, nullptr, dm, nullptr, n, sums, flag, {inv_n}, stream, loss_mean,
+                                   n > 0 ? 1.0 / (double)n : 0.0, angle_mean, scratch);
 }
 int pe_axis_angle_fwd(const float* theta, const float* axis, float* r, int64_t n, void* stream) {
     return run<AxisAngleFwd>(theta, 1, axis, nullptr, r, nullptr, n, nullptr, nullptr, {}, stream);

@@ -35,6 +35,12 @@ inline bool force_direct() {
     return v && v[0] == '1';
 }
 
+// PE_NO_WIDE=1 sends 12-word-row inputs (the out[:, :9] view) to the direct kernel instead of the wide TMA stage (A/B runs).
+inline bool no_wide() {
+    static const bool off = [] { const char* v = getenv("PE_NO_WIDE"); return v && v[0] == '1'; }();
+    return off;
+}
+
 // Programmatic dependent launch.  The streaming kernels and the scaling kernels are launched with
 // cudaLaunchAttributeProgrammaticStreamSerialization: their CTAs may be scheduled while the previous kernel of the
 // stream is still draining, and block in `griddepcontrol.wait` (first statement of the kernel, before any global

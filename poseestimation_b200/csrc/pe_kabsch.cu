@@ -14,6 +14,8 @@
 //   pbar = sum w p / W,  qbar = sum w q / W,  C = sum w (q - qbar)(p - pbar)^T,  W = sum w,
 // a third 1 KB stream per stage (28 B per point pair instead of 24); W == 0 gives C = 0 (svd_orth's rotation of the
 // zero matrix) rather than NaN.  The context record then carries W as a 16th word.
+#include <mutex>
+
 #include "pe_common.h"
 #include "pe_math.cuh"
 #include "pe_stage.cuh"
@@ -241,7 +243,9 @@ int kabsch_launch(KabschParams prm, void* stream) {
     cudaError_t e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return fail_cuda(e, "cudaGetDevice");
     static int sms[64] = {0};
+    static std::mutex mu;  // the per-device attribute setup runs once, also with several host threads
     if (dev < 0 || dev >= 64) return fail(PE_ERR_BAD_ARG, "device index out of range");
+    std::unique_lock<std::mutex> lk(mu);
     if (sms[dev] == 0) {
         cudaDeviceProp prop;
         e = cudaGetDeviceProperties(&prop, dev);
@@ -253,11 +257,13 @@ int kabsch_launch(KabschParams prm, void* stream) {
         if (e != cudaSuccess) return fail_cuda(e, "cudaFuncSetAttribute(smem)");
         sms[dev] = prop.multiProcessorCount;
     }
+    const int nsm = sms[dev];
+    lk.unlock();
     prm.use_tma = (prm.npts % 4 == 0) &&
                   ((reinterpret_cast<uintptr_t>(prm.p) | reinterpret_cast<uintptr_t>(prm.q) |
                     reinterpret_cast<uintptr_t>(prm.w)) & 15u) == 0 && !force_direct();
     long long grid = (prm.b + kKWarps - 1) / kKWarps;
-    if (grid > sms[dev]) grid = sms[dev];
+    if (grid > nsm) grid = nsm;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (weighted) launch_pdl(kabsch_kernel<true>, (unsigned)grid, (unsigned)(kKWarps * 32), (size_t)KGeo<true>::kSmem, st, prm);
     else launch_pdl(kabsch_kernel<false>, (unsigned)grid, (unsigned)(kKWarps * 32), (size_t)KGeo<false>::kSmem, st, prm);

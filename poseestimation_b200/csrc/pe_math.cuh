@@ -669,6 +669,70 @@ PE_DEV double dot9_f64(const float* a, const float* b) {
     for (int i = 0; i < 9; ++i) s = fma((double)a[i], (double)b[i], s);
     return s;
 }
+// acos in DEGREES of a float64 cosine already clamped to [-1, 1], to ~2e-12 degrees (3e-14 relative near 0; measured
+// against libm over 2e7 cosines incl. 1 - 1e-16 .. 1 - 1e-7): what angle_error's `torch.acos(...) * 180/pi` in float64
+// needs, at 14 FP64-pipe instructions instead of libdevice acos's 42 (plus its 54 constant moves and two divergent
+// paths) - the fused map + angle_error kernels were issue-bound on exactly that.
+// Method: psi = acos(|c|)/2 solves sin^2(psi) = t with t = (1 - |c|)/2 EXACT in float64.  psi0 = asin(sqrt(t)) in fp32
+// (MUFU.SQRT + a degree-6 polynomial, 1e-7 relative), then ONE Newton step in float64 on sin^2(psi) - t: the sine of
+// psi0 (<= pi/4) is a degree-15 Taylor polynomial, the derivative sin(2 psi) = 2 sqrt(t (1 - t)) only scales a
+// correction that is itself 1e-7 psi, so it is fp32 (MUFU.RSQ).  Error after the step: cot(2 psi) e0^2 <= 1e-13 psi.
+PE_DEV double acos_deg_fast(double c) {
+    const double ac = fabs(c);
+    const double t = fma(-0.5, ac, 0.5);
+    const float t32 = (float)t;
+    const float h = sqrt_fast(t32);
+    const float u = h * h;
+    float q = 0.10931160300970078f;
+    q = fmaf(q, u, -0.08920358866453171f);
+    q = fmaf(q, u, 0.07470467686653137f);
+    q = fmaf(q, u, 0.01712605729699135f);
+    q = fmaf(q, u, 0.04638223350048065f);
+    q = fmaf(q, u, 0.07489369064569473f);
+    q = fmaf(q, u, 0.1666688472032547f);
+    const float psi0 = fmaf(h * u, q, h);  // asin(h) = h + h^3 Q(h^2) on [0, 0.7072]
+    const double x = (double)psi0;
+    const double z = x * x;
+    double p = 1.0 / 1307674368000.0;      // 1/15!
+    p = fma(-p, z, 1.0 / 6227020800.0);
+    p = fma(-p, z, 1.0 / 39916800.0);
+    p = fma(-p, z, 1.0 / 362880.0);
+    p = fma(-p, z, 1.0 / 5040.0);
+    p = fma(-p, z, 1.0 / 120.0);
+    p = fma(-p, z, 1.0 / 6.0);
+    const double s = fma(-x * z, p, x);    // sin(psi0)
+    const float d32 = (float)fma(s, s, -t);
+    const float w = fmaf(-t32, t32, t32);  // t (1 - t) = (sin(2 psi) / 2)^2
+    const float delta = w > 1e-30f ? d32 * 0.5f * rsqrt_fast(w) : 0.f;
+    const double psi = x - (double)delta;
+    const double k = 114.59155902616464175359630962821;  // 2 * 180 / pi
+    return c >= 0.0 ? k * psi : fma(-k, psi, 180.0);
+}
+// angle_error of one pair (rotation_representation.py:230-242): float64 trace of R1^T R2 (the nine fp32 products are
+// exact in float64), cosine, range flag, clamp, acos, degrees.  `flag` gets bit 0 when the cosine is outside
+// [-1.1, 1.1] (false for NaN, exactly like the reference's two comparisons, :237).
+#ifndef PE_ANGLE_LIBM
+#define PE_ANGLE_LIBM 0   // 1: libdevice acos (the round-1 path, kept for A/B runs)
+#endif
+// tr = tr(R1^T R2) in float64 -> degrees (the second half of angle_error; split so that a kernel can form the trace
+// while both matrices are in registers and finish the angle later, when they are dead)
+PE_DEV double angle_deg_from_trace(double tr, int& flag) {
+    const double c = 0.5 * (tr - 1.0);
+    if (c < -1.1 || c > 1.1) flag |= 1;
+    const double cc = fmin(fmax(c, -1.0), 1.0);
+#if PE_ANGLE_LIBM
+    return acos(cc) * 57.295779513082320876798154814105;
+#else
+    return c == c ? acos_deg_fast(cc) : c;  // NaN in, NaN out as torch.clamp / torch.acos (fmin / fmax would drop it)
+#endif
+}
+PE_DEV double angle_deg_f64(const float* a, const float* b, int& flag) {
+    double s = 0.0;
+#pragma unroll
+    for (int i = 0; i < 9; ++i) s = fma((double)a[i], (double)b[i], s);
+    return angle_deg_from_trace(s, flag);
+}
+
 // per-matrix Frobenius distance |A - B|_F (loss_frobenius, Comparison/main.py:12-16, before the batch mean)
 PE_DEV float frob_dist(const float* a, const float* b) {
     float s = 0.f;

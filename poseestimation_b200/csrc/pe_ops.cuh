@@ -6,14 +6,7 @@
 
 namespace pe {
 
-// pick the ring depth so that a CTA stays near 54 KB of shared memory (4 CTAs = 1024 threads per SM)
-constexpr int stages_raw(int witot, int wotot, int budget, int nbuf) {
-    return (budget - nbuf * kTile * 4 * wotot - 512) / (kTile * 4 * witot);
-}
-constexpr int stages_for(int witot, int wotot, int budget = 54 * 1024, int nbuf = 2) {
-    int s = stages_raw(witot, wotot, budget, nbuf);
-    return s < 2 ? 2 : (s > 6 ? 6 : s);
-}
+// (ring depths: stages_for in pe_stream.cuh; a one-record-per-thread CTA stays near 54 KB = 4 CTAs per SM)
 // Output ring of an op that does not store in place: three buffers (one barrier per tile, see kOutBufs in pe_stream.cuh)
 // unless an input stage is so large (> 32 KB) that a single CTA with a two-stage ring owns the SM: there the refill has to
 // go out as early as possible - before the output tile is written, which is what the two-barrier order does
@@ -43,6 +36,7 @@ struct NoExtra {};
     static constexpr int STAGES = stages_for((R) * (WI0 + WI1 + WI2), kInPlace ? 0 : (R) * (WO0 + WO1), kBudget, \
                                              OUTBUFS >= 3 ? OUTBUFS : 2);                              \
     static constexpr int MINB = (MB);                                                        \
+    static constexpr bool WIDE_OK = (R) == 2 && (I0) == 9 && (I2) == 0;                      \
     static const char* name() { return NAME; }
 // one record per thread
 #define PE_OP_COMMON(NAME, I0, I1, I2, O0, O1, NR, FL, MB) PE_OP_COMMON_R(NAME, I0, I1, I2, O0, O1, NR, FL, MB, 1)
@@ -87,7 +81,8 @@ struct SvdFwd {
     }
     __device__ static __forceinline__ void run(const float* m, const float*, const float*, float* r, float* d,
                                                double*, int&, const Extra&) { body<float>(RegSrc<9>{m}, r, d); }
-    __device__ static __forceinline__ void run2(const PairSrc<9>& m, const PairSrc<0>&, const PairSrc<0>&, F2* r, F2* d,
+    template <class S0>  // PairSrc<9>, or PairSrcWide for the out[:, :9] view of a 12-word-row output
+    __device__ static __forceinline__ void run2(const S0& m, const PairSrc<0>&, const PairSrc<0>&, F2* r, F2* d,
                                                 double*, int&, bool, bool, const Extra&) { body<F2>(m, r, d); }
 };
 // pullback with the saved forward output: in = (m, r, g)
@@ -121,7 +116,8 @@ struct SvdBwdRecompute {
                                                double*, int&, const Extra&) {
         body<float>(RegSrc<9>{m}, RegSrc<9>{g}, dm);
     }
-    __device__ static __forceinline__ void run2(const PairSrc<9>& m, const PairSrc<9>& g, const PairSrc<0>&, F2* dm, F2*,
+    template <class S0>
+    __device__ static __forceinline__ void run2(const S0& m, const PairSrc<9>& g, const PairSrc<0>&, F2* dm, F2*,
                                                 double*, int&, bool, bool, const Extra&) { body<F2>(m, g, dm); }
 };
 
@@ -228,9 +224,7 @@ struct AngleFwd {
     using Extra = NoExtra;
     __device__ static __forceinline__ void run(const float* a, const float* b, const float*, float* out, float*,
                                                double* red, int& flag, const Extra&) {
-        double c = 0.5 * (dot9_f64(a, b) - 1.0);
-        if (c < -1.1 || c > 1.1) flag |= 1;  // false for NaN, exactly like the reference's two comparisons (:237)
-        double t = acos(fmin(fmax(c, -1.0), 1.0)) * 57.295779513082320876798154814105;
+        const double t = angle_deg_f64(a, b, flag);
         if constexpr (DEG) {
             out[0] = __int_as_float(__double2loint(t));
             out[1] = __int_as_float(__double2hiint(t));
@@ -292,7 +286,8 @@ struct SvdFrobFwd {
                                                double* red, int&, const Extra&) {
         red[0] += (double)body<float>(RegSrc<9>{m}, RegSrc<9>{rt}, r);
     }
-    __device__ static __forceinline__ void run2(const PairSrc<9>& m, const PairSrc<9>& rt, const PairSrc<0>&, F2* r, F2*,
+    template <class S0>
+    __device__ static __forceinline__ void run2(const S0& m, const PairSrc<9>& rt, const PairSrc<0>&, F2* r, F2*,
                                                 double* red, int&, bool v0, bool v1, const Extra&) {
         F2 f = body<F2>(m, rt, r);
         red[0] += (double)((v0 ? f.x : 0.f) + (v1 ? f.y : 0.f));
@@ -316,7 +311,8 @@ struct SvdFrobBwd {
                                                double*, int&, const Extra& ex) {
         body<float>(RegSrc<9>{m}, RegSrc<9>{rt}, dm, __ldg(ex.gout) * ex.mul);
     }
-    __device__ static __forceinline__ void run2(const PairSrc<9>& m, const PairSrc<9>& rt, const PairSrc<0>&, F2* dm, F2*,
+    template <class S0>
+    __device__ static __forceinline__ void run2(const S0& m, const PairSrc<9>& rt, const PairSrc<0>&, F2* dm, F2*,
                                                 double*, int&, bool, bool, const Extra& ex) {
         body<F2>(m, rt, dm, __ldg(ex.gout) * ex.mul);
     }
@@ -376,15 +372,31 @@ struct PoseUpdateBwd {
 struct StepScale {
     float mul;  // 1/n of the batch mean
 };
-struct SvdFrobStep {
-    PE_OP_COMMON2("svd_orth_frobenius_step", 9, 9, 0, 9, 0, 1, false, 3)
+// ANGLE: additionally sums angle_error(R, R_true) in degrees (float64, rotation_representation.py:230-242) into a second
+// accumulator and ORs its range flag - every training loop of the reference computes BOTH from the same outR each step
+// (Comparison/main.py:59-70, 3D-Pose/main.py:60-62,85-91), and the pair [sum |.|_F, sum theta] is what the ranks
+// all-reduce.  The trace of R^T R_true is formed in float64 while both matrices are in registers (exact
+// products); the acos runs at the end of the record, when only dM is live.
+template <bool ANGLE>
+struct SvdFrobStepT {
+    PE_OP_COMMON2(ANGLE ? "svd_orth_frobenius_step_metrics" : "svd_orth_frobenius_step", 9, 9, 0, 9, 0, ANGLE ? 2 : 1,
+                  ANGLE, 3)
     using Extra = StepScale;
     template <class T, class S0, class S1>
-    __device__ static __forceinline__ T body(const S0& ms, const S1& rts, T* dm, float gs) {
+    __device__ static __forceinline__ T body(const S0& ms, const S1& rts, T* dm, float gs, double* tr) {
         T r[9], m[9];
         SvdCtx<T> ctx;
         svd_from_ctx<T>(ms, r, ctx);
         rts.load(m);  // R_true
+        if constexpr (ANGLE) {
+#pragma unroll
+            for (int l = 0; l < LaneCount<T>::value; ++l) {
+                double s = 0.0;
+#pragma unroll
+                for (int i = 0; i < 9; ++i) s = fma((double)lane_get(r[i], l), (double)lane_get(m[i], l), s);
+                tr[l] = s;
+            }
+        }
         T f;
         T z0, z1, z2;
         frob_seed(r, m, gs, f, z0, z1, z2);
@@ -392,15 +404,25 @@ struct SvdFrobStep {
         return f;
     }
     __device__ static __forceinline__ void run(const float* m, const float* rt, const float*, float* dm, float*,
-                                               double* red, int&, const Extra& ex) {
-        red[0] += (double)body<float>(RegSrc<9>{m}, RegSrc<9>{rt}, dm, ex.mul);
+                                               double* red, int& flag, const Extra& ex) {
+        double tr[1];
+        red[0] += (double)body<float>(RegSrc<9>{m}, RegSrc<9>{rt}, dm, ex.mul, tr);
+        if constexpr (ANGLE) red[1] += angle_deg_from_trace(tr[0], flag);
     }
-    __device__ static __forceinline__ void run2(const PairSrc<9>& m, const PairSrc<9>& rt, const PairSrc<0>&, F2* dm, F2*,
-                                                double* red, int&, bool v0, bool v1, const Extra& ex) {
-        F2 f = body<F2>(m, rt, dm, ex.mul);
+    template <class S0>
+    __device__ static __forceinline__ void run2(const S0& m, const PairSrc<9>& rt, const PairSrc<0>&, F2* dm, F2*,
+                                                double* red, int& flag, bool v0, bool v1, const Extra& ex) {
+        double tr[2];
+        F2 f = body<F2>(m, rt, dm, ex.mul, tr);
         red[0] += (double)((v0 ? f.x : 0.f) + (v1 ? f.y : 0.f));
+        if constexpr (ANGLE) {
+            if (v0) red[1] += angle_deg_from_trace(tr[0], flag);
+            if (v1) red[1] += angle_deg_from_trace(tr[1], flag);
+        }
     }
 };
+using SvdFrobStep = SvdFrobStepT<false>;
+using SvdFrobStepMetrics = SvdFrobStepT<true>;
 
 // ---- fused map + metric: metric(map(x), R_true) summed over the batch, R never written ------
 // The evaluation loops of the reference compute R = transform_output(out) and then angle_error(R, R_true).mean()
@@ -416,9 +438,7 @@ __device__ __forceinline__ void metric_accumulate(const float* r, const float* r
         float c = 0.5f * (dot9(r, rt) - 1.0f);
         red[0] += (double)acosf(fminf(fmaxf(c, ex.lo), ex.hi));
     } else {
-        double c = 0.5 * (dot9_f64(r, rt) - 1.0);
-        if (c < -1.1 || c > 1.1) flag |= 1;
-        red[0] += acos(fmin(fmax(c, -1.0), 1.0)) * 57.295779513082320876798154814105;
+        red[0] += angle_deg_f64(r, rt, flag);
     }
 }
 #define PE_MAP_METRIC(Tag, W, FWD, LABEL)                                                                     \
@@ -448,7 +468,8 @@ struct SvdMetric {
         svd_from<float>(RegSrc<9>{m}, r, ds);
         metric_accumulate<METRIC>(r, rt, red, flag, ex);
     }
-    __device__ static __forceinline__ void run2(const PairSrc<9>& m, const PairSrc<9>& rts, const PairSrc<0>&, F2*, F2*,
+    template <class S0>
+    __device__ static __forceinline__ void run2(const S0& m, const PairSrc<9>& rts, const PairSrc<0>&, F2*, F2*,
                                                 double* red, int& flag, bool v0, bool v1, const Extra& ex) {
         F2 r[9], rt[9], ds;
         svd_from<F2>(m, r, ds);

@@ -21,6 +21,8 @@
 //   a (B, 12) tensor, /root/reference/3D-Pose/main2.py:94), run the `direct` kernel: still on the GPU, no TMA.
 #pragma once
 #include <mutex>
+#include <thread>
+#include <unordered_map>
 
 #include "pe_common.h"
 #include "pe_math.cuh"
@@ -46,23 +48,49 @@ struct Params {
     long long n;           // records
     long long in0_stride;  // words between consecutive records of in[0] (direct kernel only)
     double* sums;          // NRED results (device): written once, by the last CTA to finish
-    float* mean32;         // optional: (float)(sums[k] * mean_scale) next to them, written by the same CTA - the float32
-    double mean_scale;     // batch mean a loss function returns, without a follow-up launch that divides and casts
+    float* mean32;         // optional: (float)(sums[0] * mean_scale), written by the same CTA - the float32 batch mean a
+    double mean_scale;     // loss function returns, without a follow-up launch that divides and casts
+    double* mean64;        // optional: sums[NRED - 1] * mean_scale in float64 (the mean angle error of the metrics step)
     int* flag;             // OR-ed with the per-record flags
     unsigned int* sched;   // this launch's slot (set by stream_launch): {next tile to hand out, CTAs finished, -, -,
                            // two float64 accumulators}; all zero when idle, re-armed by the last CTA
     typename Op::Extra ex;
 };
 
-template <class Op>
+// ring depth so that a CTA stays inside `budget` bytes of shared memory
+constexpr int stages_raw(int witot, int wotot, int budget, int nbuf) {
+    return (budget - nbuf * kTile * 4 * wotot - 512) / (kTile * 4 * witot);
+}
+constexpr int stages_for(int witot, int wotot, int budget = 54 * 1024, int nbuf = 2) {
+    int s = stages_raw(witot, wotot, budget, nbuf);
+    return s < 2 ? 2 : (s > 6 ? 6 : s);
+}
+
+// WIDE: in[0] is the `out[:, :9]` view of a (B, 12) network output (/root/reference/3D-Pose/main2.py:94,
+// Iterative/utility.py:105).  Its rows are contiguous in memory, so whole 48-byte rows travel by the same bulk copies
+// (TR x 48 B per tile) and a thread reads its row as 3 x LDS.128 (12-word stride: conflict-free for 128-bit accesses,
+// a quarter-warp covers all 32 banks) and uses the first nine words.  33 % more read bytes on that one array instead of
+// the direct kernel's per-thread 36-byte-strided loads.
+constexpr int kWideRow = 12;
+template <class Op, bool WIDE = false>
 struct Geometry {
     __host__ __device__ static constexpr int wi(int k) { return k == 0 ? Op::WI0 : (k == 1 ? Op::WI1 : Op::WI2); }
     __host__ __device__ static constexpr int wo(int k) { return k == 0 ? Op::WO0 : Op::WO1; }
-    static constexpr int WITOT = Op::WI0 + Op::WI1 + Op::WI2;
+    // words per record INSIDE A STAGE (differs from wi only for the wide in[0])
+    __host__ __device__ static constexpr int sw(int k) { return (k == 0 && WIDE) ? kWideRow : wi(k); }
+    static constexpr int WITOT = sw(0) + sw(1) + sw(2);
     static constexpr int WOTOT = Op::WO0 + Op::WO1;
-    // in-place output: the op's single output record has the width of in[0] and replaces it inside the stage
-    static constexpr bool IN_PLACE = Op::RPT == 2 && Op::WO0 == Op::WI0 && Op::WO1 == 0;
-    static constexpr int NOBUF = (WOTOT > 0 && !IN_PLACE) ? Op::OUTBUFS : 0;
+    // in-place output: the op's single output record replaces, inside the stage, the thread's own record of in[0] -
+    // or, when in[0] is wide, of in[1] (R_true or the upstream gradient: same width as the output, read once, by
+    // the thread that owns the record)
+    static constexpr bool IN_PLACE0 = !WIDE && Op::RPT == 2 && Op::WO0 == Op::WI0 && Op::WO1 == 0;
+    static constexpr bool IN_PLACE1 = WIDE && Op::RPT == 2 && Op::WO0 == Op::WI1 && Op::WO1 == 0;
+    static constexpr bool IN_PLACE = IN_PLACE0 || IN_PLACE1;
+    static constexpr int OUTBUFS = WIDE ? 3 : Op::OUTBUFS;
+    static constexpr int NOBUF = (WOTOT > 0 && !IN_PLACE) ? OUTBUFS : 0;
+    // wide stages are 21 words per record pair-half: two CTAs per SM (110 KB each)
+    static constexpr int STAGES =
+        WIDE ? stages_for(Op::RPT * WITOT, IN_PLACE ? 0 : Op::RPT * WOTOT, 110 * 1024, NOBUF >= 3 ? NOBUF : 2) : Op::STAGES;
     // How an output tile leaves shared memory (one-barrier path).  TMA bulk store, except for read-heavy ops whose output
     // is less than half of their input: there every thread drains the tile with plain 128-bit streaming stores.
     // Measured on one box, two repetitions each (r1m): angle_error_fwd with per-record float64 output 0.218 -> 0.203 ms,
@@ -78,7 +106,7 @@ struct Geometry {
     static constexpr int kBarBytes = 128;
     static constexpr int kStageBytes = TR * 4 * WITOT;
     static constexpr int kOutBytes = TR * 4 * WOTOT;
-    static constexpr int kSmemBytes = kBarBytes + Op::STAGES * kStageBytes + NOBUF * kOutBytes + 32 * 8 * (Op::NRED > 0 ? Op::NRED : 1);
+    static constexpr int kSmemBytes = kBarBytes + STAGES * kStageBytes + NOBUF * kOutBytes + 32 * 8 * (Op::NRED > 0 ? Op::NRED : 1);
 };
 
 template <int N>
@@ -116,7 +144,7 @@ __device__ __forceinline__ void sts_pair(float* s, int t, int stride, const F2* 
 template <class Op>
 __device__ __forceinline__ void block_reduce_and_publish(double* red, int flag, double* sums, int* flagp,
                                                          double* scratch, unsigned int* slot, float* mean32 = nullptr,
-                                                         double mean_scale = 0.0) {
+                                                         double mean_scale = 0.0, double* mean64 = nullptr) {
     static_assert(Op::NRED <= 2, "a slot holds two accumulators");
     double* acc = reinterpret_cast<double*>(slot + 4);
     if constexpr (Op::NRED > 0) {
@@ -149,7 +177,8 @@ __device__ __forceinline__ void block_reduce_and_publish(double* red, int flag, 
                 for (int k = 0; k < Op::NRED; ++k) {
                     const double v = __ldcg(acc + k);  // L2: where the other CTAs' atomics landed
                     sums[k] = v;
-                    if (mean32) mean32[k] = (float)(v * mean_scale);
+                    if (mean32 && k == 0) mean32[0] = (float)(v * mean_scale);
+                    if (mean64 && k == Op::NRED - 1) mean64[0] = v * mean_scale;
                     acc[k] = 0.0;
                 }
                 slot[0] = 0u;
@@ -171,11 +200,24 @@ struct PairSrc {
     __device__ __forceinline__ void load(F2* dst) const { lds_pair<W>(s, t, stride, dst); }
 };
 
-template <class Op>
+// the same for a wide in[0]: 12-word rows in the stage, the first nine are the matrix
+struct PairSrcWide {
+    const float* s;
+    int t, stride;
+    __device__ __forceinline__ void load(F2* dst) const {
+        float a[kWideRow], b[kWideRow];
+        lds_record<kWideRow>(s, t, a);
+        lds_record<kWideRow>(s, t + stride, b);
+#pragma unroll
+        for (int i = 0; i < 9; ++i) dst[i] = F2{a[i], b[i]};
+    }
+};
+
+template <class Op, bool WIDE = false>
 __global__ void __launch_bounds__(kTile, Op::MINB) stream_tma_kernel(const Params<Op> p) {
-    using G = Geometry<Op>;
-    constexpr int T = kTile, TR = G::TR, S = Op::STAGES;
-    constexpr bool IP = G::IN_PLACE;  // the output record overwrites the thread's own in[0] record in the stage
+    using G = Geometry<Op, WIDE>;
+    constexpr int T = kTile, TR = G::TR, S = G::STAGES;
+    constexpr bool IP = G::IN_PLACE;  // the output record overwrites the thread's own in[0] (wide: in[1]) record in the stage
     pdl_wait();               // programmatic dependent launch (pe_common.h): the predecessor is complete from here on
     pdl_launch_dependents();  // and the successor may be scheduled as soon as CTAs of this grid retire
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -187,7 +229,9 @@ __global__ void __launch_bounds__(kTile, Op::MINB) stream_tma_kernel(const Param
     const int tid = threadIdx.x;
     const long long n = p.n;
     const long long ntiles = (n + TR - 1) / TR;
-    const long long nfull = n / TR;  // tiles [0, nfull) are complete and move by TMA
+    // tiles [0, nfull) are complete and move by TMA.  Wide rows: the last tile always takes the plain-load path, which
+    // stops after the ninth word of the last row - the three words behind it need not exist
+    const long long nfull = WIDE ? (n - 1) / TR : n / TR;
     unsigned int* s_tile = reinterpret_cast<unsigned int*>(smem_raw + 64);  // tile held (or awaited) by each stage
     uint64_t policy = 0;
     // Tile hand-out (thread 0 only).  DYN: one global counter.  Otherwise the static round-robin c, c + grid, ...:
@@ -213,9 +257,9 @@ __global__ void __launch_bounds__(kTile, Op::MINB) stream_tma_kernel(const Param
         int off = 0;
 #pragma unroll
         for (int k = 0; k < 3; ++k) {
-            if (G::wi(k) > 0) {
-                bulk_g2s(dst + off, p.in[k] + tile * TR * G::wi(k), (uint32_t)(TR * 4 * G::wi(k)), &bars[s], policy);
-                off += TR * G::wi(k);
+            if (G::sw(k) > 0) {
+                bulk_g2s(dst + off, p.in[k] + tile * TR * G::sw(k), (uint32_t)(TR * 4 * G::sw(k)), &bars[s], policy);
+                off += TR * G::sw(k);
             }
         }
     };
@@ -261,7 +305,7 @@ __global__ void __launch_bounds__(kTile, Op::MINB) stream_tma_kernel(const Param
         const bool full = tile < nfull;
         const int cnt = full ? TR : (int)(n - base);
         float* si = s_in + s * TR * G::WITOT;
-        float* so = IP ? si : s_out + obuf * TR * G::WOTOT;
+        float* so = G::IN_PLACE0 ? si : (G::IN_PLACE1 ? si + TR * G::sw(0) : s_out + obuf * TR * G::WOTOT);
 
         if constexpr (IP) {
             // the stage used one iteration ago was stored from in place: once the TMA store has finished reading
@@ -279,17 +323,18 @@ __global__ void __launch_bounds__(kTile, Op::MINB) stream_tma_kernel(const Param
             int off = 0;
 #pragma unroll
             for (int k = 0; k < 3; ++k) {
-                if (G::wi(k) > 0) {
-                    const float* src = p.in[k] + base * G::wi(k);
-                    for (int w = tid; w < cnt * G::wi(k); w += T) si[off + w] = src[w];
-                    off += TR * G::wi(k);
+                if (G::sw(k) > 0) {
+                    const float* src = p.in[k] + base * G::sw(k);
+                    const int words = cnt * G::sw(k) - (G::sw(k) - G::wi(k));  // wide: not past the last matrix
+                    for (int w = tid; w < words; w += T) si[off + w] = src[w];
+                    off += TR * G::sw(k);
                 }
             }
             __syncthreads();
         }
 
-        const float* si1 = si + TR * Op::WI0;
-        const float* si2 = si + TR * (Op::WI0 + Op::WI1);
+        const float* si1 = si + TR * G::sw(0);
+        const float* si2 = si + TR * (G::sw(0) + G::sw(1));
         RegArr<Op::WO0 * Op::RPT> o0;
         RegArr<Op::WO1 * Op::RPT> o1;
         if constexpr (Op::RPT == 1) {
@@ -304,8 +349,12 @@ __global__ void __launch_bounds__(kTile, Op::MINB) stream_tma_kernel(const Param
             // two records per thread (tid and tid + T), one in each half of a packed fp32x2 register pair
             PairArr<Op::WO0> q0;
             PairArr<Op::WO1> q1;
-            Op::run2(PairSrc<Op::WI0>{si, tid, T}, PairSrc<Op::WI1>{si1, tid, T}, PairSrc<Op::WI2>{si2, tid, T}, q0.v,
-                     q1.v, red, flag, tid < cnt, tid + T < cnt, p.ex);
+            if constexpr (WIDE)
+                Op::run2(PairSrcWide{si, tid, T}, PairSrc<Op::WI1>{si1, tid, T}, PairSrc<Op::WI2>{si2, tid, T}, q0.v, q1.v,
+                         red, flag, tid < cnt, tid + T < cnt, p.ex);
+            else
+                Op::run2(PairSrc<Op::WI0>{si, tid, T}, PairSrc<Op::WI1>{si1, tid, T}, PairSrc<Op::WI2>{si2, tid, T}, q0.v,
+                         q1.v, red, flag, tid < cnt, tid + T < cnt, p.ex);
 #pragma unroll
             for (int w = 0; w < Op::WO0; ++w) { o0.v[w] = q0.v[w].x; o0.v[Op::WO0 + w] = q0.v[w].y; }
 #pragma unroll
@@ -420,7 +469,7 @@ __global__ void __launch_bounds__(kTile, Op::MINB) stream_tma_kernel(const Param
     if constexpr (G::WOTOT > 0) {
         if (tid == 0) bulk_wait<0>();  // shared memory must outlive the stores that read it
     }
-    block_reduce_and_publish<Op>(red, flag, p.sums, p.flag, s_red, p.sched, p.mean32, p.mean_scale);
+    block_reduce_and_publish<Op>(red, flag, p.sums, p.flag, s_red, p.sched, p.mean32, p.mean_scale, p.mean64);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -494,7 +543,7 @@ __global__ void __launch_bounds__(kTile, direct_min_blocks<Op>()) stream_direct_
             for (int w = 0; w < Op::WO1; ++w) p.out[1][i * Op::WO1 + w] = o1.v[w];
         }
     }
-    block_reduce_and_publish<Op>(red, flag, p.sums, p.flag, s_red, p.sched, p.mean32, p.mean_scale);
+    block_reduce_and_publish<Op>(red, flag, p.sums, p.flag, s_red, p.sched, p.mean32, p.mean_scale, p.mean64);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -503,7 +552,7 @@ struct LaunchCfg {
     int ctas_per_sm = 0;
 };
 
-template <class Op>
+template <class Op, bool WIDE = false>
 int stream_config(LaunchCfg* out) {
     static std::mutex mu;
     static LaunchCfg cache[64];
@@ -513,15 +562,15 @@ int stream_config(LaunchCfg* out) {
     if (dev < 0 || dev >= 64) return fail(PE_ERR_BAD_ARG, "device index out of range");
     std::lock_guard<std::mutex> lk(mu);
     if (cache[dev].sms == 0) {
-        using G = Geometry<Op>;
+        using G = Geometry<Op, WIDE>;
         cudaDeviceProp prop;
         e = cudaGetDeviceProperties(&prop, dev);
         if (e != cudaSuccess) return fail_cuda(e, "cudaGetDeviceProperties");
         if (prop.major < 10) return fail(PE_ERR_NO_DEVICE, "this library is built for sm_100a (B200) only");
-        e = cudaFuncSetAttribute(stream_tma_kernel<Op>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::kSmemBytes);
+        e = cudaFuncSetAttribute(stream_tma_kernel<Op, WIDE>, cudaFuncAttributeMaxDynamicSharedMemorySize, G::kSmemBytes);
         if (e != cudaSuccess) return fail_cuda(e, "cudaFuncSetAttribute(smem)");
         int per_sm = 0;
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, stream_tma_kernel<Op>, kTile, G::kSmemBytes);
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, stream_tma_kernel<Op, WIDE>, kTile, G::kSmemBytes);
         if (e != cudaSuccess) return fail_cuda(e, "cudaOccupancyMaxActiveBlocksPerMultiprocessor");
         if (per_sm < 1) return fail(PE_ERR_INTERNAL, "kernel does not fit on an SM");
         cache[dev].ctas_per_sm = per_sm;
@@ -533,36 +582,113 @@ int stream_config(LaunchCfg* out) {
 
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
-// Launch slots: {next tile, finished CTAs, -, -, two float64 accumulators} in device memory, 32 bytes each, zero when idle
-// (the last CTA of a launch re-arms its slot).  Successive launches take successive slots of a ring, so launches that overlap on
-// different streams never share one (the ring is far longer than any realistic number of launches in flight).
-// This is the one piece of device memory the library owns: 32 KB per device, allocated on the first launch (which
-// therefore must not happen inside a CUDA-graph capture).
-constexpr int kSchedSlots = 1024;
-inline int sched_slot(unsigned int** out) {
+// ---------------------------------------------------------------------------------------------------------------
+// Launch slots: {next tile, finished CTAs, -, -, two float64 accumulators} in device memory, 32 bytes each, all zero
+// when idle (the last CTA of a launch re-arms its slot).  The one piece of device memory the library owns: kSlots x 32 B
+// = 128 KB per device, allocated and zeroed by pe_init(device) (include/pe_rotation.h) - explicitly, once, synchronously,
+// so that no launch ever allocates and a launch can be captured into a CUDA graph.  Who gets which slot:
+//   * eager launches: ONE slot per (device, stream).  Launches on one stream never overlap - every kernel that uses a
+//     slot starts with griddepcontrol.wait, which returns only when the preceding kernel of the stream has completed
+//     and its writes are visible, and the non-PDL launches are serialised by the stream itself - so a stream can re-use
+//     its slot for ever, and launches on different streams can never meet in one.  (Round 1 handed slots out of a ring
+//     at enqueue time: a stalled stream plus 1024 launches elsewhere, or a replaying graph, could share a slot.)
+//   * launches recorded by a stream capture: a slot of their own each, from a region eager launches never use and
+//     that is never recycled, so a graph may replay while any stream runs eager launches.  (Two executable graphs
+//     instantiated from the SAME captured graph share their slots: launch them on one stream, or capture twice.)
+//   * a caller can bypass all of this by passing its own 32-byte zeroed scratch (pe_svd_orth_frobenius_step_metrics).
+// Both regions are finite; running out is an error code (PE_ERR_INTERNAL), never a silently shared slot.
+constexpr int kStreamSlots = 1024;
+constexpr int kGraphSlots = 3072;
+constexpr int kSlots = kStreamSlots + kGraphSlots;
+struct SlotPool {
+    unsigned int* base = nullptr;
+    std::unordered_map<unsigned long long, int> by_stream;
+    int graph_next = 0;
+};
+inline std::mutex& slot_mutex() {
     static std::mutex mu;
-    static unsigned int* pool[64] = {nullptr};
-    static unsigned long long next[64] = {0};
+    return mu;
+}
+inline SlotPool* slot_pools() {
+    static SlotPool pools[64];
+    return pools;
+}
+// allocate + zero the pool of the given device (idempotent).  Synchronises the device once: the zeroes are in place
+// before any stream, blocking or not, can run a kernel that reads them.
+inline int slots_init(int dev) {
+    if (dev < 0 || dev >= 64) return fail(PE_ERR_BAD_ARG, "device index out of range");
+    std::lock_guard<std::mutex> lk(slot_mutex());
+    SlotPool& sp = slot_pools()[dev];
+    if (sp.base) return 0;
+    int prev = 0;
+    cudaError_t e = cudaGetDevice(&prev);
+    if (e != cudaSuccess) return fail_cuda(e, "cudaGetDevice");
+    if (prev != dev) {
+        e = cudaSetDevice(dev);
+        if (e != cudaSuccess) return fail_cuda(e, "cudaSetDevice");
+    }
+    void* ptr = nullptr;
+    e = cudaMalloc(&ptr, (size_t)kSlots * 32);
+    if (e == cudaSuccess) e = cudaMemset(ptr, 0, (size_t)kSlots * 32);
+    if (e == cudaSuccess) e = cudaDeviceSynchronize();
+    if (e == cudaSuccess) sp.base = static_cast<unsigned int*>(ptr);
+    if (prev != dev) cudaSetDevice(prev);
+    if (e != cudaSuccess) return fail_cuda(e, "pe_init: slot pool");
+    return 0;
+}
+inline int sched_slot(cudaStream_t st, unsigned int** out) {
     int dev = 0;
     cudaError_t e = cudaGetDevice(&dev);
     if (e != cudaSuccess) return fail_cuda(e, "cudaGetDevice");
     if (dev < 0 || dev >= 64) return fail(PE_ERR_BAD_ARG, "device index out of range");
-    std::lock_guard<std::mutex> lk(mu);
-    if (!pool[dev]) {
-        void* ptr = nullptr;
-        e = cudaMalloc(&ptr, kSchedSlots * 32);
-        if (e != cudaSuccess) return fail_cuda(e, "cudaMalloc(scheduler slots)");
-        e = cudaMemset(ptr, 0, kSchedSlots * 32);
-        if (e != cudaSuccess) return fail_cuda(e, "cudaMemset(scheduler slots)");
-        pool[dev] = static_cast<unsigned int*>(ptr);
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    e = cudaStreamIsCapturing(st, &cap);
+    if (e != cudaSuccess) return fail_cuda(e, "cudaStreamIsCapturing");
+    const bool capturing = cap != cudaStreamCaptureStatusNone;
+    if (!slot_pools()[dev].base) {
+        if (capturing)
+            return fail(PE_ERR_BAD_ARG, "pe_init(device) must be called before a launch is captured into a CUDA graph");
+        if (int rc = slots_init(dev)) return rc;
     }
-    *out = pool[dev] + (next[dev]++ % kSchedSlots) * 8;
+    std::lock_guard<std::mutex> lk(slot_mutex());
+    SlotPool& sp = slot_pools()[dev];
+    int idx;
+    if (capturing) {
+        if (sp.graph_next >= kGraphSlots) return fail(PE_ERR_INTERNAL, "out of launch slots for captured launches");
+        idx = kStreamSlots + sp.graph_next++;
+    } else {
+        unsigned long long key = reinterpret_cast<unsigned long long>(st);
+        if (st == cudaStreamPerThread)  // one handle, a different stream in every host thread
+            key ^= (unsigned long long)std::hash<std::thread::id>()(std::this_thread::get_id()) << 8;
+        auto it = sp.by_stream.find(key);
+        if (it == sp.by_stream.end()) {
+            if ((int)sp.by_stream.size() >= kStreamSlots) return fail(PE_ERR_INTERNAL, "out of launch slots (more than 1024 streams)");
+            it = sp.by_stream.emplace(key, (int)sp.by_stream.size()).first;
+        }
+        idx = it->second;
+    }
+    *out = sp.base + (size_t)idx * 8;
     return 0;
 }
 
 // force_direct: test hook (PE_FORCE_DIRECT=1) so that the non-TMA kernel is covered on aligned inputs too
+template <class Op, bool WIDE>
+int stream_launch_tma(Params<Op>& p, cudaStream_t stream, long long ntiles) {
+    using G = Geometry<Op, WIDE>;
+    LaunchCfg cfg;
+    if (int rc = stream_config<Op, WIDE>(&cfg)) return rc;
+    long long grid = (long long)cfg.sms * cfg.ctas_per_sm;
+    if (grid > ntiles) grid = ntiles;
+    cudaError_t le = launch_pdl(stream_tma_kernel<Op, WIDE>, (unsigned)grid, (unsigned)kTile, (size_t)G::kSmemBytes, stream, p);
+    if (le != cudaSuccess) return fail_cuda(le, Op::name());
+    return 0;
+}
+
 template <class Op>
-int stream_launch(Params<Op> p, cudaStream_t stream) {
+constexpr bool wide_ok() { return Op::RPT == 2 && Op::WI0 == 9 && Op::WIDE_OK; }
+
+template <class Op>
+int stream_launch(Params<Op> p, cudaStream_t stream, void* scratch = nullptr) {
     using G = Geometry<Op>;
     if (p.n < 0) return fail(PE_ERR_BAD_ARG, "negative record count");
     if (p.n == 0) return 0;
@@ -573,29 +699,35 @@ int stream_launch(Params<Op> p, cudaStream_t stream) {
     if (Op::NRED > 0 && p.sums == nullptr) return fail(PE_ERR_BAD_ARG, "null accumulator pointer");
     if (Op::FLAG && p.flag == nullptr) return fail(PE_ERR_BAD_ARG, "null flag pointer");
     if (p.in0_stride < G::wi(0)) return fail(PE_ERR_BAD_ARG, "row stride smaller than the record");
-    LaunchCfg cfg;
-    if (int rc = stream_config<Op>(&cfg)) return rc;
-    // Strided or unaligned arrays take the direct kernel.  (Tried: keeping the TMA kernel and gathering a strided in[0]
-    // tile by tile with plain coalesced loads - slower than the direct kernel, 0.49 vs 0.40 ms for svd_orth on a
-    // stride-12 view of 2^24 matrices: the gather is not prefetched and costs a barrier per tile.)
-    bool tma = (p.in0_stride == G::wi(0)) && !force_direct();
-    for (int k = 0; k < 3; ++k) tma = tma && (G::wi(k) == 0 || aligned16(p.in[k]));
-    for (int k = 0; k < 2; ++k) tma = tma && (G::wo(k) == 0 || aligned16(p.out[k]));
-    const long long ntiles = (p.n + G::TR - 1) / G::TR;
-    if (tma) {
-        long long grid = (long long)cfg.sms * cfg.ctas_per_sm;
-        if (grid > ntiles) grid = ntiles;
-        if constexpr (G::SLOT) {
-            if (int rc = sched_slot(&p.sched)) return rc;
+    // Dense, 16-byte aligned arrays take the TMA kernel; so does the SVD family on 12-word rows (wide stage).  Anything
+    // else (other strides, unaligned bases) takes the direct kernel.  (Tried: keeping the dense TMA kernel and gathering
+    // a strided in[0] tile by tile with plain coalesced loads - slower than the direct kernel, 0.49 vs 0.40 ms for
+    // svd_orth on a stride-12 view of 2^24 matrices: the gather is not prefetched and costs a barrier per tile.)
+    bool aligned = !force_direct();
+    for (int k = 0; k < 3; ++k) aligned = aligned && (G::wi(k) == 0 || aligned16(p.in[k]));
+    for (int k = 0; k < 2; ++k) aligned = aligned && (G::wo(k) == 0 || aligned16(p.out[k]));
+    const bool dense = aligned && p.in0_stride == G::wi(0);
+    const bool wide = aligned && wide_ok<Op>() && p.in0_stride == kWideRow && !no_wide();
+    if constexpr (G::SLOT) {
+        if (scratch) {
+            if (reinterpret_cast<uintptr_t>(scratch) & 7u) return fail(PE_ERR_BAD_ARG, "scratch not aligned to 8 bytes");
+            p.sched = static_cast<unsigned int*>(scratch);
+        } else if (int rc = sched_slot(stream, &p.sched)) {
+            return rc;
         }
-        cudaError_t le = launch_pdl(stream_tma_kernel<Op>, (unsigned)grid, (unsigned)kTile, (size_t)G::kSmemBytes, stream, p);
-        if (le != cudaSuccess) return fail_cuda(le, Op::name());
+    }
+    const long long ntiles = (p.n + G::TR - 1) / G::TR;
+    if (dense) {
+        if (int rc = stream_launch_tma<Op, false>(p, stream, ntiles)) return rc;
+    } else if (wide) {
+        if constexpr (wide_ok<Op>()) {
+            if (int rc = stream_launch_tma<Op, true>(p, stream, ntiles)) return rc;
+        }
     } else {
+        LaunchCfg cfg;
+        if (int rc = stream_config<Op>(&cfg)) return rc;
         long long grid = (long long)cfg.sms * 8;
         if (grid > ntiles) grid = ntiles;
-        if constexpr (G::SLOT) {
-            if (int rc = sched_slot(&p.sched)) return rc;
-        }
         stream_direct_kernel<Op><<<(unsigned)grid, kTile, 0, stream>>>(p);
     }
     cudaError_t e = cudaGetLastError();

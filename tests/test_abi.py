@@ -45,7 +45,7 @@ def test_library_exports_every_declared_symbol(built):
 def test_ctypes_table_matches_header(built):
     from poseestimation_b200 import _lib
     d = _declared()
-    compute = {k: v for k, v in d.items() if k not in ("pe_version", "pe_last_error", "pe_launch_count")}
+    compute = {k: v for k, v in d.items() if k not in ("pe_version", "pe_last_error", "pe_launch_count", "pe_init")}
     assert set(compute) == set(_lib.SIGNATURES)
     for name, args in compute.items():
         sig = _lib.SIGNATURES[name]
@@ -65,7 +65,7 @@ def test_ctypes_table_matches_header(built):
 
 def test_version_and_error_convention(built):
     from poseestimation_b200 import _lib
-    assert _lib.version() == 100
+    assert _lib.version() == 200
     # negative count is rejected before any CUDA call
     rc = _lib.lib.pe_svd_orth_fwd(None, 9, None, None, -1, None)
     assert rc == -1
