@@ -19,9 +19,9 @@
  *   - `*_stride` is the distance in FLOATS between consecutive input records (9 for a dense (n, 9) array, 12 for
  *     the out[:, :9] view of a (n, 12) network output); outputs are always dense;
  *   - `stream` is a cudaStream_t passed as void*; all work is enqueued on it, nothing synchronises;
- *   - accumulators: `double* sum` is WRITTEN by the call (its previous content is ignored; the partial sums meet in
- *     library-owned scratch and the last thread block to finish stores the total), `int* flag` is zeroed by the call
- *     on `stream` and then OR-ed into;
+ *   - accumulators: `double* sum` and `int* flag` are WRITTEN by the call (previous content ignored; the partial sums
+ *     and flag bits meet in the launch slot and the last thread block to finish stores the totals): a reducing call is
+ *     ONE stream operation, no memset in front of it;
  *   - return value: 0 = success, > 0 = a cudaError_t from the launch, < 0 = PE_ERR_* below;
  *     pe_last_error() gives a message for the calling thread's last non-zero return;
  *   - there is no CPU path: without an sm_100 device every compute entry point fails.
@@ -78,6 +78,9 @@ int pe_ortho5d_bwd(const float* a, int64_t a_stride, const float* g, float* da, 
 /* ---- 8(f).1  vec_3d_to_SO3(x) = so3_exp_map(x)          rotation_representation.py:245-320 ------------------- */
 int pe_expmap_fwd(const float* v, int64_t v_stride, float* r, int64_t n, void* stream);
 int pe_expmap_bwd(const float* v, int64_t v_stride, const float* g, float* dv, int64_t n, void* stream);
+/* so3_exp_map(log_rot, eps) with the caller's clamp bound on |v|^2 (:245-272; the two above use the default 1e-4). */
+int pe_expmap_eps_fwd(const float* v, int64_t v_stride, float eps, float* r, int64_t n, void* stream);
+int pe_expmap_eps_bwd(const float* v, int64_t v_stride, const float* g, float eps, float* dv, int64_t n, void* stream);
 
 /* ---- a5  loss_frobenius(R_pred, R_true)                 Comparison/main.py:12-16 (+ 7 copies) ----------------
  * *sum = sum_b |a_b - b_b|_F (the caller divides by n: the mean of line 16; across ranks the sums all-reduce). */
@@ -131,9 +134,9 @@ int pe_svd_orth_frobenius_step_mean(const float* m, int64_t m_stride, const floa
  * and angle_error(outR, R) from the same outR):  as pe_svd_orth_frobenius_step, and additionally
  *   sums[0] = sum_b |r_true_b - r_b|_F,  sums[1] = sum_b angle_error(r_b, r_true_b) in degrees (float64 trace and acos
  *   of the fp32 r the step would have written, rotation_representation.py:230-242),
- *   *flag |= 1 if a cosine left [-1.1, 1.1] (:237; the binding raises ValueError),
+ *   sums[2] = 1.0 if a cosine left [-1.1, 1.1] (:237; the binding raises ValueError), else 0.0; *flag (nullable) the
+ *   same as an int.  sums[0..2] is the 24-byte vector the ranks all-reduce.
  *   *loss_mean (nullable) = (float)(sums[0] / n),  *angle_mean (nullable) = sums[1] / n.
- * [sums[0], sums[1], n] is the vector the ranks all-reduce.
  * scratch: NULL, or 32 bytes of caller-owned device memory, 8-byte aligned, zero before its first use (the launch
  * leaves it zero again): then the launch touches no library-owned memory at all - one scratch per launch that can be
  * in flight at a time (e.g. per captured graph node). */

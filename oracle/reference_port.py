@@ -337,8 +337,19 @@ def calculate_T_pred(model_output: torch.Tensor, T_init: torch.Tensor) -> torch.
 
 
 def transform_pts(T: torch.Tensor, pts: torch.Tensor) -> torch.Tensor:
-    """Iterative/loss.py:51-69 for T of shape (B, 4, 4)."""
-    return (T[:, None, :3, :3] @ pts[..., None]).squeeze(-1) + T[:, None, :3, 3]
+    """Iterative/loss.py:51-69: T of shape (B, 4, 4) -> (B, N, 3), or (B, K, 4, 4) -> (B, K, N, 3) (:59-61)."""
+    bsz, n_pts = T.shape[0], pts.shape[1]
+    assert pts.shape == (bsz, n_pts, 3)                                      # :58
+    if T.dim() == 4:
+        pts = pts.unsqueeze(1)                                               # :60
+        assert T.shape[-2:] == (4, 4)                                        # :61
+    elif T.dim() == 3:
+        assert T.shape == (bsz, 4, 4)                                        # :63
+    else:
+        raise ValueError('Unsupported shape for T', T.shape)                 # :65
+    pts = pts.unsqueeze(-1)                                                  # :66
+    T = T.unsqueeze(-3)                                                      # :67
+    return (T[..., :3, :3] @ pts + T[..., :3, [-1]]).squeeze(-1)             # :68-69
 
 
 def compute_ADD_L1_loss(TCO_gt, TCO_pred, points, use_batch_mean=True):

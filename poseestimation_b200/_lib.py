@@ -31,6 +31,8 @@ SIGNATURES = {
     "pe_ortho5d_bwd": [_f, _i64, _f, _f, _i64, _f],
     "pe_expmap_fwd": [_f, _i64, _f, _i64, _f],
     "pe_expmap_bwd": [_f, _i64, _f, _f, _i64, _f],
+    "pe_expmap_eps_fwd": [_f, _i64, _flt, _f, _i64, _f],
+    "pe_expmap_eps_bwd": [_f, _i64, _f, _flt, _f, _i64, _f],
     "pe_frobenius_fwd": [_f, _f, _f, _i64, _f],
     "pe_frobenius_mean_fwd": [_f, _f, _f, _f, _i64, _f],
     "pe_frobenius_bwd": [_f, _f, _f, _flt, _f, _f, _i64, _f],

@@ -34,13 +34,15 @@ def up_to_date() -> bool:
     return all(os.path.getmtime(d) <= t for d in deps)
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
-    if not force and up_to_date():
+def build(force: bool = False, verbose: bool = False, out: str = OUT, defines: tuple = ()) -> str:
+    """`out` / `defines`: A/B variants of the library (e.g. -DPE_ANGLE_LIBM=1 into scratch_bin/), selected at run time with
+    the environment variable PE_ROTATION_LIB; the product build takes neither."""
+    if not force and out == OUT and up_to_date():
         return OUT
     # -cudart shared: the static runtime would embed the names of every runtime entry point (e.g. the batched memcpy
     # calls, which this library never makes) in the shipped artefact; the process already has torch's libcudart loaded
     cmd = [nvcc(), "-O3", "-std=c++17", "--threads", "0", *ARCH, "-lineinfo", "-cudart", "shared", "-Xcompiler", "-fPIC", "-shared",
-           *[os.path.join(CSRC, s) for s in SOURCES], "-o", OUT]
+           *defines, *[os.path.join(CSRC, s) for s in SOURCES], "-o", out]
     if verbose:
         cmd[1:1] = ["-Xptxas", "-v"]
     res = subprocess.run(cmd, capture_output=True, text=True)
@@ -48,8 +50,10 @@ def build(force: bool = False, verbose: bool = False) -> str:
         sys.stderr.write(res.stdout + res.stderr)
     if res.returncode != 0:
         raise RuntimeError("nvcc failed building libpe_rotation.so")
-    return OUT
+    return out
 
 
 if __name__ == "__main__":
-    print(build(force="-f" in sys.argv or "--force" in sys.argv, verbose="-v" in sys.argv))
+    dest = sys.argv[sys.argv.index("-o") + 1] if "-o" in sys.argv else OUT
+    print(build(force="-f" in sys.argv or "--force" in sys.argv, verbose="-v" in sys.argv, out=dest,
+                defines=tuple(a for a in sys.argv[1:] if a.startswith("-D"))))

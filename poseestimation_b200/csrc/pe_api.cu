@@ -18,6 +18,7 @@ Params<Op> make_params(const float* i0, long long stride0, const float* i1, cons
     p.mean_scale = 0.0;
     p.mean64 = nullptr;
     p.flag = flag;
+    p.flag_to_sums = 0;
     p.sched = nullptr;  // assigned by stream_launch
     p.ex = ex;
     return p;
@@ -26,7 +27,7 @@ Params<Op> make_params(const float* i0, long long stride0, const float* i1, cons
 template <class Op>
 int run(const float* i0, long long stride0, const float* i1, const float* i2, float* o0, float* o1, long long n,
         double* sums, int* flag, typename Op::Extra ex, void* stream, float* mean32 = nullptr, double mean_scale = 0.0,
-        double* mean64 = nullptr, void* scratch = nullptr) {
+        double* mean64 = nullptr, void* scratch = nullptr, bool flag_to_sums = false) {
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     if (n < 0) return fail(PE_ERR_BAD_ARG, "negative record count");
     // natural alignment of every array (a misaligned access would be a sticky device fault, not an error code)
@@ -42,11 +43,15 @@ int run(const float* i0, long long stride0, const float* i1, const float* i2, fl
         }
     }
     if (Op::FLAG) {
-        if (!flag) return fail(PE_ERR_BAD_ARG, "null flag pointer");
-        cudaError_t e = cudaMemsetAsync(flag, 0, sizeof(int), st);
-        if (e != cudaSuccess) return fail_cuda(e, "cudaMemsetAsync(flag)");
+        if (!flag && !flag_to_sums) return fail(PE_ERR_BAD_ARG, "null flag pointer");
+        if (n == 0) {  // otherwise the kernel's last CTA writes the flag (its bits meet in the launch slot)
+            cudaError_t e = flag ? cudaMemsetAsync(flag, 0, sizeof(int), st) : cudaSuccess;
+            if (e == cudaSuccess && flag_to_sums) e = cudaMemsetAsync(sums + Op::NRED, 0, sizeof(double), st);
+            if (e != cudaSuccess) return fail_cuda(e, "cudaMemsetAsync(flag)");
+        }
     }
     Params<Op> p = make_params<Op>(i0, stride0, i1, i2, o0, o1, n, sums, flag, ex);
+    p.flag_to_sums = flag_to_sums ? 1 : 0;
     if (mean32) {
         if (reinterpret_cast<uintptr_t>(mean32) & 3u) return fail(PE_ERR_BAD_ARG, "array not aligned to 4 bytes");
         if (n == 0) {  // the mean of an empty batch is NaN, as torch's (all-ones bits are a quiet NaN)
@@ -159,6 +164,14 @@ PE_MAP_API(quat, Quat)
 PE_MAP_API(euler, Euler)
 PE_MAP_API(ortho5d, Ortho5d)
 PE_MAP_API(expmap, Expmap)
+int pe_expmap_eps_fwd(const float* v, int64_t stride, float eps, float* r, int64_t n, void* stream) {
+    if (!(eps > 0.f)) return fail(PE_ERR_BAD_ARG, "eps must be positive");
+    return run<ExpmapEpsFwd>(v, stride, nullptr, nullptr, r, nullptr, n, nullptr, nullptr, {eps}, stream);
+}
+int pe_expmap_eps_bwd(const float* v, int64_t stride, const float* g, float eps, float* dv, int64_t n, void* stream) {
+    if (!(eps > 0.f)) return fail(PE_ERR_BAD_ARG, "eps must be positive");
+    return run<ExpmapEpsBwd>(v, stride, g, nullptr, dv, nullptr, n, nullptr, nullptr, {eps}, stream);
+}
 
 int pe_frobenius_fwd(const float* a, const float* b, double* sum, int64_t n, void* stream) {
     return run<FrobFwd>(a, 9, b, nullptr, nullptr, nullptr, n, sum, nullptr, {}, stream);
@@ -235,7 +248,7 @@ int pe_svd_orth_frobenius_step_metrics(const float* m, int64_t m_stride, const f
                                        double* sums, float* loss_mean, double* angle_mean, int* flag, void* scratch,
                                        int64_t n, void* stream) {
     return run<SvdFrobStepMetrics>(m, m_stride, r_true, nullptr, dm, nullptr, n, sums, flag, {inv_n}, stream, loss_mean,
-                                   n > 0 ? 1.0 / (double)n : 0.0, angle_mean, scratch);
+                                   n > 0 ? 1.0 / (double)n : 0.0, angle_mean, scratch, true);
 }
 int pe_axis_angle_fwd(const float* theta, const float* axis, float* r, int64_t n, void* stream) {
     return run<AxisAngleFwd>(theta, 1, axis, nullptr, r, nullptr, n, nullptr, nullptr, {}, stream);

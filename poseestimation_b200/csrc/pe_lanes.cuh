@@ -106,6 +106,26 @@ struct SvdCtx {
     int deg;
 };
 
+// The scalar routine for degenerate lanes.  PE_FALLBACK_NOINLINE=1 keeps it out of line (one copy per kernel instead of
+// one per lane, its registers not part of the hot path's allocation); A/B switch, see DESIGN.md 4.2.
+#ifndef PE_FALLBACK_NOINLINE
+#define PE_FALLBACK_NOINLINE 0
+#endif
+#if PE_FALLBACK_NOINLINE && defined(__CUDACC__)
+static __device__ __noinline__ void svd_orth_fast_cold(const float* m, float* r, float* ds) {
+    float d;
+    svd_orth_fast(m, r, d);
+    *ds = d;
+}
+#endif
+PE_DEV void svd_orth_degenerate_lane(const float* m, float* r, float& ds) {
+#if PE_FALLBACK_NOINLINE && defined(__CUDA_ARCH__)
+    svd_orth_fast_cold(m, r, &ds);
+#else
+    svd_orth_fast(m, r, ds);
+#endif
+}
+
 template <class T, class Fetch>
 PE_DEV void svd_orth_f(const Fetch& fetch, T* r, T& dsign, SvdCtx<T>* ctx = nullptr) {
     T a[9];
@@ -212,7 +232,7 @@ PE_DEV void svd_orth_f(const Fetch& fetch, T* r, T& dsign, SvdCtx<T>* ctx = null
             fetch(a);
 #pragma unroll
             for (int i = 0; i < 9; ++i) ms[i] = lane_get(a[i], k);
-            svd_orth_fast(ms, rs, ds);
+            svd_orth_degenerate_lane(ms, rs, ds);
 #pragma unroll
             for (int i = 0; i < 9; ++i) lane_put(r[i], k, rs[i]);
             lane_put(dsign, k, ds);

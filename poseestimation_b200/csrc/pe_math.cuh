@@ -519,9 +519,9 @@ PE_DEV void ortho5d_pullback(const float* a, const float* g, float* da) {
 // theta = sqrt(max(|v|^2, 1e-4)); R = (sin theta/theta) K + ((1-cos theta)/theta^2) K^2 + I, K = hat(v).
 // K^2 = v v^T - |v|^2 I uses the UNclamped |v|^2, as the reference's bmm(K, K) does.
 constexpr float kExpEps = 1e-4f;
-PE_DEV void expmap_factors(const float* v, float& n2, float& th, float& f1, float& f2, float& sn, float& cs) {
+PE_DEV void expmap_factors(const float* v, float eps, float& n2, float& th, float& f1, float& f2, float& sn, float& cs) {
     n2 = fmaf(v[2], v[2], fmaf(v[1], v[1], v[0] * v[0]));
-    float c = fmaxf(n2, kExpEps);
+    float c = fmaxf(n2, eps);
     float it = rsqrt_nr(c);
     th = c * it;
     sincos_f(th, &sn, &cs);
@@ -530,17 +530,17 @@ PE_DEV void expmap_factors(const float* v, float& n2, float& th, float& f1, floa
     f1 = sn * it;
     f2 = 2.0f * sh * sh * it * it;  // (1 - cos) / theta^2 without the cancellation
 }
-PE_DEV void expmap(const float* v, float* r) {
+PE_DEV void expmap(const float* v, float* r, float eps = kExpEps) {
     float n2, th, f1, f2, sn, cs;
-    expmap_factors(v, n2, th, f1, f2, sn, cs);
+    expmap_factors(v, eps, n2, th, f1, f2, sn, cs);
     float x = v[0], y = v[1], z = v[2];
     r[0] = fmaf(f2, x * x - n2, 1.0f); r[1] = fmaf(f2, x * y, -f1 * z);   r[2] = fmaf(f2, x * z, f1 * y);
     r[3] = fmaf(f2, x * y, f1 * z);    r[4] = fmaf(f2, y * y - n2, 1.0f); r[5] = fmaf(f2, y * z, -f1 * x);
     r[6] = fmaf(f2, x * z, -f1 * y);   r[7] = fmaf(f2, y * z, f1 * x);    r[8] = fmaf(f2, z * z - n2, 1.0f);
 }
-PE_DEV void expmap_pullback(const float* v, const float* g, float* dv) {
+PE_DEV void expmap_pullback(const float* v, const float* g, float* dv, float eps = kExpEps) {
     float n2, th, f1, f2, sn, cs;
-    expmap_factors(v, n2, th, f1, f2, sn, cs);
+    expmap_factors(v, eps, n2, th, f1, f2, sn, cs);
     float x = v[0], y = v[1], z = v[2];
     float a0 = g[7] - g[5], a1 = g[2] - g[6], a2 = g[3] - g[1];  // sum_ij G_ij dK_ij/dv
     float tr = g[0] + g[4] + g[8];
@@ -553,7 +553,7 @@ PE_DEV void expmap_pullback(const float* v, const float* g, float* dv) {
     float d0 = fmaf(f2, fmaf(-2.0f * tr, x, h0), f1 * a0);
     float d1 = fmaf(f2, fmaf(-2.0f * tr, y, h1), f1 * a1);
     float d2 = fmaf(f2, fmaf(-2.0f * tr, z, h2), f1 * a2);
-    if (n2 >= kExpEps) {  // torch.clamp passes the gradient only where the input is not below the bound
+    if (n2 >= eps) {  // torch.clamp passes the gradient only where the input is not below the bound
         float t2 = th * th, p1, p2;  // p1 = f1'(theta)/theta, p2 = f2'(theta)/theta
         if (th < 0.25f) {
             p1 = -(1.0f / 3.0f) + t2 * ((1.0f / 30.0f) - t2 * (1.0f / 840.0f));

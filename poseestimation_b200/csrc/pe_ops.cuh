@@ -143,7 +143,23 @@ PE_MAP_OPS(Ortho6d, 6, ortho6d, ortho6d_pullback, "ortho6d")   // rotation_repre
 PE_MAP_OPS(Quat, 4, quat_map, quat_pullback, "quat")           // rotation_representation.py:139-172
 PE_MAP_OPS(Euler, 3, euler_map, euler_pullback, "euler")       // rotation_representation.py:92-115
 PE_MAP_OPS(Ortho5d, 5, ortho5d, ortho5d_pullback, "ortho5d")   // rotation_representation.py:120-136
-PE_MAP_OPS(Expmap, 3, expmap, expmap_pullback, "expmap")       // rotation_representation.py:245-320
+PE_MAP_OPS(Expmap, 3, expmap, expmap_pullback, "expmap")       // rotation_representation.py:245-320 (eps = 1e-4)
+// so3_exp_map(log_rot, eps) with the caller's clamp bound (rotation_representation.py:245-272 takes any eps)
+struct ExpEps {
+    float eps;
+};
+struct ExpmapEpsFwd {
+    PE_OP_COMMON("expmap_eps_fwd", 3, 0, 0, 9, 0, 0, false, 4)
+    using Extra = ExpEps;
+    __device__ static __forceinline__ void run(const float* x, const float*, const float*, float* r, float*, double*,
+                                               int&, const Extra& ex) { expmap(x, r, ex.eps); }
+};
+struct ExpmapEpsBwd {
+    PE_OP_COMMON("expmap_eps_bwd", 3, 9, 0, 3, 0, 0, false, 4)
+    using Extra = ExpEps;
+    __device__ static __forceinline__ void run(const float* x, const float* g, const float*, float* dx, float*, double*,
+                                               int&, const Extra& ex) { expmap_pullback(x, g, dx, ex.eps); }
+};
 
 // ---- a5 loss_frobenius (Comparison/main.py:12-16) ---------------------------------------------------------------
 struct FrobFwd {

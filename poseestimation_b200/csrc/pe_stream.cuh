@@ -51,9 +51,11 @@ struct Params {
     float* mean32;         // optional: (float)(sums[0] * mean_scale), written by the same CTA - the float32 batch mean a
     double mean_scale;     // loss function returns, without a follow-up launch that divides and casts
     double* mean64;        // optional: sums[NRED - 1] * mean_scale in float64 (the mean angle error of the metrics step)
-    int* flag;             // OR-ed with the per-record flags
-    unsigned int* sched;   // this launch's slot (set by stream_launch): {next tile to hand out, CTAs finished, -, -,
-                           // two float64 accumulators}; all zero when idle, re-armed by the last CTA
+    int* flag;             // WRITTEN by the last CTA: the OR of the per-record flags (they meet in the slot)
+    int flag_to_sums;      // also store that OR as a double behind the NRED sums: [sum |.|_F, sum theta, flag] is the
+                           // vector the ranks all-reduce
+    unsigned int* sched;   // this launch's slot (set by stream_launch): {next tile to hand out, CTAs finished, flag bits,
+                           // -, two float64 accumulators}; all zero when idle, re-armed by the last CTA
     typename Op::Extra ex;
 };
 
@@ -102,7 +104,7 @@ struct Geometry {
 #endif
     static constexpr int TR = kTile * Op::RPT;  // records per tile (RPT records per thread)
     static constexpr bool DYNAMIC = Op::RPT == 2;  // tiles drawn from a global counter (see stream_tma_kernel)
-    static constexpr bool SLOT = DYNAMIC || Op::NRED > 0;  // the launch needs a slot (scheduler and / or accumulators)
+    static constexpr bool SLOT = DYNAMIC || Op::NRED > 0 || Op::FLAG;  // the launch needs a slot (scheduler / accumulators / flag)
     static constexpr int kBarBytes = 128;
     static constexpr int kStageBytes = TR * 4 * WITOT;
     static constexpr int kOutBytes = TR * 4 * WOTOT;
@@ -142,10 +144,9 @@ __device__ __forceinline__ void sts_pair(float* s, int t, int stride, const F2* 
 // caller's accumulators in front of it).  Also re-arms the tile counter of the dynamic scheduler: every CTA has drawn
 // its last index before it gets here.
 template <class Op>
-__device__ __forceinline__ void block_reduce_and_publish(double* red, int flag, double* sums, int* flagp,
-                                                         double* scratch, unsigned int* slot, float* mean32 = nullptr,
-                                                         double mean_scale = 0.0, double* mean64 = nullptr) {
+__device__ __forceinline__ void block_reduce_and_publish(double* red, int flag, double* scratch, const Params<Op>& p) {
     static_assert(Op::NRED <= 2, "a slot holds two accumulators");
+    unsigned int* slot = p.sched;
     double* acc = reinterpret_cast<double*>(slot + 4);
     if constexpr (Op::NRED > 0) {
         const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -166,7 +167,7 @@ __device__ __forceinline__ void block_reduce_and_publish(double* red, int flag, 
     }
     if constexpr (Op::FLAG) {
         int any = __syncthreads_or(flag);
-        if (threadIdx.x == 0 && any) atomicOr(flagp, any);
+        if (threadIdx.x == 0 && any) atomicOr(slot + 2, (unsigned int)any);
     }
     if constexpr (Geometry<Op>::SLOT) {
         if (threadIdx.x == 0) {
@@ -176,10 +177,16 @@ __device__ __forceinline__ void block_reduce_and_publish(double* red, int flag, 
 #pragma unroll
                 for (int k = 0; k < Op::NRED; ++k) {
                     const double v = __ldcg(acc + k);  // L2: where the other CTAs' atomics landed
-                    sums[k] = v;
-                    if (mean32 && k == 0) mean32[0] = (float)(v * mean_scale);
-                    if (mean64 && k == Op::NRED - 1) mean64[0] = v * mean_scale;
+                    p.sums[k] = v;
+                    if (p.mean32 && k == 0) p.mean32[0] = (float)(v * p.mean_scale);
+                    if (p.mean64 && k == Op::NRED - 1) p.mean64[0] = v * p.mean_scale;
                     acc[k] = 0.0;
+                }
+                if constexpr (Op::FLAG) {
+                    const int f = (int)__ldcg(slot + 2);
+                    if (p.flag) *p.flag = f;
+                    if (p.flag_to_sums) p.sums[Op::NRED] = (double)f;
+                    slot[2] = 0u;
                 }
                 slot[0] = 0u;
                 slot[1] = 0u;
@@ -469,7 +476,7 @@ __global__ void __launch_bounds__(kTile, Op::MINB) stream_tma_kernel(const Param
     if constexpr (G::WOTOT > 0) {
         if (tid == 0) bulk_wait<0>();  // shared memory must outlive the stores that read it
     }
-    block_reduce_and_publish<Op>(red, flag, p.sums, p.flag, s_red, p.sched, p.mean32, p.mean_scale, p.mean64);
+    block_reduce_and_publish<Op>(red, flag, s_red, p);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -543,7 +550,7 @@ __global__ void __launch_bounds__(kTile, direct_min_blocks<Op>()) stream_direct_
             for (int w = 0; w < Op::WO1; ++w) p.out[1][i * Op::WO1 + w] = o1.v[w];
         }
     }
-    block_reduce_and_publish<Op>(red, flag, p.sums, p.flag, s_red, p.sched, p.mean32, p.mean_scale, p.mean64);
+    block_reduce_and_publish<Op>(red, flag, s_red, p);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -697,7 +704,7 @@ int stream_launch(Params<Op> p, cudaStream_t stream, void* scratch = nullptr) {
     for (int k = 0; k < 2; ++k)
         if (G::wo(k) > 0 && p.out[k] == nullptr) return fail(PE_ERR_BAD_ARG, "null output pointer");
     if (Op::NRED > 0 && p.sums == nullptr) return fail(PE_ERR_BAD_ARG, "null accumulator pointer");
-    if (Op::FLAG && p.flag == nullptr) return fail(PE_ERR_BAD_ARG, "null flag pointer");
+    if (Op::FLAG && p.flag == nullptr && !p.flag_to_sums) return fail(PE_ERR_BAD_ARG, "null flag pointer");
     if (p.in0_stride < G::wi(0)) return fail(PE_ERR_BAD_ARG, "row stride smaller than the record");
     // Dense, 16-byte aligned arrays take the TMA kernel; so does the SVD family on 12-word rows (wide stage).  Anything
     // else (other strides, unaligned bases) takes the direct kernel.  (Tried: keeping the dense TMA kernel and gathering

@@ -35,8 +35,7 @@ def get_scene_parameters():
 def calculate_T_pred(model_output, T_init, device=None, rot_repr='SVD'):
     """Iterative/utility.py:90-128.  model_output: (B, >=12) network output (9 rotation entries, vx, vy, vz);
     T_init: (B, 4, 4).  Returns T_pred (B, 4, 4); differentiable w.r.t. model_output (T_init is an input pose)."""
-    if rot_repr != 'SVD':
-        raise ValueError("calculate_T_pred: the reference only implements rot_repr='SVD' (Iterative/utility.py:107)")
+    # `rot_repr` is accepted and ignored, as in the reference (Iterative/utility.py:90-107 always orthogonalises)
     fx, fy = get_scene_parameters()
     out = model_output[:, :12]                       # strided view, read in place
     return _ops.pose_update(out, T_init.float(), float(fx), float(fy))
@@ -47,10 +46,16 @@ def transform_pts(T, pts):
     bsz = T.shape[0]
     n_pts = pts.shape[1]
     assert pts.shape == (bsz, n_pts, 3)                                  # :58
-    if T.dim() == 3:
+    if T.dim() == 4:                                                     # :59-61: K poses per item, (B, K, 4, 4)
+        assert T.shape[-2:] == (4, 4) and T.shape[0] == bsz
+        k = T.shape[1]
+        tf = T.reshape(bsz * k, 4, 4)
+        pf = pts.unsqueeze(1).expand(bsz, k, n_pts, 3).reshape(bsz * k, n_pts, 3)
+        return _ops.affine_points(tf[:, :3, :3], tf[:, :3, 3], pf, False).reshape(bsz, k, n_pts, 3)
+    elif T.dim() == 3:
         assert T.shape == (bsz, 4, 4)                                    # :63
     else:
-        raise ValueError('Unsupported shape for T', T.shape)             # :65 (the 4-D broadcast form is unused)
+        raise ValueError('Unsupported shape for T', T.shape)             # :65
     return _ops.affine_points(T[:, :3, :3], T[:, :3, 3], pts, False)
 
 

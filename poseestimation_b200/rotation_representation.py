@@ -13,8 +13,9 @@ its experiment scripts), ``kabsch``, ``svd_frobenius_loss`` (fused map + loss) a
 """
 from __future__ import annotations
 
-import math
+import math  # noqa: F401
 
+import numpy as np  # noqa: F401  (the reference module's star-import hands `np` and `torch` to its importers)
 import torch
 
 try:  # importable both as poseestimation_b200.rotation_representation and as a top-level rotation_representation
@@ -25,14 +26,14 @@ except ImportError:  # pragma: no cover - top-level import through sys.path
     _sys.path.insert(0, _os.path.dirname(_os.path.dirname(_os.path.abspath(__file__))))
     from poseestimation_b200 import ops as _ops
 
-__all__ = [
-    "compute_rotation_matrix_from_ortho6d", "normalize_vector", "cross_product", "stereographic_unproject",
-    "compute_rotation_matrix_from_euler", "compute_rotation_matrix_from_ortho5d",
-    "compute_rotation_matrix_from_quaternion", "symmetric_orthogonalization",
-    "compute_geodesic_distance_from_two_matrices", "angle_error", "so3_exp_map", "hat", "vec_3d_to_SO3",
-    "transform_output", "get_scene_parameters", "parametrization",
-    "loss_frobenius", "geodesic", "kabsch", "svd_frobenius_loss", "svd_frobenius_loss_and_grad", "mean_angle_error", "map_metric", "install",
-]
+# No __all__ on purpose: the reference module has none, so `from rotation_representation import *` (Comparison/models.py:11,
+# UPNA/main.py:23, 3D-Pose/main.py:23) also hands `torch`, `np`, `nn`, `os`, `sys` to the importing script, and some of
+# them rely on that.  Public names of this module = everything without a leading underscore.
+import os  # noqa: E402,F401
+import sys  # noqa: E402,F401
+import torch.functional as F  # noqa: E402,F401
+import torch.nn as nn  # noqa: E402,F401
+from os.path import join as pjoin  # noqa: E402,F401
 
 
 # ---------------------------------------------------------------------------------------------------------------------
@@ -47,7 +48,10 @@ def symmetric_orthogonalization(x):
         rec = x                                   # possibly strided rows: no copy
     else:
         rec = x.reshape(-1, 9)                    # reference: x.view(-1, 3, 3)
-    return _ops.svd_orth(rec)
+    r = _ops.svd_orth(rec)
+    if r.requires_grad and not torch.compiler.is_compiling():
+        _ops.tag_svd_output(r, rec)               # lets loss_frobenius(r, R_true) take the single-pass step kernel
+    return r
 
 
 def compute_rotation_matrix_from_ortho6d(poses):
@@ -76,9 +80,9 @@ def so3_exp_map(log_rot, eps: float = 0.0001):
     """Rodrigues formula with |v|^2 clamped at ``eps`` (rotation_representation.py:245-272)."""
     if log_rot.dim() != 2 or log_rot.shape[1] != 3:
         raise ValueError("Input tensor shape has to be Nx3.")           # :255-256
-    if abs(eps - 1e-4) > 1e-12:
-        raise ValueError("the native kernel implements the reference's default eps = 1e-4 only")
-    return _ops.expmap(log_rot)
+    if eps == 0.0001:
+        return _ops.expmap(log_rot)
+    return _ops.expmap_eps(log_rot, float(eps))
 
 
 def vec_3d_to_SO3(x):
@@ -138,13 +142,13 @@ def geodesic(R1, R2, reduction="mean"):
     return None                                   # the reference falls off the end of the function
 
 
-def angle_error(R1, R2):
+def angle_error(t_R1, t_R2):
     """Angle between rotations in DEGREES, computed in float64, (B,) float64 (rotation_representation.py:230-242).
 
     Raises ``ValueError`` if any cosine falls outside [-1.1, 1.1] (:237-239) - this reads one int back from the
     device, the same synchronisation the reference's ``torch.any`` incurs.
     """
-    deg, flag = _ops.angle_error_deg(R1, R2)
+    deg, flag = _ops.angle_error_deg(t_R1, t_R2)
     if int(flag.item()) & 1:
         raise ValueError("angle out of range, input probably not proper rotation matrices")
     return deg
@@ -195,19 +199,38 @@ def map_metric(rot_rep, x, R_true, metric="angle_error", reduction="mean", check
 
 
 def loss_frobenius(R_pred, R_true):
-    """mean_b |R_true - R_pred|_F (un-squared), 0-d float32 (Comparison/main.py:12-16 and its 7 copies)."""
+    """mean_b |R_true - R_pred|_F (un-squared), 0-d float32 (Comparison/main.py:12-16 and its 7 copies).
+
+    When one argument is the untouched output of :func:`symmetric_orthogonalization` and a gradient will be asked for
+    (the reference's training step, Comparison/main.py:59-62, UPNA/main.py:54-57, 3D-Pose/main.py:60,85-91), the loss
+    and d loss/d x come from ONE kernel on that call's own input (``ops.frobenius_of_svd_output``): the unchanged two-call
+    surface then costs 72 + 108 B/matrix instead of 360.  Same numbers as :func:`svd_frobenius_loss`."""
+    fused = _ops.frobenius_of_svd_output(R_pred, R_true)
+    if fused is not None:
+        return fused
     return _ops.frobenius_mean(R_pred, R_true)
 
 
-def svd_frobenius_loss(x, R_true, single_pass=True):
+def svd_frobenius_loss(x, R_true, single_pass=True, with_angle=False, check=True):
     """``loss_frobenius(symmetric_orthogonalization(x), R_true)`` fused (Comparison/main.py:59-62 and the 7 copies).
 
     When ``x`` needs a gradient the default is the single-pass step: ONE decomposition per matrix yields the loss and
-    d loss/d x (108 B/matrix), and ``backward`` only scales that gradient by the upstream scalar (72 B/matrix).
-    ``single_pass=False`` keeps nothing between the passes (72 B forward, 108 B backward that recomputes the SVD)."""
+    d loss/d x (108 B/matrix), and ``backward`` only scales that gradient by the upstream scalar (72 B/matrix, nothing
+    when it is exactly 1).  ``single_pass=False`` keeps nothing between the passes (72 B forward, 108 B backward that
+    recomputes the SVD).
+
+    ``with_angle=True`` returns ``(loss, mean_angle)``: ``angle_error(symmetric_orthogonalization(x), R_true).mean()`` in
+    degrees (0-d float64) from the SAME kernel - the metric every training loop of the reference computes next to the
+    loss (Comparison/main.py:59-70, 3D-Pose/main.py:85-91).  ``check`` reads the range flag back and raises the
+    reference's ``ValueError`` (rotation_representation.py:237-239); ``check=False`` synchronises nothing."""
     rec = x if (x.dim() == 2 and x.shape[1] == 9) else x.reshape(-1, 9)
+    if with_angle:
+        loss, angle, flag = _ops.fused_step_loss(rec, R_true, True)
+        if check and int(flag.item()) & 1:
+            raise ValueError("angle out of range, input probably not proper rotation matrices")
+        return loss, angle
     if single_pass and torch.is_grad_enabled() and rec.requires_grad:
-        return _ops.svd_orth_frobenius_step(rec, R_true)[0]
+        return _ops.fused_step_loss(rec, R_true, False)
     return _ops.svd_orth_frobenius(rec, R_true)
 
 

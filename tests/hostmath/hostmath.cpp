@@ -21,6 +21,15 @@ void hm_ortho5d(const float* x, float* r, long n) { LOOP pe::ortho5d(x + 5 * i, 
 void hm_ortho5d_bwd(const float* x, const float* g, float* dx, long n) { LOOP pe::ortho5d_pullback(x + 5 * i, g + 9 * i, dx + 5 * i); }
 void hm_expmap(const float* x, float* r, long n) { LOOP pe::expmap(x + 3 * i, r + 9 * i); }
 void hm_expmap_bwd(const float* x, const float* g, float* dx, long n) { LOOP pe::expmap_pullback(x + 3 * i, g + 9 * i, dx + 3 * i); }
+void hm_expmap_eps(const float* x, const float* eps, float* r, long n) { LOOP pe::expmap(x + 3 * i, r + 9 * i, eps[0]); }
+void hm_expmap_eps_bwd(const float* x, const float* g, const float* eps, float* dx, long n) {
+    LOOP pe::expmap_pullback(x + 3 * i, g + 9 * i, dx + 3 * i, eps[0]);
+}
+// angle_error's float64 tail: the Newton acos (degrees) and the full per-pair angle with its range flag
+void hm_acos_deg(const double* c, double* deg, long n) { LOOP deg[i] = pe::acos_deg_fast(c[i]); }
+void hm_angle_deg(const float* a, const float* b, double* deg, int* flag, long n) {
+    LOOP { int f = 0; deg[i] = pe::angle_deg_f64(a + 9 * i, b + 9 * i, f); flag[i] = f; }
+}
 // sampler map, Kabsch backward coefficients, CosyPose pose update (fx = fy = 4000/9, utility.py:73-88)
 void hm_axis_angle(const float* th, const float* ax, float* r, long n) { LOOP pe::axis_angle_matrix(th[i], ax + 3 * i, r + 9 * i); }
 void hm_kabsch_bwd_coeffs(const float* ctx, const float* r, const float* g, const float* inv_n, float* cq, float* cp, long n) {

@@ -190,8 +190,9 @@ def test_pose_update_matches_reference_golden(it, golden):
         (g64,) = torch.autograd.grad(t64, o64, T(z["g_T"]))
         assert _rel(o.grad.cpu()[:, :12], g64).max() <= 1e-4
         assert o.grad.shape == src.shape and (o.grad[:, 12:] == 0).all()
-    with pytest.raises(ValueError):
-        it.calculate_T_pred(T(z["out"]).cuda(), T(z["T_init"]).cuda(), "cuda", rot_repr="6D")
+    # rot_repr is accepted and ignored, exactly as Iterative/utility.py:90-107 does
+    assert torch.equal(it.calculate_T_pred(T(z["out"]).cuda(), T(z["T_init"]).cuda(), "cuda", rot_repr="6D"),
+                       it.calculate_T_pred(T(z["out"]).cuda(), T(z["T_init"]).cuda(), "cuda"))
 
 
 def test_parametrization_svd_is_the_pose_update_kernel(rr, it, golden):

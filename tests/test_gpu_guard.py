@@ -144,6 +144,34 @@ def test_record_kernels_stay_inside_their_outputs(abi, n, off):
     assert abs(float(s2.words().view(torch.float64)[0]) - float(s.words().view(torch.float64)[0])) <= 1e-9 * n
     assert torch.equal(dm2.words(), dm.words())
     done("pe_svd_orth_frobenius_step_mean")
+    # the step with its metric: [sum |.|_F, sum theta, flag] + float32 / float64 means + int flag, dense and 12-word rows
+    for src, stride in ((m, 9), (wide, 12)):
+        dm3, s3 = out(9 * n), Guarded(6, 0)
+        mean, amean, flag = out(1), Guarded(2, 0), Guarded(1, 0)
+        outs.extend([s3, amean, flag])
+        _call(abi, "pe_svd_orth_frobenius_step_metrics", src.ptr, stride, rot2.ptr, 1.0 / n, dm3.ptr, s3.ptr, mean.ptr,
+              amean.ptr, flag.ptr, None, n, st)
+        torch.cuda.synchronize()
+        if stride == 9:
+            assert torch.equal(dm3.words(), dm.words())
+        v = s3.words().view(torch.float64)
+        assert abs(float(amean.words().view(torch.float64)[0]) - float(v[1]) / n) <= 1e-12 and float(v[2]) == 0.0
+        done("pe_svd_orth_frobenius_step_metrics")
+    # the other SVD-family kernels on 12-word rows (wide TMA stage when aligned, direct kernel otherwise)
+    dmw = out(9 * n)
+    _call(abi, "pe_svd_orth_bwd", wide.ptr, 12, None, g9.ptr, dmw.ptr, n, st)
+    done("pe_svd_orth_bwd(strided)")
+    rw, sw = out(9 * n), out(2, f64=True)
+    _call(abi, "pe_svd_orth_frobenius_fwd", wide.ptr, 12, rot2.ptr, rw.ptr, sw.ptr, n, st)
+    done("pe_svd_orth_frobenius_fwd(strided)")
+    dmw = out(9 * n)
+    _call(abi, "pe_svd_orth_frobenius_bwd", wide.ptr, 12, rot2.ptr, one.ptr, 1.0 / n, dmw.ptr, n, st)
+    done("pe_svd_orth_frobenius_bwd(strided)")
+    x3 = _inp(rnd(n, 3), off)
+    r3, d3 = out(9 * n), out(3 * n)
+    _call(abi, "pe_expmap_eps_fwd", x3.ptr, 3, 1e-2, r3.ptr, n, st)
+    _call(abi, "pe_expmap_eps_bwd", x3.ptr, 3, g9.ptr, 1e-2, d3.ptr, n, st)
+    done("pe_expmap_eps")
     if off == 0:                                                    # documented: 16-byte aligned arrays only
         y = out(9 * n)
         _call(abi, "pe_scale_by_scalar", m.ptr, one.ptr, y.ptr, 9 * n, st)

@@ -256,12 +256,21 @@ def test_single_pass_step_backward_details(rr, ops):
     # gradient accumulation over two steps adds up
     rr.svd_frobenius_loss(x1, rt).backward()
     assert torch.allclose(x1.grad, 2 * g, rtol=1e-6, atol=0)
-    # a second traversal of the same graph is refused loudly, and single_pass=False allows it
+    # a second traversal of the same graph finds the stored gradient handed over and takes the recompute kernel
     x2 = x.clone().requires_grad_(True)
     loss = rr.svd_frobenius_loss(x2, rt)
     loss.backward(retain_graph=True)
-    with pytest.raises(RuntimeError, match="second backward"):
+    loss.backward()
+    assert torch.allclose(x2.grad, 2 * g, rtol=1e-5, atol=1e-9)
+    with pytest.raises(RuntimeError):                      # ... and without retain_graph torch refuses, as for any graph
         loss.backward()
+    # the registered (dispatcher) op is functional: its dx output is never written again, two traversals are exact
+    x4 = x.clone().requires_grad_(True)
+    l4, dx4 = ops.svd_orth_frobenius_step.op(x4, rt)
+    keep = dx4.clone()
+    (l4 * 3.0).backward(retain_graph=True)
+    (l4 * 3.0).backward()
+    assert torch.equal(dx4, keep) and torch.allclose(x4.grad, 6 * g, rtol=1e-6, atol=0)
     x3 = x.clone().requires_grad_(True)
     loss = rr.svd_frobenius_loss(x3, rt, single_pass=False)
     loss.backward(retain_graph=True)

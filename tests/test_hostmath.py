@@ -207,3 +207,58 @@ def test_kabsch_backward_coefficients_vs_oracle_autograd(hm):
     dp = q.double() @ A_p.transpose(1, 2) + b_p[:, None]
     assert _rel(dq.numpy(), dq_ref.numpy()).max() <= 1e-4
     assert _rel(dp.numpy(), dp_ref.numpy()).max() <= 1e-4
+
+
+def test_newton_acos_in_degrees_vs_libm(hm):
+    """acos_deg_fast (pe_math.cuh): 14 FP64 instructions instead of libdevice acos; must agree with float64 acos to
+    far below the 1e-9 degree tolerance of the angle_error tests, including next to +-1 and at 0."""
+    import ctypes
+    rng = np.random.default_rng(0)
+    c = np.concatenate([rng.uniform(-1, 1, 400000), 1 - 10.0 ** rng.uniform(-16, -1, 100000),
+                        -1 + 10.0 ** rng.uniform(-16, -1, 100000), rng.uniform(-1e-3, 1e-3, 10000),
+                        np.array([1.0, -1.0, 0.0, 0.5, -0.5])])
+    c = np.clip(c, -1.0, 1.0)
+    out = np.empty_like(c)
+    dp = ctypes.POINTER(ctypes.c_double)
+    hm.hm_acos_deg(c.ctypes.data_as(dp), out.ctypes.data_as(dp), ctypes.c_long(len(c)))
+    ref = np.degrees(np.arccos(c))
+    assert np.abs(out - ref).max() <= 5e-12
+    nz = ref > 0
+    assert (np.abs(out - ref)[nz] / ref[nz]).max() <= 1e-12
+    assert out[-5] == 0.0 and out[-4] == 180.0
+
+
+def test_angle_error_record_vs_oracle(hm):
+    """angle_deg_f64 = float64 trace of the fp32 entries + range flag + clamp + Newton acos, against the oracle's
+    angle_error (rotation_representation.py:230-242) on the same fp32 inputs; NaN propagates, the flag does not fire on it."""
+    import ctypes
+    g = torch.Generator().manual_seed(3)
+    r1 = O.symmetric_orthogonalization(torch.randn(20000, 9, generator=g).double()).float()
+    r2 = O.symmetric_orthogonalization(torch.randn(20000, 9, generator=g).double()).float()
+    r2[:100] = r1[:100]                                  # identical pairs: the acos floor near zero angle
+    a, b = np.ascontiguousarray(r1.reshape(-1, 9).numpy()), np.ascontiguousarray(r2.reshape(-1, 9).numpy())
+    deg, flag = np.empty(len(a)), np.empty(len(a), np.int32)
+    fp, dp, ip = ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int)
+    hm.hm_angle_deg(a.ctypes.data_as(fp), b.ctypes.data_as(fp), deg.ctypes.data_as(dp), flag.ctypes.data_as(ip),
+                    ctypes.c_long(len(a)))
+    ref = O.angle_error(r1, r2).numpy()
+    assert np.abs(deg - ref).max() <= 1e-10 and not flag.any()
+    bad = np.ascontiguousarray(np.stack([3 * np.eye(3).reshape(9), np.full(9, np.nan)]).astype(np.float32))
+    eye = np.ascontiguousarray(np.stack([np.eye(3).reshape(9)] * 2).astype(np.float32))
+    d2, f2 = np.empty(2), np.empty(2, np.int32)
+    hm.hm_angle_deg(bad.ctypes.data_as(fp), eye.ctypes.data_as(fp), d2.ctypes.data_as(dp), f2.ctypes.data_as(ip),
+                    ctypes.c_long(2))
+    assert f2[0] == 1 and d2[0] == 0.0                   # cos = 4 -> flagged; clamped to 1 -> 0 degrees
+    assert f2[1] == 0 and np.isnan(d2[1])                # NaN: no flag (both comparisons false, :237), NaN angle
+
+
+def test_expmap_with_other_clamp_bounds_vs_golden(hm, golden):
+    z = golden("round2")
+    v = z["exp_v"]
+    for tag, eps in (("1em2", 1e-2), ("1em6", 1e-6)):
+        e = np.array([eps], np.float32)
+        r = hostmath.call(hm, "hm_expmap_eps", v, e, (len(v), 9))
+        assert np.abs(r.reshape(-1, 3, 3) - z[f"exp_r_{tag}"]).max() <= 2e-6
+        dv = hostmath.call(hm, "hm_expmap_eps_bwd", v, z["exp_w"].reshape(-1, 9), e, (len(v), 3))
+        scale = np.abs(z[f"exp_g_{tag}"]).max(1)
+        assert (np.abs(dv - z[f"exp_g_{tag}"]).max(1) / np.maximum(scale, 1.0)).max() <= 2e-5

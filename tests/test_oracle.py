@@ -189,3 +189,25 @@ def test_sampler_map_matches_reference(golden):
     r = m[:8]
     want = torch.bmm(r[:, None].expand(8, 50, 3, 3).reshape(-1, 3, 3), pc.reshape(-1, 3, 1)).view(8, 50, 3)
     assert np.abs(O.rotate_cloud(r, pc).numpy() - want.numpy()).max() <= 1e-15   # point_cloud/main.py:173-181
+
+
+def test_round2_fixture_matches_reference(golden):
+    """tests/golden/round2.npz (make_golden_r2.py): 4-D transform_pts, so3_exp_map with other clamp bounds, and the
+    training step with its metric (Comparison/main.py:59-70)."""
+    z = golden("round2")
+    got = O.transform_pts(T(z["tp4_T"]).double(), T(z["tp4_pts"]).double()).numpy()
+    assert got.shape == z["tp4_out"].shape == (6, 3, 50, 3) and np.abs(got - z["tp4_out"]).max() <= 1e-12
+    for tag, eps in (("1em2", 1e-2), ("1em6", 1e-6)):
+        v = T(z["exp_v"]).double().requires_grad_(True)
+        r = O.so3_exp_map(v, eps)
+        (g,) = torch.autograd.grad((r * T(z["exp_w"])).sum(), v)
+        assert np.abs(r.detach().numpy() - z[f"exp_r_{tag}"]).max() <= 1e-12
+        assert np.abs(g.numpy() - z[f"exp_g_{tag}"]).max() <= 1e-10
+    x, rt = T(z["step_x"]), T(z["step_r_true"])
+    r64 = O.symmetric_orthogonalization(x.double())
+    assert abs(O.loss_frobenius(r64, rt.double()).item() - float(z["step_loss_f64"])) <= 1e-12
+    assert np.abs(O.angle_error(r64, rt.double()).numpy() - z["step_angle_f64"]).max() <= 1e-8
+    # the fp32 pipeline of the scripts: outR in fp32, angles in float64 from it
+    r32 = O.symmetric_orthogonalization(x)
+    assert abs(O.loss_frobenius(r32, rt).item() - float(z["step_loss_fp32"])) <= 1e-6
+    assert np.abs(O.angle_error(r32, rt).numpy() - z["step_angle_fp32_pipeline"]).max() <= 1e-9

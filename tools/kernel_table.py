@@ -67,6 +67,13 @@ def main():
     add("svd_orth_frobenius_fwd", 72, lambda: check(lib.pe_svd_orth_frobenius_fwd(P(x9), 9, P(r1), None, P(sums), n, st), ""))
     add("svd_orth_frobenius_bwd", 108, lambda: check(lib.pe_svd_orth_frobenius_bwd(P(x9), 9, P(r1), P(one), 1.0 / n, P(o9b), n, st), ""))
     add("svd_orth_frobenius_step (loss + grad, one SVD)", 108, lambda: check(lib.pe_svd_orth_frobenius_step(P(x9), 9, P(r1), 1.0 / n, P(o9b), P(sums), n, st), ""))
+    sums3 = torch.zeros(3, dtype=torch.float64, device=dev)
+    add("svd_orth_frobenius_step_metrics (loss + mean angle + grad)", 108, lambda: check(lib.pe_svd_orth_frobenius_step_metrics(P(x9), 9, P(r1), 1.0 / n, P(o9b), P(sums3), None, None, None, None, n, st), ""))
+    w12 = rnd(n, 12)
+    add("svd_orth_fwd on out[:, :9] of (n, 12) (wide TMA stage)", 72, lambda: check(lib.pe_svd_orth_fwd(P(w12), 12, P(o9), None, n, st), ""))
+    add("svd_orth_bwd (recompute) on the (n, 12) view", 108, lambda: check(lib.pe_svd_orth_bwd(P(w12), 12, None, P(g9), P(o9b), n, st), ""))
+    add("step_metrics on the (n, 12) view", 108, lambda: check(lib.pe_svd_orth_frobenius_step_metrics(P(w12), 12, P(r1), 1.0 / n, P(o9b), P(sums3), None, None, None, None, n, st), ""))
+    del w12
     add("scale_by_scalar (backward of the step)", 72, lambda: check(lib.pe_scale_by_scalar(P(o9b), P(one), P(o9), 9 * n, st), ""))
     for name, w in (("ortho6d", 6), ("quat", 4), ("euler", 3), ("ortho5d", 5), ("expmap", 3)):
         xi, dxi = rnd(n, w), torch.empty(n, w, device=dev)

@@ -99,8 +99,42 @@ def main():
         torch.cuda.synchronize()
         assert torch.equal(grad, ref_grad) and abs(float(loss) - float(ref_loss)) <= 1e-6
         row["loss_and_grad_cuda_graph_us"] = timed(graph.replay, args.reps)
+
+        def step_with_metric():
+            x.grad = None
+            loss, ang = rr.svd_frobenius_loss(x, rt, with_angle=True, check=False)
+            loss.backward()
+
+        row["fused_step_with_mean_angle_us"] = timed(step_with_metric, args.reps)
         res[str(b)] = {k: round(v, 2) for k, v in row.items()}
-    print(json.dumps({"what": "microseconds per call, wall clock, 1 B200", "reps": args.reps, "batch": res}))
+    # Kabsch at the reference's cloud batch (point_cloud/main.py:257: 128 clouds x 1024 points) and smaller: one warp per
+    # pair, so 128 pairs occupy 16 of 148 SMs - is a call launch-bound (then nothing is to gain) or stream-bound?
+    kab = {}
+    for b, npts in ((32, 1024), (128, 1024), (128, 4096), (1024, 1024)):
+        p = torch.rand(b, npts, 3, device=dev) - 0.5
+        q = torch.rand(b, npts, 3, device=dev) - 0.5
+        w = torch.rand(b, npts, device=dev)
+        pg, qg = p.clone().requires_grad_(True), q.clone().requires_grad_(True)
+
+        def fwd_bwd():
+            pg.grad = qg.grad = None
+            r, t = rr.kabsch(pg, qg)
+            (r.sum() + t.sum()).backward()
+
+        graph = torch.cuda.CUDAGraph()
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            rr.kabsch(p, q)
+        torch.cuda.current_stream().wait_stream(side)
+        with torch.cuda.graph(graph):
+            rr.kabsch(p, q)
+        kab[f"{b}x{npts}"] = {"kabsch_fwd_us": round(timed(lambda: rr.kabsch(p, q), args.reps), 2),
+                              "kabsch_fwd_cuda_graph_us": round(timed(graph.replay, args.reps), 2),
+                              "kabsch_weighted_fwd_us": round(timed(lambda: rr.kabsch(p, q, weights=w), args.reps), 2),
+                              "kabsch_fwd_bwd_us": round(timed(fwd_bwd, args.reps), 2)}
+    print(json.dumps({"what": "microseconds per call, wall clock, 1 B200", "reps": args.reps, "batch": res,
+                      "kabsch": kab}))
 
 
 if __name__ == "__main__":

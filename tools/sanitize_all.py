@@ -4,8 +4,8 @@ available:
     compute-sanitizer --tool memcheck  --error-exitcode 3 python tools/sanitize_all.py
     compute-sanitizer --tool racecheck --error-exitcode 3 python tools/sanitize_all.py
 
-(On the GPU pool this repository was measured on, compute-sanitizer is switched off; tests/test_gpu_guard.py is the
-stand-in there: guard bands around every output of every entry point.)
+(tools/run_sanitizers.sh runs all four tools and keeps the logs; profiles/r2_sanitizer_*.log are its output on the GPU
+pool.  tests/test_gpu_guard.py - guard bands around every output of every entry point - runs with the GPU tests.)
 
 Sizes cover: one record, a ragged tail (n % 256 != 0, n % 512 != 0), several tiles per CTA (so the shared-memory rings
 wrap and the tile scheduler hands out more tiles than there are CTAs), unaligned / strided inputs (the direct kernels),
@@ -38,6 +38,19 @@ def main():
             x.grad = None
             rr.svd_frobenius_loss(x, rt, single_pass=single).backward()
         loss, g = rr.svd_frobenius_loss_and_grad(x.detach(), rt)
+        # the step with its metric, the drop-in route that parks its gradient on the svd_orth node, a second traversal
+        x.grad = None
+        loss, ang = rr.svd_frobenius_loss(x, rt, with_angle=True)
+        loss.backward()
+        x.grad = None
+        rloss = rr.loss_frobenius(rr.symmetric_orthogonalization(x), rt)
+        rloss.backward(retain_graph=True)
+        rloss.backward()
+        # 12-word rows whose storage ends with the last matrix (wide TMA stage: last tile by plain loads)
+        tight = torch.randn(n * 12 - 3, device=dev).as_strided((n, 9), (12, 1))
+        rr.symmetric_orthogonalization(tight)
+        rr.svd_frobenius_loss_and_grad(tight, rt)
+        rr.map_metric("SVD", tight, rt)
         # strided rows (read in place) and an unaligned base (direct kernels)
         wide = torch.randn(n, 12, device=dev)
         rr.symmetric_orthogonalization(wide[:, :9])
@@ -90,6 +103,22 @@ def main():
         it.compute_ADD_L1_loss(poses, poses2, p.detach()).backward()
         it.compute_ADD_L1_loss(poses, poses2, p.detach(), use_batch_mean=False)
         it.compute_disentangled_ADD_L1_loss(poses2, poses, p.detach()).backward()
+    # a captured step replayed next to eager launches on another stream (launch slots: per stream / per captured launch)
+    n = 40000
+    xa, xb = torch.randn(n, 9, device=dev), torch.randn(n, 9, device=dev)
+    rt = rr.symmetric_orthogonalization(torch.randn(n, 9, device=dev))
+    s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
+    with torch.cuda.stream(s1):
+        rr.svd_frobenius_loss_and_grad(xa, rt)
+    torch.cuda.synchronize()
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph, stream=s1):
+        rr.svd_frobenius_loss_and_grad(xa, rt)
+    for _ in range(int(os.environ.get("PE_SANITIZE_REPLAYS", 20))):
+        with torch.cuda.stream(s1):
+            graph.replay()
+        with torch.cuda.stream(s2):
+            rr.svd_frobenius_loss_and_grad(xb, rt)
     torch.cuda.synchronize()
     print(f"sanitize_all: {lib.pe_launch_count() - start} launches, ok")
 
