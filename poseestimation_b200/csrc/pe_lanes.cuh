@@ -348,6 +348,54 @@ PE_DEV void svd_orth_pullback_t(const T* m, const T* r, const T* g, T* dm) {
     svd_orth_pullback_solve(m, r, z0, z1, z2, dm);
 }
 
+// ---- angle_error for the fused sums, lane-generic ---------------------------------------------------------------------
+// tr(R^T R_t) - 1 (= 2 cos) as an UNEVALUATED float32 pair ahi + lo, error-free to ~1e-11: every product is added to a
+// big accumulator (96 = 1.5 * 2^6, one ulp = 2^-17) by ONE fused multiply-add, whose rounding error is recovered
+// exactly by two more (acc - acc' is exact, r m - (acc' - acc) is the error, <= 2^-18) and summed on the side.  Four
+// packed instructions per product and no conversion, against 2 conversions + 1 DFMA per product and lane in float64.
+// acc stays inside [64, 128) for |trace| <= 32, i.e. for anything that is remotely a pair of rotations.
+template <class T>
+PE_DEV void trace_minus_one_split(const T* r, const T* m, T& ahi, T& lo) {
+    const T z = r[0];
+    const T minus1 = t_set(z, -1.0f);
+    T acc = t_set(z, 96.0f);
+    lo = t_set(z, 0.0f);
+#pragma unroll
+    for (int i = 0; i < 9; ++i) {
+        const T an = t_fma(r[i], m[i], acc);
+        const T dl = t_fma(an, minus1, acc);
+        lo = t_add(lo, t_fma(r[i], m[i], dl));
+        acc = an;
+    }
+    ahi = t_add(acc, t_set(z, -97.0f));
+}
+// t = (1 - |cos|)/2 from that pair (exact up to the final rounding) and the sign of the cosine
+template <class T, class M>
+PE_DEV T half_versine_from_split(T ahi, T lo, M& neg, T& a32) {
+    const T z = ahi;
+    a32 = t_add(ahi, lo);
+    neg = t_ltz(a32);
+    const T sg = t_sel(neg, t_set(z, 0.25f), t_set(z, -0.25f));  // -sign(cos) / 4
+    return t_fma(sg, lo, t_fma(t_set(z, -0.25f), t_abs(ahi), t_set(z, 0.5f)));
+}
+// degrees from t = sin^2(angle/2 or (180 - angle)/2): angle_deg_tail32 of pe_math.cuh for one or two lanes
+template <class T, class M>
+PE_DEV T angle_deg_tail32_t(T t, M neg) {
+    const T z = t;
+    t = t_sel(t_ltz(t), t_set(z, 0.0f), t);
+    const T h = t_sqrt_fast(t);
+    const T u = t_mul(h, h);
+    T q = t_set(z, kAsinC6);
+    q = t_fma(q, u, t_set(z, kAsinC5));
+    q = t_fma(q, u, t_set(z, kAsinC4));
+    q = t_fma(q, u, t_set(z, kAsinC3));
+    q = t_fma(q, u, t_set(z, kAsinC2));
+    q = t_fma(q, u, t_set(z, kAsinC1));
+    q = t_fma(q, u, t_set(z, kAsinC0));
+    const T psi = t_fma(t_mul(h, u), q, h);
+    return t_fma(psi, t_sel(neg, t_set(z, -kTwoRadToDeg), t_set(z, kTwoRadToDeg)), t_sel(neg, t_set(z, 180.0f), t_set(z, 0.0f)));
+}
+
 // d = a - b and |d|_F^2, lane-generic
 template <class T>
 PE_DEV T diff9_sq(const T* a, const T* b, T* d) {

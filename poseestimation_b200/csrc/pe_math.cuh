@@ -714,6 +714,9 @@ PE_DEV double acos_deg_fast(double c) {
 #ifndef PE_ANGLE_LIBM
 #define PE_ANGLE_LIBM 0   // 1: libdevice acos (the round-1 path, kept for A/B runs)
 #endif
+#ifndef PE_FUSED_ANGLE_F64
+#define PE_FUSED_ANGLE_F64 0   // 1: the fused means finish the angle in float64 as well (A/B runs)
+#endif
 // tr = tr(R1^T R2) in float64 -> degrees (the second half of angle_error; split so that a kernel can form the trace
 // while both matrices are in registers and finish the angle later, when they are dead)
 PE_DEV double angle_deg_from_trace(double tr, int& flag) {
@@ -724,6 +727,41 @@ PE_DEV double angle_deg_from_trace(double tr, int& flag) {
     return acos(cc) * 57.295779513082320876798154814105;
 #else
     return c == c ? acos_deg_fast(cc) : c;  // NaN in, NaN out as torch.clamp / torch.acos (fmin / fmax would drop it)
+#endif
+}
+// The same angle for kernels that only SUM it over the batch (the fused means): the float64 part stops at
+// t = (1 - |c|)/2 = 1/2 - |tr - 1|/4, which is exact, and the arcsine of sqrt(t) is float32 - psi = asin(sqrt t) is
+// well conditioned everywhere (relative error 1e-7 from t's rounding, the polynomial and MUFU.SQRT), so the angle is good to
+// 1e-7 rad + 180 * 2^-24 degrees: <= 2e-5 degrees per record, without the blow-up near 0 and 180 degrees that a
+// float32 TRACE would have; the per-record errors are independent, so a batch mean moves by less than 1e-6 degrees
+// (north_star: 1e-4).  12 FP32 + 2 MUFU + 3 FP64 instructions instead of 24 FP32 + 14 FP64 + 4 conversions.
+constexpr float kAsinC6 = 0.10931160300970078f, kAsinC5 = -0.08920358866453171f, kAsinC4 = 0.07470467686653137f,
+                kAsinC3 = 0.01712605729699135f, kAsinC2 = 0.04638223350048065f, kAsinC1 = 0.07489369064569473f,
+                kAsinC0 = 0.1666688472032547f;
+constexpr float kTwoRadToDeg = 114.59155902616464f;  // 2 * 180 / pi
+PE_DEV float angle_deg_tail32(float t, bool cos_nonneg) {
+    t = t < 0.f ? 0.f : t;  // |c| > 1: the reference clamps the cosine; NaN stays NaN
+    const float h = sqrt_fast(t);
+    const float u = h * h;
+    float q = kAsinC6;
+    q = fmaf(q, u, kAsinC5);
+    q = fmaf(q, u, kAsinC4);
+    q = fmaf(q, u, kAsinC3);
+    q = fmaf(q, u, kAsinC2);
+    q = fmaf(q, u, kAsinC1);
+    q = fmaf(q, u, kAsinC0);
+    const float psi = fmaf(h * u, q, h);
+    return cos_nonneg ? kTwoRadToDeg * psi : fmaf(-kTwoRadToDeg, psi, 180.0f);
+}
+PE_DEV double angle_deg_sum_term(double tr, int& flag) {
+#if PE_FUSED_ANGLE_F64
+    return angle_deg_from_trace(tr, flag);
+#else
+    const double a = tr - 1.0;                       // 2 c
+    const float a32 = (float)a;
+    if (a32 < -2.2f || a32 > 2.2f) flag |= 1;        // c outside [-1.1, 1.1]
+    const float t = (float)fma(-0.25, fabs(a), 0.5); // (1 - |c|) / 2, exact in float64 before the rounding
+    return (double)angle_deg_tail32(t, !(a < 0.0));
 #endif
 }
 PE_DEV double angle_deg_f64(const float* a, const float* b, int& flag) {

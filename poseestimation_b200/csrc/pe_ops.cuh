@@ -393,25 +393,62 @@ struct StepScale {
 // (Comparison/main.py:59-70, 3D-Pose/main.py:60-62,85-91), and the pair [sum |.|_F, sum theta] is what the ranks
 // all-reduce.  The trace of R^T R_true is formed in float64 while both matrices are in registers (exact
 // products); the acos runs at the end of the record, when only dM is live.
+// PE_STEP_ANGLE: how the step kernel evaluates the angle (A/B switch; DESIGN.md 4.4 has the measurements)
+//   0  float64 trace (9 DFMA + 18 conversions per lane) and the float64 Newton acos
+//   1  float64 trace, float32 arcsine tail (angle_deg_sum_term)
+//   2  error-free float32 trace (trace_minus_one_split, packed for both lanes) and the float32 tail: no float64 at all
+//      until the angle is added to the accumulator
+#ifndef PE_STEP_ANGLE
+#define PE_STEP_ANGLE 2
+#endif
+// sum of the angles of one record (pair) from the error-free float32 trace (pe_lanes.cuh), with the range flag
+template <class T>
+__device__ __forceinline__ void angle_sum_from_split(T ahi, T lo, double& red, int& flag, bool v0, bool v1) {
+    const bool valid[2] = {v0, v1};
+    decltype(t_ltz(ahi)) neg;
+    T a32;
+    const T t = half_versine_from_split(ahi, lo, neg, a32);
+    const T deg = angle_deg_tail32_t(t, neg);
+#pragma unroll
+    for (int l = 0; l < LaneCount<T>::value; ++l) {
+        if (valid[l]) {
+            const float a = lane_get(a32, l);
+            if (a < -2.2f || a > 2.2f) flag |= 1;  // cosine outside [-1.1, 1.1] (rotation_representation.py:237)
+            red += (double)lane_get(deg, l);
+        }
+    }
+}
+template <class T>
+struct AngleSeed {
+#if PE_STEP_ANGLE == 2
+    T ahi, lo;
+#else
+    double tr[LaneCount<T>::value];
+#endif
+};
 template <bool ANGLE>
 struct SvdFrobStepT {
     PE_OP_COMMON2(ANGLE ? "svd_orth_frobenius_step_metrics" : "svd_orth_frobenius_step", 9, 9, 0, 9, 0, ANGLE ? 2 : 1,
                   ANGLE, 3)
     using Extra = StepScale;
     template <class T, class S0, class S1>
-    __device__ static __forceinline__ T body(const S0& ms, const S1& rts, T* dm, float gs, double* tr) {
+    __device__ static __forceinline__ T body(const S0& ms, const S1& rts, T* dm, float gs, AngleSeed<T>& seed) {
         T r[9], m[9];
         SvdCtx<T> ctx;
         svd_from_ctx<T>(ms, r, ctx);
         rts.load(m);  // R_true
         if constexpr (ANGLE) {
+#if PE_STEP_ANGLE == 2
+            trace_minus_one_split(r, m, seed.ahi, seed.lo);
+#else
 #pragma unroll
             for (int l = 0; l < LaneCount<T>::value; ++l) {
                 double s = 0.0;
 #pragma unroll
                 for (int i = 0; i < 9; ++i) s = fma((double)lane_get(r[i], l), (double)lane_get(m[i], l), s);
-                tr[l] = s;
+                seed.tr[l] = s;
             }
+#endif
         }
         T f;
         T z0, z1, z2;
@@ -419,22 +456,38 @@ struct SvdFrobStepT {
         pullback_ctx<T>(ctx, ms, r, z0, z1, z2, dm);
         return f;
     }
+    // the angle(s) of the record (pair) from what the body kept; runs when only dM is live
+    template <class T>
+    __device__ static __forceinline__ void finish(const AngleSeed<T>& seed, double* red, int& flag, bool v0, bool v1) {
+#if PE_STEP_ANGLE == 2
+        angle_sum_from_split(seed.ahi, seed.lo, red[1], flag, v0, v1);
+#else
+        const bool valid[2] = {v0, v1};
+#pragma unroll
+        for (int l = 0; l < LaneCount<T>::value; ++l) {
+            if (valid[l]) {
+#if PE_STEP_ANGLE == 1
+                red[1] += angle_deg_sum_term(seed.tr[l], flag);
+#else
+                red[1] += angle_deg_from_trace(seed.tr[l], flag);
+#endif
+            }
+        }
+#endif
+    }
     __device__ static __forceinline__ void run(const float* m, const float* rt, const float*, float* dm, float*,
                                                double* red, int& flag, const Extra& ex) {
-        double tr[1];
-        red[0] += (double)body<float>(RegSrc<9>{m}, RegSrc<9>{rt}, dm, ex.mul, tr);
-        if constexpr (ANGLE) red[1] += angle_deg_from_trace(tr[0], flag);
+        AngleSeed<float> seed;
+        red[0] += (double)body<float>(RegSrc<9>{m}, RegSrc<9>{rt}, dm, ex.mul, seed);
+        if constexpr (ANGLE) finish<float>(seed, red, flag, true, false);
     }
     template <class S0>
     __device__ static __forceinline__ void run2(const S0& m, const PairSrc<9>& rt, const PairSrc<0>&, F2* dm, F2*,
                                                 double* red, int& flag, bool v0, bool v1, const Extra& ex) {
-        double tr[2];
-        F2 f = body<F2>(m, rt, dm, ex.mul, tr);
+        AngleSeed<F2> seed;
+        F2 f = body<F2>(m, rt, dm, ex.mul, seed);
         red[0] += (double)((v0 ? f.x : 0.f) + (v1 ? f.y : 0.f));
-        if constexpr (ANGLE) {
-            if (v0) red[1] += angle_deg_from_trace(tr[0], flag);
-            if (v1) red[1] += angle_deg_from_trace(tr[1], flag);
-        }
+        if constexpr (ANGLE) finish<F2>(seed, red, flag, v0, v1);
     }
 };
 using SvdFrobStep = SvdFrobStepT<false>;
@@ -454,7 +507,7 @@ __device__ __forceinline__ void metric_accumulate(const float* r, const float* r
         float c = 0.5f * (dot9(r, rt) - 1.0f);
         red[0] += (double)acosf(fminf(fmaxf(c, ex.lo), ex.hi));
     } else {
-        red[0] += angle_deg_f64(r, rt, flag);
+        red[0] += angle_deg_sum_term(dot9_f64(r, rt), flag);
     }
 }
 #define PE_MAP_METRIC(Tag, W, FWD, LABEL)                                                                     \
@@ -490,6 +543,14 @@ struct SvdMetric {
         F2 r[9], rt[9], ds;
         svd_from<F2>(m, r, ds);
         rts.load(rt);
+#if PE_STEP_ANGLE == 2
+        if constexpr (METRIC == 2) {  // both lanes at once: error-free float32 trace, float32 arcsine
+            F2 ahi, lo;
+            trace_minus_one_split(r, rt, ahi, lo);
+            angle_sum_from_split(ahi, lo, red[0], flag, v0, v1);
+            return;
+        }
+#endif
         float a[9], b[9];
         if (v0) {
 #pragma unroll

@@ -205,9 +205,10 @@ def loss_frobenius(R_pred, R_true):
     (the reference's training step, Comparison/main.py:59-62, UPNA/main.py:54-57, 3D-Pose/main.py:60,85-91), the loss
     and d loss/d x come from ONE kernel on that call's own input (``ops.frobenius_of_svd_output``): the unchanged two-call
     surface then costs 72 + 108 B/matrix instead of 360.  Same numbers as :func:`svd_frobenius_loss`."""
-    fused = _ops.frobenius_of_svd_output(R_pred, R_true)
-    if fused is not None:
-        return fused
+    if not torch.compiler.is_compiling():          # (a traced graph goes through the registered ops)
+        fused = _ops.frobenius_of_svd_output(R_pred, R_true)
+        if fused is not None:
+            return fused
     return _ops.frobenius_mean(R_pred, R_true)
 
 

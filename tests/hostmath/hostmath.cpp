@@ -30,6 +30,24 @@ void hm_acos_deg(const double* c, double* deg, long n) { LOOP deg[i] = pe::acos_
 void hm_angle_deg(const float* a, const float* b, double* deg, int* flag, long n) {
     LOOP { int f = 0; deg[i] = pe::angle_deg_f64(a + 9 * i, b + 9 * i, f); flag[i] = f; }
 }
+// the fused sums' angle: float64 trace + float32 tail (scalar kernels), and the error-free float32 trace + float32 tail
+// in the packed two-lane form of the SVD kernels (record i rides with record i + n/2)
+void hm_angle_sum_term(const float* a, const float* b, double* deg, int* flag, long n) {
+    LOOP { int f = 0; deg[i] = pe::angle_deg_sum_term(pe::dot9_f64(a + 9 * i, b + 9 * i), f); flag[i] = f; }
+}
+void hm_angle_split_x2(const float* a, const float* b, double* deg, float* ahi_lo, long n) {
+    long h = n / 2;
+    for (long i = 0; i < h; ++i) {
+        pe::F2 aa[9], bb[9], ahi, lo, a32;
+        for (int k = 0; k < 9; ++k) { aa[k] = pe::F2{a[9 * i + k], a[9 * (i + h) + k]}; bb[k] = pe::F2{b[9 * i + k], b[9 * (i + h) + k]}; }
+        pe::trace_minus_one_split(aa, bb, ahi, lo);
+        pe::B2 neg;
+        pe::F2 t = pe::half_versine_from_split(ahi, lo, neg, a32);
+        pe::F2 d = pe::angle_deg_tail32_t(t, neg);
+        deg[i] = d.x; deg[i + h] = d.y;
+        ahi_lo[2 * i] = ahi.x; ahi_lo[2 * i + 1] = lo.x; ahi_lo[2 * (i + h)] = ahi.y; ahi_lo[2 * (i + h) + 1] = lo.y;
+    }
+}
 // sampler map, Kabsch backward coefficients, CosyPose pose update (fx = fy = 4000/9, utility.py:73-88)
 void hm_axis_angle(const float* th, const float* ax, float* r, long n) { LOOP pe::axis_angle_matrix(th[i], ax + 3 * i, r + 9 * i); }
 void hm_kabsch_bwd_coeffs(const float* ctx, const float* r, const float* g, const float* inv_n, float* cq, float* cp, long n) {

@@ -143,7 +143,7 @@ def test_config3_fused_map_metric_equals_map_then_metric(rr, fname, w, key):
     x = torch.randn(N3, w, device="cuda")
     rt = rr.compute_rotation_matrix_from_quaternion(torch.randn(N3, 4, device="cuda"))
     r = getattr(rr, fname)(x)
-    assert abs(rr.map_metric(rot_rep, x, rt, "angle_error").item() - rr.mean_angle_error(r, rt).item()) <= 1e-9 * 180
+    assert abs(rr.map_metric(rot_rep, x, rt, "angle_error").item() - rr.mean_angle_error(r, rt).item()) <= 1e-7
     assert abs(rr.map_metric(rot_rep, x, rt, "geodesic").item() - rr.geodesic(r, rt, "mean").item()) <= 1e-6
     assert abs(rr.map_metric(rot_rep, x, rt, "frobenius").item() - rr.loss_frobenius(r, rt).item()) <= 1e-6
     # the map of a rotation's own parameters has zero distance to it (up to the acos floor of a float cosine)

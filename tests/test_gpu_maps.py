@@ -149,8 +149,10 @@ def test_fused_map_metric_matches_oracle_and_unfused(rr, key, w, fname, n):
     got = rr.map_metric(key, xd, rtd, "angle_error")
     assert got.dtype == torch.float64 and got.dim() == 0
     assert abs(got.item() - want) <= 1e-4 * max(1.0, 30.0 / n ** 0.5)        # north_star: 1e-4 degrees on the mean
+    # the fused sums finish the angle with a float32 arcsine of the exact (1 - |cos|)/2: <= 2e-5 degrees per record
+    # against the all-float64 angle_error kernel, errors independent from record to record
     unfused = rr.mean_angle_error(getattr(rr, fname)(xd), rtd).item()
-    assert abs(got.item() - unfused) <= 1e-9 * 180
+    assert abs(got.item() - unfused) <= 2e-5 / max(1.0, n ** 0.5 / 8)
     assert abs(rr.map_metric(key, xd, rtd, "angle_error", reduction="sum").item() / n - got.item()) <= 1e-9 * 180
     # geodesic with the clamp of point_cloud/main.py:61-73 and of rotation_representation.py:209-227
     for metric, fn in (("geodesic", lambda a, b: O.geodesic(a, b, "mean")),
@@ -169,7 +171,7 @@ def test_fused_map_metric_interface(rr):
     # a (B, 12) network output read in place through its first columns
     a = rr.map_metric("SVD", x[:, :9], rt)
     b = rr.mean_angle_error(rr.symmetric_orthogonalization(x[:, :9]), rt)
-    assert abs(a.item() - b.item()) <= 1e-9
+    assert abs(a.item() - b.item()) <= 2e-5
     with pytest.raises(KeyError):
         rr.map_metric("7D", x[:, :7], rt)
     with pytest.raises(ValueError):

@@ -49,9 +49,10 @@ def test_step_with_angle_vs_reference_golden(rr, golden):
     assert abs(loss.item() - float(z["step_loss_f64"])) <= 1e-6
     assert abs(ang.item() - z["step_angle_f64"].mean()) <= 1e-4                # north_star
     assert abs(ang.item() - z["step_angle_fp32_pipeline"].mean()) <= 1e-4
-    # identical to the two-call route on the same device: the step forms the same fp32 R in registers
+    # the two-call route on the same device: the step forms the same fp32 R in registers, its trace error-free in
+    # float32, and finishes with a float32 arcsine: <= 2e-5 degrees per record, independent errors
     unfused = rr.mean_angle_error(rr.symmetric_orthogonalization(x), rt)
-    assert abs(ang.item() - unfused.item()) <= 1e-9
+    assert abs(ang.item() - unfused.item()) <= 2e-6
     loss.backward()
     xe = x.clone().requires_grad_(True)
     rr.svd_frobenius_loss(xe, rt).backward()
@@ -70,7 +71,7 @@ def test_step_with_angle_vs_oracle_and_unfused(rr, ops, n):
     assert abs(ang.item() - want_ang) <= 1e-4
     l2, dx2 = ops.svd_orth_frobenius_step(xd, rtd)
     assert torch.equal(dx, dx2) and abs(loss.item() - l2.item()) <= 1e-6
-    assert abs(ang.item() - rr.mean_angle_error(rr.symmetric_orthogonalization(xd), rtd).item()) <= 1e-9
+    assert abs(ang.item() - rr.mean_angle_error(rr.symmetric_orthogonalization(xd), rtd).item()) <= 2e-5 / max(1.0, n ** 0.5 / 8)
     # strided (B, 12) rows and an unaligned base: the wide TMA stage and the direct kernel give the same numbers
     wide = torch.zeros(n, 12, device="cuda")
     wide[:, :9] = xd
@@ -119,7 +120,7 @@ def test_c_abi_step_metrics_vector_and_caller_scratch(abi, rr):
         assert abs(mean32.item() - sums[0].item() / n) <= 1e-6 and abs(mean64.item() - sums[1].item() / n) <= 1e-12
         out.append(sums.clone())
     assert torch.allclose(out[0], out[1], rtol=1e-12, atol=0)
-    assert abs(out[0][1].item() / n - rr.mean_angle_error(rr.symmetric_orthogonalization(x), rt).item()) <= 1e-9
+    assert abs(out[0][1].item() / n - rr.mean_angle_error(rr.symmetric_orthogonalization(x), rt).item()) <= 1e-6
     # bad targets: the flag reaches both forms
     sums = torch.zeros(3, dtype=torch.float64, device="cuda")
     bad = (3.0 * torch.eye(3, device="cuda")).repeat(n, 1, 1).reshape(n, 9).contiguous()

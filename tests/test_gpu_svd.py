@@ -395,7 +395,10 @@ def test_registered_ops_trace_under_torch_compile(rr):
     xc = x.clone().requires_grad_(True)
     lc = torch.compile(step, backend="aot_eager", fullgraph=True)(xc, rt)
     lc.backward()
-    assert abs(float(le.detach()) - float(lc.detach())) <= 1e-6 and torch.equal(xe.grad, xc.grad)
+    # eager: loss_frobenius recognises the svd_orth output and runs the single-pass step; traced: the two registered ops
+    # (svd_orth + frobenius_mean with their own backward kernels).  Same mathematics, different kernels.
+    assert abs(float(le.detach()) - float(lc.detach())) <= 1e-6
+    assert (xe.grad - xc.grad).abs().max().item() <= 2e-6 * xe.grad.abs().max().item()
 
 
 @pytest.mark.parametrize("n", [1, 2, 3, 512, 1001, 70001])

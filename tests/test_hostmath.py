@@ -262,3 +262,34 @@ def test_expmap_with_other_clamp_bounds_vs_golden(hm, golden):
         dv = hostmath.call(hm, "hm_expmap_eps_bwd", v, z["exp_w"].reshape(-1, 9), e, (len(v), 3))
         scale = np.abs(z[f"exp_g_{tag}"]).max(1)
         assert (np.abs(dv - z[f"exp_g_{tag}"]).max(1) / np.maximum(scale, 1.0)).max() <= 2e-5
+
+
+def test_fused_sum_angle_forms_vs_oracle(hm):
+    """The angle the fused-mean kernels add up: (a) float64 trace + float32 arcsine tail, (b) error-free float32 trace
+    (big-accumulator FMA + recovered rounding errors) + the same tail, two lanes at once.  Against the oracle's float64
+    angle_error on the same fp32 matrices: <= 2e-5 degrees per record everywhere - also for identical pairs, where a
+    float32 trace would be off by 0.03 degrees - and the error-free trace equals the float64 one to 2e-11."""
+    import ctypes
+    g = torch.Generator().manual_seed(4)
+    n = 40000
+    r1 = O.symmetric_orthogonalization(torch.randn(n, 9, generator=g).double()).float()
+    r2 = O.symmetric_orthogonalization(torch.randn(n, 9, generator=g).double()).float()
+    r2[:2000] = r1[:2000]                                                  # zero angle: the reference's acos floor
+    small = O.so3_exp_map(1e-3 * torch.randn(2000, 3, generator=g).double())
+    r2[2000:4000] = torch.bmm(r1[2000:4000].double(), small).float()       # ~0.06 degree apart
+    flip = torch.diag(torch.tensor([1.0, -1.0, -1.0]))
+    r2[4000:6000] = torch.matmul(r1[4000:6000], flip)                      # 180 degrees
+    a, b = np.ascontiguousarray(r1.reshape(-1, 9).numpy()), np.ascontiguousarray(r2.reshape(-1, 9).numpy())
+    ref = O.angle_error(r1, r2).numpy()
+    fp, dp, ip = ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_int)
+    deg, flag = np.empty(n), np.empty(n, np.int32)
+    hm.hm_angle_sum_term(a.ctypes.data_as(fp), b.ctypes.data_as(fp), deg.ctypes.data_as(dp), flag.ctypes.data_as(ip),
+                         ctypes.c_long(n))
+    assert np.abs(deg - ref).max() <= 2e-5 and not flag.any()
+    deg2, pair = np.empty(n), np.empty((n, 2), np.float32)
+    hm.hm_angle_split_x2(a.ctypes.data_as(fp), b.ctypes.data_as(fp), deg2.ctypes.data_as(dp), pair.ctypes.data_as(fp),
+                         ctypes.c_long(n))
+    tr = (r1.double().reshape(n, 9) * r2.double().reshape(n, 9)).sum(1).numpy()
+    assert np.abs(pair[:, 0].astype(np.float64) + pair[:, 1].astype(np.float64) - (tr - 1.0)).max() <= 2e-11
+    assert np.abs(deg2 - ref).max() <= 2e-5
+    assert abs(deg2.mean() - ref.mean()) <= 1e-6 and abs(deg.mean() - ref.mean()) <= 1e-6
