@@ -369,6 +369,22 @@ PE_DEV void trace_minus_one_split(const T* r, const T* m, T& ahi, T& lo) {
     }
     ahi = t_add(acc, t_set(z, -97.0f));
 }
+// one matrix pair per thread (the one-record-per-thread kernels): the nine products ride in the two halves of packed
+// registers (elements 0-4 and 5-8), two accumulators, merged exactly at the end
+PE_DEV void trace_minus_one_split_scalar(const float* r, const float* m, float& ahi, float& lo) {
+    const F2 minus1{-1.0f, -1.0f};
+    F2 acc{96.0f, 96.0f}, l{0.0f, 0.0f};
+#pragma unroll
+    for (int i = 0; i < 5; ++i) {
+        const F2 a{r[i], i + 5 < 9 ? r[i + 5] : 0.0f}, b{m[i], i + 5 < 9 ? m[i + 5] : 0.0f};
+        const F2 an = f2_fma(a, b, acc);
+        const F2 dl = f2_fma(an, minus1, acc);
+        l = t_add(l, f2_fma(a, b, dl));
+        acc = an;
+    }
+    ahi = (acc.x - 96.0f) + (acc.y - 97.0f);  // both on the 2^-17 grid, |sum| < 16: exact
+    lo = l.x + l.y;
+}
 // t = (1 - |cos|)/2 from that pair (exact up to the final rounding) and the sign of the cosine
 template <class T, class M>
 PE_DEV T half_versine_from_split(T ahi, T lo, M& neg, T& a32) {

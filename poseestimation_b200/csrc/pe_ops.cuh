@@ -507,7 +507,15 @@ __device__ __forceinline__ void metric_accumulate(const float* r, const float* r
         float c = 0.5f * (dot9(r, rt) - 1.0f);
         red[0] += (double)acosf(fminf(fmaxf(c, ex.lo), ex.hi));
     } else {
+#if PE_STEP_ANGLE == 2
+        // error-free float32 trace: the float64 one costs 18 conversions per record, and those saturate the XU pipe
+        // (ncu r2c: quat / euler + angle_error at 66 % / 59 % XU, FMA pipe at 24 %)
+        float ahi, lo;
+        trace_minus_one_split_scalar(r, rt, ahi, lo);
+        angle_sum_from_split<float>(ahi, lo, red[0], flag, true, false);
+#else
         red[0] += angle_deg_sum_term(dot9_f64(r, rt), flag);
+#endif
     }
 }
 #define PE_MAP_METRIC(Tag, W, FWD, LABEL)                                                                     \

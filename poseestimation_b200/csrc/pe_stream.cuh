@@ -207,16 +207,25 @@ struct PairSrc {
     __device__ __forceinline__ void load(F2* dst) const { lds_pair<W>(s, t, stride, dst); }
 };
 
-// the same for a wide in[0]: 12-word rows in the stage, the first nine are the matrix
+// the same for a wide in[0]: 12-word rows in the stage, the first nine are the matrix.  Each row is read as three
+// 128-bit loads (conflict-free at a 12-word stride).  The third one is spelled in PTX: only its first word is used, and
+// the compiler otherwise narrows it to a 32-bit LDS, which at this stride is a 4-way bank conflict (ncu source page of
+// r2c: 786 432 excessive wavefronts per launch on exactly those two instructions).
+__device__ __forceinline__ float lds128_first(const float* p) {
+    float x, y, z, w;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(x), "=f"(y), "=f"(z), "=f"(w) : "r"(smem_u32(p)) : "memory");
+    return x;
+}
 struct PairSrcWide {
     const float* s;
     int t, stride;
     __device__ __forceinline__ void load(F2* dst) const {
-        float a[kWideRow], b[kWideRow];
-        lds_record<kWideRow>(s, t, a);
-        lds_record<kWideRow>(s, t + stride, b);
+        float a[8], b[8];
+        lds_record<8>(s + 4 * t, t, a);               // words 0..7 of row t (row stride 12 = 8 + 4)
+        lds_record<8>(s + 4 * (t + stride), t + stride, b);
 #pragma unroll
-        for (int i = 0; i < 9; ++i) dst[i] = F2{a[i], b[i]};
+        for (int i = 0; i < 8; ++i) dst[i] = F2{a[i], b[i]};
+        dst[8] = F2{lds128_first(s + kWideRow * t + 8), lds128_first(s + kWideRow * (t + stride) + 8)};
     }
 };
 

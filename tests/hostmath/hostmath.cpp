@@ -35,6 +35,16 @@ void hm_angle_deg(const float* a, const float* b, double* deg, int* flag, long n
 void hm_angle_sum_term(const float* a, const float* b, double* deg, int* flag, long n) {
     LOOP { int f = 0; deg[i] = pe::angle_deg_sum_term(pe::dot9_f64(a + 9 * i, b + 9 * i), f); flag[i] = f; }
 }
+void hm_angle_split_scalar(const float* a, const float* b, double* deg, float* ahi_lo, long n) {
+    LOOP {
+        float ahi, lo, a32;
+        pe::trace_minus_one_split_scalar(a + 9 * i, b + 9 * i, ahi, lo);
+        bool neg;
+        float t = pe::half_versine_from_split(ahi, lo, neg, a32);
+        deg[i] = pe::angle_deg_tail32_t(t, neg);
+        ahi_lo[2 * i] = ahi; ahi_lo[2 * i + 1] = lo;
+    }
+}
 void hm_angle_split_x2(const float* a, const float* b, double* deg, float* ahi_lo, long n) {
     long h = n / 2;
     for (long i = 0; i < h; ++i) {

@@ -364,6 +364,54 @@ def test_many_streams_and_threads_share_nothing(abi, rr):
         assert torch.equal(gw, gg) and abs(lw.item() - lg.item()) <= 1e-6
 
 
+def test_repeated_launches_are_bitwise_stable(abi, rr):
+    """compute-sanitizer is closed on the GPU pool (profiles/r2_sanitizer_refusal.txt), so this is the race detector for
+    the shared-memory rings and the tile hand-over: 200 launches of every ring kernel family on ONE input - small grid
+    per SM count, many tiles per CTA, ragged tail - must reproduce the first launch's per-record output bit for bit
+    (a record read before its bulk copy landed, or overwritten before its bulk store left, flips bits), and the sums to
+    float64 round-off."""
+    lib, check = abi.lib, abi.check
+    st = torch.cuda.current_stream().cuda_stream
+    n = (1 << 20) + 77
+    g = torch.Generator(device="cuda").manual_seed(9)
+    x = torch.randn(n, 9, device="cuda", generator=g)
+    wide = torch.randn(n, 12, device="cuda", generator=g)
+    up = torch.randn(n, 9, device="cuda", generator=g)
+    rt = rr.symmetric_orthogonalization(torch.randn(n, 9, device="cuda", generator=g)).reshape(n, 9)
+    x6 = torch.randn(n, 6, device="cuda", generator=g)
+    P = lambda t: t.data_ptr()
+    out = torch.empty(n, 9, device="cuda")
+    out6 = torch.empty(n, 6, device="cuda")
+    sums = torch.zeros(3, dtype=torch.float64, device="cuda")
+    deg = torch.empty(n, dtype=torch.float64, device="cuda")
+    flag = torch.zeros(1, dtype=torch.int32, device="cuda")
+    cases = {
+        "svd_fwd": (lambda: lib.pe_svd_orth_fwd(P(x), 9, P(out), None, n, st), out),
+        "svd_fwd_wide": (lambda: lib.pe_svd_orth_fwd(P(wide), 12, P(out), None, n, st), out),
+        "svd_bwd": (lambda: lib.pe_svd_orth_bwd(P(x), 9, None, P(up), P(out), n, st), out),
+        "svd_bwd_wide": (lambda: lib.pe_svd_orth_bwd(P(wide), 12, None, P(up), P(out), n, st), out),
+        "step_metrics": (lambda: lib.pe_svd_orth_frobenius_step_metrics(P(x), 9, P(rt), 1.0 / n, P(out), P(sums), None,
+                                                                        None, None, None, n, st), out),
+        "step_metrics_wide": (lambda: lib.pe_svd_orth_frobenius_step_metrics(P(wide), 12, P(rt), 1.0 / n, P(out),
+                                                                             P(sums), None, None, None, None, n, st), out),
+        "ortho6d_fwd": (lambda: lib.pe_ortho6d_fwd(P(x6), 6, P(out), n, st), out),
+        "ortho6d_bwd": (lambda: lib.pe_ortho6d_bwd(P(x6), 6, P(up), P(out6), n, st), out6),
+        "angle_error": (lambda: lib.pe_angle_error_fwd(P(rt), P(rt.flip(0).contiguous()), P(deg), P(sums), P(flag), n, st),
+                        deg),
+    }
+    for name, (call, res) in cases.items():
+        check(call(), name)
+        first, first_sums = res.clone(), sums.clone()
+        bad = 0
+        for rep in range(200):
+            check(call(), name)
+            if rep % 20 == 19:
+                bad += int((res.view(torch.int32) != first.view(torch.int32)).sum()) if res.dtype == torch.float32 else \
+                    int((res.view(torch.int64) != first.view(torch.int64)).sum())
+                assert torch.allclose(sums, first_sums, rtol=1e-12, atol=0), name
+        assert bad == 0, f"{name}: {bad} words changed between launches on the same input"
+
+
 # ---------------------------------------------------------------------------------------------------------------------
 # wide TMA stage (12-word rows)
 @pytest.mark.parametrize("n", [512, 1024, 1537, 200000])

@@ -293,3 +293,9 @@ def test_fused_sum_angle_forms_vs_oracle(hm):
     assert np.abs(pair[:, 0].astype(np.float64) + pair[:, 1].astype(np.float64) - (tr - 1.0)).max() <= 2e-11
     assert np.abs(deg2 - ref).max() <= 2e-5
     assert abs(deg2.mean() - ref.mean()) <= 1e-6 and abs(deg.mean() - ref.mean()) <= 1e-6
+    # the one-record-per-thread form (elements 0-4 / 5-8 in the two halves of packed registers)
+    deg3, pair3 = np.empty(n), np.empty((n, 2), np.float32)
+    hm.hm_angle_split_scalar(a.ctypes.data_as(fp), b.ctypes.data_as(fp), deg3.ctypes.data_as(dp),
+                             pair3.ctypes.data_as(fp), ctypes.c_long(n))
+    assert np.abs(pair3[:, 0].astype(np.float64) + pair3[:, 1].astype(np.float64) - (tr - 1.0)).max() <= 2e-11
+    assert np.abs(deg3 - ref).max() <= 2e-5 and abs(deg3.mean() - ref.mean()) <= 1e-6
