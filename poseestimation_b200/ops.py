@@ -678,13 +678,14 @@ def _step_launch(x: Tensor, r_true: Tensor, with_angle: bool):
     loss = torch.empty((), dtype=torch.float32, device=dev)
     with torch.cuda.device(dev):
         if with_angle:
-            sums = torch.empty((4,), dtype=torch.float64, device=dev)      # [sum |.|_F, sum theta, flag, mean theta]
+            sums = torch.empty((3,), dtype=torch.float64, device=dev)      # [sum |.|_F, sum theta, flag]
+            angle = torch.empty((), dtype=torch.float64, device=dev)
             flag = torch.empty((1,), dtype=torch.int32, device=dev)
             check(lib.pe_svd_orth_frobenius_step_metrics(x.data_ptr(), stride, rt.data_ptr(), 1.0 / n, dx.data_ptr(),
-                                                         sums.data_ptr(), loss.data_ptr(), sums.data_ptr() + 24,
+                                                         sums.data_ptr(), loss.data_ptr(), angle.data_ptr(),
                                                          flag.data_ptr(), None, n, _stream()),
                   "pe_svd_orth_frobenius_step_metrics")
-            return loss, sums[3], flag, dx
+            return loss, angle, flag, dx
         s = torch.empty((1,), dtype=torch.float64, device=dev)
         check(lib.pe_svd_orth_frobenius_step_mean(x.data_ptr(), stride, rt.data_ptr(), 1.0 / n, dx.data_ptr(),
                                                   s.data_ptr(), loss.data_ptr(), n, _stream()),
@@ -779,18 +780,19 @@ class _FusedStep(torch.autograd.Function):
     """svd_frobenius_loss(x, R_true[, with_angle]): loss (and mean angle error + its range flag) of the step."""
 
     @staticmethod
-    def forward(ctx, x, r_true, with_angle):
-        loss, angle, flag, dx = _step_launch(x, r_true, with_angle)
+    def forward(ctx, x, r_true, metric):
+        # `metric`: None, or a list that receives (mean angle, flag) - they are not differentiable and a node with one
+        # output is ~15 us cheaper per call than one with three
+        loss, angle, flag, dx = _step_launch(x, r_true, metric is not None)
         ctx.dx = dx
         ctx.save_for_backward(x, r_true)
-        if with_angle:
-            ctx.mark_non_differentiable(angle, flag)
-            return loss, angle, flag
+        if metric is not None:
+            metric.extend((angle, flag))
         return loss
 
     @staticmethod
     @_once
-    def backward(ctx, g_loss, *_):
+    def backward(ctx, g_loss):
         dx, ctx.dx = ctx.dx, None
         if dx is None:                               # second traversal: 108 B/matrix recompute kernel
             x, rt = ctx.saved_tensors
@@ -805,7 +807,11 @@ def fused_step_loss(x: Tensor, r_true: Tensor, with_angle: bool = False):
     eager = (not torch.compiler.is_compiling() and type(x) in (Tensor, torch.nn.Parameter) and x.is_cuda
              and type(r_true) in (Tensor, torch.nn.Parameter))
     if eager and torch.is_grad_enabled() and x.requires_grad:
-        return _FusedStep.apply(x, r_true, with_angle)
+        if not with_angle:
+            return _FusedStep.apply(x, r_true, None)
+        metric: list = []
+        loss = _FusedStep.apply(x, r_true, metric)
+        return loss, metric[0], metric[1]
     if with_angle:
         loss, angle, flag, _ = svd_orth_frobenius_step_metrics(x, r_true)
         return loss, angle, flag

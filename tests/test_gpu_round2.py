@@ -385,6 +385,7 @@ def test_repeated_launches_are_bitwise_stable(abi, rr):
     sums = torch.zeros(3, dtype=torch.float64, device="cuda")
     deg = torch.empty(n, dtype=torch.float64, device="cuda")
     flag = torch.zeros(1, dtype=torch.int32, device="cuda")
+    rt2 = rt.flip(0).contiguous()
     cases = {
         "svd_fwd": (lambda: lib.pe_svd_orth_fwd(P(x), 9, P(out), None, n, st), out),
         "svd_fwd_wide": (lambda: lib.pe_svd_orth_fwd(P(wide), 12, P(out), None, n, st), out),
@@ -396,8 +397,7 @@ def test_repeated_launches_are_bitwise_stable(abi, rr):
                                                                              P(sums), None, None, None, None, n, st), out),
         "ortho6d_fwd": (lambda: lib.pe_ortho6d_fwd(P(x6), 6, P(out), n, st), out),
         "ortho6d_bwd": (lambda: lib.pe_ortho6d_bwd(P(x6), 6, P(up), P(out6), n, st), out6),
-        "angle_error": (lambda: lib.pe_angle_error_fwd(P(rt), P(rt.flip(0).contiguous()), P(deg), P(sums), P(flag), n, st),
-                        deg),
+        "angle_error": (lambda: lib.pe_angle_error_fwd(P(rt), P(rt2), P(deg), P(sums), P(flag), n, st), deg),
     }
     for name, (call, res) in cases.items():
         check(call(), name)
