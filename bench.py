@@ -256,7 +256,9 @@ class Ctx:
             sys.stdout.flush()
             self.stdout_fd = os.dup(1)
             os.dup2(2, 1)
-            dist.init_process_group("nccl", device_id=self.dev)
+            import datetime
+            # a mismatch in the collective sequence must fail in two minutes, not in NCCL's default ten
+            dist.init_process_group("nccl", device_id=self.dev, timeout=datetime.timedelta(seconds=120))
         from poseestimation_b200 import _lib, launch_count
         import poseestimation_b200.rotation_representation as rr
         self.lib, self.check, self.launch_count, self.rr = _lib.lib, _lib.check, launch_count, rr
@@ -356,11 +358,12 @@ class StepLoop:
         if sampler is not None:
             sampler.start()
             time.sleep(0.25)
-            # the sampler's start-up left the GPU idle for a quarter of a second: three more untimed steps, so that the
-            # timed region starts on a device that is awake, then the barrier + synchronize the contract asks for
-            for i in range(3):
-                self.step(i)
-            self.drain()
+        # the sampler's start-up left rank 0's GPU idle for a quarter of a second: three more untimed steps ON EVERY RANK
+        # (each step carries a collective), so that the timed region starts on devices that are awake, then the barrier +
+        # synchronize the contract asks for
+        for i in range(3):
+            self.step(i)
+        self.drain()
         ev = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(steps)]
         launches0 = c.launch_count()
         c.sync_all()
