@@ -65,7 +65,8 @@ def parse_args():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
-    ap.add_argument("--n", type=int, default=N_DEFAULT, help="matrices per GPU")
+    ap.add_argument("--n", "--per-gpu", dest="n", type=int, default=N_DEFAULT,
+                    help="matrices per GPU (under torchrun spell it --per-gpu: its own parser rejects the prefix --n)")
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--cpu-sample", type=int, default=1 << 18, help="matrices per step of --impl reference")
     ap.add_argument("--no-cpu-baseline", action="store_true")
