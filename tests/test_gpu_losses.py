@@ -118,8 +118,11 @@ def test_kabsch_vs_oracle(rr, b, npts):
     r, t = rr.kabsch(p.cuda(), q.cuda())
     r_ref, t_ref = O.kabsch(p, q)
     if npts >= 4:
-        assert (r.cpu().double() - r_ref).abs().max() <= 2e-5
-        assert (t.cpu().double() - t_ref).abs().max() <= 2e-5
+        # north_star's 1e-5 wherever the cloud determines the rotation well (N >= 64 points); a handful of noisy points
+        # leaves H = sum (q - qbar)(p - pbar)^T badly conditioned and every fp32 method loses digits there
+        tol = 1e-5 if npts >= 64 else 2e-5
+        assert (r.cpu().double() - r_ref).abs().max() <= tol
+        assert (t.cpu().double() - t_ref).abs().max() <= 2e-5     # |t| ~ 1-3: its own fp32 rounding plus |pbar| * err(R)
     rd = r.cpu().double()
     assert (rd @ rd.transpose(1, 2) - torch.eye(3, dtype=torch.float64)).abs().max() <= 1e-5
     assert (torch.linalg.det(rd) - 1).abs().max() <= 1e-5
@@ -134,7 +137,7 @@ def test_kabsch_full_size_round_trip(rr):
     rot = O.sample_rotations_axis_angle(b, g).float().cuda()
     q = torch.bmm(p, rot.transpose(1, 2))
     r, t = rr.kabsch(p, q)
-    assert float((r - rot).abs().max()) <= 2e-5
-    assert float(t.abs().max()) <= 2e-5
+    assert float((r - rot).abs().max()) <= 1e-5
+    assert float(t.abs().max()) <= 1e-5
     # float64 acos of a trace built from fp32 entries has a ~0.03 degree floor near zero angle (sqrt(2 * 3e-7) rad)
     assert float(rr.mean_angle_error(r, rot).item()) <= 0.05

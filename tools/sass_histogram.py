@@ -39,15 +39,15 @@ def main():
         if m and cur is not None:
             cur.append((int(m.group(1), 16), m.group(2).strip()))
     names = demangle(list(kernels))
-    want = [w for w in args.kernels.split(",") if w]
+    want = [w for w in args.kernels.split(";") if w]      # ";"-separated substrings (kernel names contain commas)
     arch = re.findall(r"arch = (sm_\w+)", sass)
     print("# SASS instruction histogram of `poseestimation_b200/libpe_rotation.so`\n")
     print(f"`cuobjdump -sass` of the in-tree build; architectures in the fat binary: {sorted(set(arch))}. "
-          "Counts are STATIC instructions per kernel (not executed counts). `hot` = instructions before the first "
-          "`EXIT`-terminated tail / out-of-line block is not separable statically, so for the SVD kernels the "
-          "scalar-vs-packed split is given instead: the packed FFMA2/FMUL2/FADD2 are the two-matrix hot path, the "
-          "scalar FFMA/FMUL are the per-lane fix-ups (lane_get/lane_put selects, reciprocals) plus the scalar "
-          "fallback `svd_orth_fast` for degenerate lanes, which is inlined twice (once per lane).\n")
+          "Counts are STATIC instructions per kernel (not executed counts).  For the SVD kernels the packed "
+          "FFMA2 / FMUL2 / FADD2 are the two-matrices-per-thread hot path; the several hundred scalar FFMA / FMUL are "
+          "the scalar routine `svd_orth_fast` for degenerate lanes (rank <= 1, zero, non-finite), inlined once per lane "
+          "behind a never-taken branch: the EXECUTED mix (ncu source page, profiles/r2c_dynamic_instruction_mix.md) has "
+          "2 scalar FMUL and no scalar FFMA per pair of matrices.\n")
     print("| kernel | total | " + " | ".join(COLS) + " |")
     print("|---|---|" + "---|" * len(COLS))
     tot = collections.Counter()
