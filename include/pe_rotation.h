@@ -93,6 +93,19 @@ int pe_frobenius_mean_fwd(const float* a, const float* b, double* sum, float* me
 int pe_frobenius_bwd(const float* a, const float* b, const float* gout, float inv_n, float* da, float* db,
                      int64_t n, void* stream);
 
+/* ---- pe_frobenius_fwd without any allocation ---------------------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).  Same inputs, output and
+ * return convention as pe_frobenius_fwd; *sum agrees with it to float64 round-off (same float32 terms, other order) and
+ * is bitwise reproducible from call to call.  Its scratch - one float64 partial per 256 records and a ticket word - is a
+ * file-scope static __device__ array of 256 KB + 256 B that every GPU loading the library holds until the process exits;
+ * that is the limit: n <= PE_STATIC_MAX_RECORDS, larger n returns PE_ERR_BAD_ARG.  The call makes no cudaMalloc /
+ * cudaFree / allocating library call, and does not need pe_init.  ALL calls share the one array: calls that overlap on
+ * the GPU (two streams, two host threads) race on it - serialise them.  The first call on a device resolves the array's
+ * device address (cudaGetSymbolAddress); make one call outside a stream capture before capturing it. */
+#define PE_STATIC_MAX_RECORDS 8388608 /* 2^23 matrices = 32768 tiles of 256 */
+int pe_frobenius_fwd_static(const float* a, const float* b, double* sum, int64_t n, void* stream);
+
 /* ---- a6  compute_geodesic_distance_from_two_matrices    rotation_representation.py:209-227  (lo, hi = -1, 1)
  * ---- a8  geodesic(R1, R2, reduction)                    point_cloud/main.py:61-73   (lo, hi = -1+1e-7, 1-1e-7)
  * theta_b = acos(clamp((tr(m1_b m2_b^T) - 1)/2, lo, hi)) in radians.  theta (n floats) and sum are each

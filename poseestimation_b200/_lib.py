@@ -35,6 +35,7 @@ SIGNATURES = {
     "pe_expmap_eps_bwd": [_f, _i64, _f, _flt, _f, _i64, _f],
     "pe_frobenius_fwd": [_f, _f, _f, _i64, _f],
     "pe_frobenius_mean_fwd": [_f, _f, _f, _f, _i64, _f],
+    "pe_frobenius_fwd_static": [_f, _f, _f, _i64, _f],
     "pe_frobenius_bwd": [_f, _f, _f, _flt, _f, _f, _i64, _f],
     "pe_geodesic_fwd": [_f, _f, _flt, _flt, _f, _f, _i64, _f],
     "pe_geodesic_bwd": [_f, _f, _flt, _flt, _f, _int, _flt, _f, _f, _i64, _f],
