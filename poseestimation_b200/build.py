@@ -53,7 +53,46 @@ def build(force: bool = False, verbose: bool = False, out: str = OUT, defines: t
     return out
 
 
+TORCH_SRC = os.path.join(CSRC, "pe_torch.cpp")
+TORCH_OUT = os.path.join(HERE, "_pe_torch.so")
+
+
+def torch_ext_up_to_date() -> bool:
+    if not os.path.exists(TORCH_OUT) or not os.path.exists(OUT):
+        return False
+    t = os.path.getmtime(TORCH_OUT)
+    deps = [TORCH_SRC, os.path.join(CSRC, "..", "..", "include", "pe_rotation.h"), os.path.abspath(__file__)]
+    return all(os.path.getmtime(d) <= t for d in deps)
+
+
+def build_torch_ext(force: bool = False, verbose: bool = False) -> str:
+    """`_pe_torch.so`: the C++ autograd node of the training step (csrc/pe_torch.cpp; host code only - no kernels),
+    compiled with g++ against the installed torch and linked to libpe_rotation.so next to it."""
+    if not force and torch_ext_up_to_date():
+        return TORCH_OUT
+    import sysconfig
+    import torch
+    from torch.utils import cpp_extension as ce
+    cuda_home = os.environ.get("CUDA_HOME", "/usr/local/cuda")
+    inc = ce.include_paths() + [sysconfig.get_paths()["include"], os.path.join(cuda_home, "include")]
+    torch_lib = os.path.join(os.path.dirname(torch.__file__), "lib")
+    cxx = shutil.which("g++") or "g++"
+    cmd = [cxx, "-O2", "-std=c++17", "-fPIC", "-shared", "-fvisibility=hidden",
+           f"-D_GLIBCXX_USE_CXX11_ABI={int(torch._C._GLIBCXX_USE_CXX11_ABI)}", "-DTORCH_EXTENSION_NAME=_pe_torch",
+           "-DTORCH_API_INCLUDE_EXTENSION_H", *[f"-I{i}" for i in inc], TORCH_SRC, "-o", TORCH_OUT,
+           f"-L{HERE}", "-lpe_rotation", f"-L{torch_lib}", "-ltorch", "-ltorch_cpu", "-ltorch_python", "-lc10", "-lc10_cuda",
+           "-Wl,-rpath,$ORIGIN", f"-Wl,-rpath,{torch_lib}"]
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if verbose or res.returncode != 0:
+        sys.stderr.write(res.stdout + res.stderr)
+    if res.returncode != 0:
+        raise RuntimeError("g++ failed building _pe_torch.so")
+    return TORCH_OUT
+
+
 if __name__ == "__main__":
     dest = sys.argv[sys.argv.index("-o") + 1] if "-o" in sys.argv else OUT
     print(build(force="-f" in sys.argv or "--force" in sys.argv, verbose="-v" in sys.argv, out=dest,
                 defines=tuple(a for a in sys.argv[1:] if a.startswith("-D"))))
+    if dest == OUT:
+        print(build_torch_ext(force="-f" in sys.argv or "--force" in sys.argv, verbose="-v" in sys.argv))

@@ -20,6 +20,15 @@ from ._lib import _initialised, check, init_device, lib
 
 NS = "pe_b200"
 
+# The C++ autograd node of the training step (csrc/pe_torch.cpp, built by build.py next to libpe_rotation.so): the same
+# C-ABI calls without Python frames in forward / backward.  Host-latency path only - when it has not been built the
+# Python node below (_FusedStep) runs the very same kernels; a library that exists but does not load is an error.
+import os as _os
+_C = None
+if _os.path.exists(_os.path.join(_os.path.dirname(_os.path.abspath(__file__)), "_pe_torch.so")) \
+        and _os.environ.get("PE_NO_CPP_NODE") != "1":
+    from . import _pe_torch as _C  # noqa: E402
+
 
 # ---------------------------------------------------------------------------------------------------------------------
 # Eager fast path.  A call of a ``torch.library.custom_op`` costs 30-40 us of Python dispatch, and ~150 us with its
@@ -807,6 +816,9 @@ def fused_step_loss(x: Tensor, r_true: Tensor, with_angle: bool = False):
     eager = (not torch.compiler.is_compiling() and type(x) in (Tensor, torch.nn.Parameter) and x.is_cuda
              and type(r_true) in (Tensor, torch.nn.Parameter))
     if eager and torch.is_grad_enabled() and x.requires_grad:
+        if _C is not None and x.dim() == 2 and x.shape[1] == 9 and x.dtype == torch.float32 and r_true.is_cuda:
+            out = _C.fused_step_loss(x, r_true, with_angle)
+            return (out[0], out[1], out[2]) if with_angle else out[0]
         if not with_angle:
             return _FusedStep.apply(x, r_true, None)
         metric: list = []

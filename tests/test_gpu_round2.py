@@ -258,6 +258,52 @@ def test_star_import_like_the_reference_scripts():
     assert "star-import ok _FusedFromSvdOutputBackward" in res.stdout
 
 
+def test_cpp_autograd_node_equals_the_python_node(rr, ops):
+    """csrc/pe_torch.cpp (the host-latency route of svd_frobenius_loss) against ops._FusedStep: the same C-ABI calls, so
+    loss, mean angle, flag and gradient are bit-identical - dense, on the (B, 12) view, with an upstream gradient other
+    than 1, over a second traversal (retain_graph), and for an empty batch."""
+    if ops._C is None:
+        pytest.skip("_pe_torch.so not built")
+    g = torch.Generator(device="cuda").manual_seed(21)
+    n = 3001
+    wide = torch.randn(n, 12, device="cuda", generator=g)
+    rt = rr.symmetric_orthogonalization(torch.randn(n, 9, device="cuda", generator=g))
+    for strided in (False, True):
+        for with_angle in (False, True):
+            # leaves: a dense (n, 9) tensor, or the (n, 12) output whose [:, :9] view is read in place (wide TMA stage)
+            lc, lp = ((wide if strided else wide[:, :9].contiguous()).detach().clone().requires_grad_(True) for _ in range(2))
+            xc, xp = (lc[:, :9], lp[:, :9]) if strided else (lc, lp)
+            assert xc.stride(0) == (12 if strided else 9)
+            out_c = ops._C.fused_step_loss(xc, rt, with_angle)
+            metric = [] if with_angle else None
+            loss_p = ops._FusedStep.apply(xp, rt, metric)
+            assert out_c[0].item() == loss_p.item() and out_c[0].dtype == torch.float32 and out_c[0].dim() == 0
+            if with_angle:
+                assert out_c[1].item() == metric[0].item() and out_c[1].dtype == torch.float64
+                assert int(out_c[2].item()) == int(metric[1].item()) == 0 and not out_c[1].requires_grad
+            (out_c[0] * 2.5).backward(retain_graph=True)
+            (loss_p * 2.5).backward(retain_graph=True)
+            assert torch.equal(lc.grad, lp.grad) and lc.grad.abs().max().item() > 0
+            out_c[0].backward()                              # second traversal: the recompute kernel on both routes
+            loss_p.backward()
+            assert torch.equal(lc.grad, lp.grad)
+            with pytest.raises(RuntimeError):
+                out_c[0].backward()
+    e = torch.zeros(0, 9, device="cuda", requires_grad=True)
+    out = ops._C.fused_step_loss(e, torch.zeros(0, 3, 3, device="cuda"), True)
+    assert torch.isnan(out[0]) and torch.isnan(out[1])
+    out[0].backward()
+    assert e.grad.shape == (0, 9)
+    with pytest.raises(RuntimeError, match="batch mismatch"):
+        ops._C.fused_step_loss(wide[:, :9].contiguous().requires_grad_(True), rt[:5], False)
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        ops._C.fused_step_loss(torch.randn(4, 9, requires_grad=True), rt[:4], False)
+    # and it is the route the public function takes
+    x = wide[:, :9].contiguous().requires_grad_(True)
+    loss = rr.svd_frobenius_loss(x, rt)
+    assert type(loss.grad_fn).__name__ == "CppFunction" and "FusedStep" in repr(loss)
+
+
 # ---------------------------------------------------------------------------------------------------------------------
 # launch slots: streams, graphs
 def test_graph_replay_next_to_eager_launches_on_another_stream(abi, rr):

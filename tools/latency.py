@@ -106,6 +106,19 @@ def main():
             loss.backward()
 
         row["fused_step_with_mean_angle_us"] = timed(step_with_metric, args.reps)
+
+        def python_node():                  # the Python autograd.Function the C++ node (csrc/pe_torch.cpp) replaces
+            x.grad = None
+            ops._FusedStep.apply(x, rt, None).backward()
+
+        row["fused_step_python_node_us"] = timed(python_node, args.reps)
+        row["cpp_node"] = float(ops._C is not None)
+
+        def floor():                        # PyTorch's own floor: one CUDA op with autograd
+            x.grad = None
+            (x * 2).sum().backward()
+
+        row["torch_one_op_autograd_floor_us"] = timed(floor, args.reps)
         res[str(b)] = {k: round(v, 2) for k, v in row.items()}
     # Kabsch at the reference's cloud batch (point_cloud/main.py:257: 128 clouds x 1024 points) and smaller: one warp per
     # pair, so 128 pairs occupy 16 of 148 SMs - is a call launch-bound (then nothing is to gain) or stream-bound?
