@@ -14,8 +14,11 @@
 #include <c10/cuda/CUDAGuard.h>
 #include <c10/cuda/CUDAStream.h>
 
+#include <torch/custom_class.h>
+
 #include <atomic>
 #include <limits>
+#include <mutex>
 
 #include "../../include/pe_rotation.h"
 
@@ -138,6 +141,165 @@ torch::autograd::variable_list FusedStep::backward(torch::autograd::AutogradCont
     return {dx, at::Tensor(), at::Tensor()};
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// The UNCHANGED call surface in C++:  R = symmetric_orthogonalization(out);  loss = loss_frobenius(R, R_true)
+// (Comparison/main.py:59-62, UPNA/main.py:54-57, 3D-Pose/main.py:60,85-91).  Same scheme as ops.frobenius_of_svd_output:
+// loss_frobenius recognises an untouched output of the SvdOrth node, runs the single-pass step on that node's own input
+// and parks the gradient (for a unit upstream gradient) where the SvdOrth node's backward finds it; its own backward
+// hands R a zero-stride all-zero gradient, so gradients of other consumers of R still add up in autograd's buffer.
+
+// what the two nodes share: gradients parked by the loss node's backward for the SvdOrth node's backward
+struct Park : torch::CustomClassHolder {
+    std::vector<std::pair<at::Tensor, at::Tensor>> pending;  // (d loss / d x for upstream 1, upstream gradient)
+};
+
+at::Tensor zero_scalar(const at::Device& dev) {
+    static std::mutex mu;
+    static at::Tensor z[64];
+    std::lock_guard<std::mutex> lk(mu);
+    const int i = dev.index();
+    TORCH_CHECK(i >= 0 && i < 64, "device index out of range");
+    if (!z[i].defined()) z[i] = at::zeros({}, at::TensorOptions().dtype(at::kFloat).device(dev));
+    return z[i];
+}
+bool is_zero_marker(const at::Tensor& g) {
+    if (!g.defined() || !g.is_cuda() || g.scalar_type() != at::kFloat) return false;
+    for (auto s : g.strides())
+        if (s != 0) return false;
+    return g.data_ptr() == zero_scalar(g.device()).data_ptr();
+}
+at::Tensor scalar32(at::Tensor g) {
+    if (g.scalar_type() != at::kFloat || g.numel() != 1 || !g.is_contiguous()) g = g.to(at::kFloat).reshape({1}).contiguous();
+    return g;
+}
+
+struct SvdOrth : public torch::autograd::Function<SvdOrth> {
+    static at::Tensor forward(torch::autograd::AutogradContext* ctx, const at::Tensor& x_in) {
+        int64_t stride = 9;
+        at::Tensor x = records9(x_in, &stride);
+        const int64_t n = x.size(0);
+        const c10::cuda::CUDAGuard guard(x.device());
+        ensure_init(x.device().index());
+        at::Tensor r = at::empty({n, 3, 3}, x.options().requires_grad(false));
+        void* st = c10::cuda::getCurrentCUDAStream(x.device().index()).stream();
+        check_rc(pe_svd_orth_fwd(x.data_ptr<float>(), stride, r.data_ptr<float>(), nullptr, n, st), "pe_svd_orth_fwd");
+        ctx->saved_data["stride"] = stride;
+        ctx->saved_data["park"] = c10::IValue::make_capsule(c10::make_intrusive<Park>());
+        ctx->save_for_backward({x});
+        return r;
+    }
+    static torch::autograd::variable_list backward(torch::autograd::AutogradContext* ctx,
+                                                   torch::autograd::variable_list grads) {
+        auto saved = ctx->get_saved_variables();
+        const at::Tensor& x = saved[0];
+        const int64_t n = x.size(0);
+        const int64_t stride = ctx->saved_data["stride"].toInt();
+        const c10::cuda::CUDAGuard guard(x.device());
+        void* st = c10::cuda::getCurrentCUDAStream(x.device().index()).stream();
+        auto park = c10::static_intrusive_pointer_cast<Park>(ctx->saved_data["park"].toCapsule());
+        at::Tensor total;
+        const at::Tensor& g = grads[0];
+        // `g` is the zero marker unless R had other consumers: their gradients go through the recompute pullback
+        if (g.defined() && !(is_zero_marker(g) && !park->pending.empty())) {
+            TORCH_CHECK(g.numel() == 9 * n, "batch mismatch: ", n, " records but ", g.numel() / 9, " upstream gradients");
+            at::Tensor gc = g.scalar_type() == at::kFloat ? g.contiguous() : g.to(at::kFloat).contiguous();
+            total = at::empty({n, 9}, x.options().requires_grad(false));
+            if (n) check_rc(pe_svd_orth_bwd(x.data_ptr<float>(), stride, nullptr, gc.data_ptr<float>(), total.data_ptr<float>(), n, st),
+                            "pe_svd_orth_bwd");
+        }
+        for (auto& p : park->pending) {
+            at::Tensor gl = scalar32(p.second);
+            if (n) check_rc(pe_scale_by_scalar_inplace(p.first.data_ptr<float>(), gl.data_ptr<float>(), 9 * n, st),
+                            "pe_scale_by_scalar_inplace");  // nothing on the device when the upstream gradient is 1
+            if (total.defined()) total.add_(p.first); else total = p.first;
+        }
+        park->pending.clear();
+        if (!total.defined()) total = at::zeros({n, 9}, x.options().requires_grad(false));
+        return {total};
+    }
+};
+
+struct FusedFromSvdOutput : public torch::autograd::Function<FusedFromSvdOutput> {
+    static at::Tensor forward(torch::autograd::AutogradContext* ctx, const at::Tensor& r, const at::Tensor& r_true,
+                              const at::Tensor& x, int64_t stride, c10::IValue park) {
+        const int64_t n = x.size(0);
+        at::Tensor rt = matrices9(r_true, n);
+        const c10::cuda::CUDAGuard guard(x.device());
+        auto f32 = x.options().requires_grad(false);
+        at::Tensor dx = at::empty({n, 9}, f32), loss;
+        if (n == 0) {
+            loss = at::full({}, std::numeric_limits<double>::quiet_NaN(), f32);
+        } else {
+            void* st = c10::cuda::getCurrentCUDAStream(x.device().index()).stream();
+            loss = at::empty({}, f32);
+            at::Tensor sum = at::empty({1}, f32.dtype(at::kDouble));
+            check_rc(pe_svd_orth_frobenius_step_mean(x.data_ptr<float>(), stride, rt.data_ptr<float>(), 1.0f / (float)n,
+                                                     dx.data_ptr<float>(), sum.data_ptr<double>(), loss.data_ptr<float>(), n, st),
+                     "pe_svd_orth_frobenius_step_mean");
+        }
+        ctx->saved_data["dx"] = dx;
+        ctx->saved_data["park"] = park;
+        ctx->save_for_backward({r, rt});
+        return loss;
+    }
+    static torch::autograd::variable_list backward(torch::autograd::AutogradContext* ctx,
+                                                   torch::autograd::variable_list grads) {
+        TORCH_CHECK(grads[0].defined(), "loss_frobenius: undefined upstream gradient");
+        auto saved = ctx->get_saved_variables();
+        const at::Tensor& r = saved[0];
+        const at::Tensor& rt = saved[1];
+        const int64_t n = rt.size(0);
+        at::Tensor dx = ctx->saved_data["dx"].toTensor();
+        if (dx.defined()) {
+            ctx->saved_data["dx"] = at::Tensor();
+            auto park = c10::static_intrusive_pointer_cast<Park>(ctx->saved_data["park"].toCapsule());
+            park->pending.emplace_back(dx, grads[0]);
+            return {zero_scalar(r.device()).expand(r.sizes()), at::Tensor(), at::Tensor(), at::Tensor(), at::Tensor()};
+        }
+        // second traversal (retain_graph): the unfused route, a dense gradient for R
+        const c10::cuda::CUDAGuard guard(r.device());
+        void* st = c10::cuda::getCurrentCUDAStream(r.device().index()).stream();
+        at::Tensor gl = scalar32(grads[0]);
+        at::Tensor rc = r.contiguous();
+        at::Tensor da = at::empty(r.sizes(), r.options().requires_grad(false));
+        if (n) check_rc(pe_frobenius_bwd(rc.data_ptr<float>(), rt.data_ptr<float>(), gl.data_ptr<float>(), 1.0f / (float)n,
+                                         da.data_ptr<float>(), nullptr, n, st), "pe_frobenius_bwd");
+        return {da, at::Tensor(), at::Tensor(), at::Tensor(), at::Tensor()};
+    }
+};
+
+at::Tensor svd_orth(const at::Tensor& x) { return SvdOrth::apply(x); }
+
+// loss_frobenius(a, b) through the single-pass step if one argument is an untouched output of the SvdOrth node and the
+// other a plain target of the same batch; nullopt otherwise (the caller then takes the generic op)
+c10::optional<at::Tensor> frobenius_of_svd_output(const at::Tensor& a, const at::Tensor& b) {
+    if (!at::GradMode::is_enabled()) return c10::nullopt;
+    const at::Tensor* pair[2][2] = {{&a, &b}, {&b, &a}};
+    for (auto& p : pair) {
+        const at::Tensor& r = *p[0];
+        const at::Tensor& other = *p[1];
+        if (!r.defined() || !r.requires_grad()) continue;
+        auto fn = r.grad_fn();
+        auto* node = dynamic_cast<torch::autograd::CppNode<SvdOrth>*>(fn.get());
+        if (!node || r.output_nr() != 0 || r._version() != 0 || r.retains_grad() || r.is_view() ||
+            !torch::autograd::impl::hooks(r).empty())
+            continue;
+        if (!other.defined() || other.requires_grad() || !other.is_cuda() || other.scalar_type() != at::kFloat ||
+            other.numel() != r.numel() || other.device() != r.device())
+            return c10::nullopt;
+        at::Tensor x;
+        try {
+            x = node->ctx_.get_saved_variables()[0];  // throws if x was modified in place or the graph was freed
+        } catch (const std::exception&) {
+            return c10::nullopt;
+        }
+        // x enters detached: the step only reads its storage; its gradient reaches it through the SvdOrth node
+        return FusedFromSvdOutput::apply(r, other, x.detach(), node->ctx_.saved_data["stride"].toInt(),
+                                         node->ctx_.saved_data["park"]);
+    }
+    return c10::nullopt;
+}
+
 std::vector<at::Tensor> fused_step_loss(const at::Tensor& x, const at::Tensor& r_true, bool with_angle) {
     return FusedStep::apply(x, r_true, with_angle);
 }
@@ -147,4 +309,8 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
     m.doc() = "C++ autograd node of the single-pass training step over libpe_rotation.so (host-latency path)";
     m.def("fused_step_loss", &fused_step_loss, "loss (and mean angle error, range flag) of the step; differentiable in x",
           py::arg("x"), py::arg("r_true"), py::arg("with_angle"));
+    m.def("svd_orth", &svd_orth, "symmetric_orthogonalization of (n, 9) records as a C++ autograd node", py::arg("x"));
+    m.def("frobenius_of_svd_output", &frobenius_of_svd_output,
+          "loss_frobenius(a, b) through the single-pass step when one argument is an untouched svd_orth output, else None",
+          py::arg("a"), py::arg("b"));
 }

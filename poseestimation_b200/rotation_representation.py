@@ -48,6 +48,9 @@ def symmetric_orthogonalization(x):
         rec = x                                   # possibly strided rows: no copy
     else:
         rec = x.reshape(-1, 9)                    # reference: x.view(-1, 3, 3)
+    if (_ops._C is not None and rec.requires_grad and type(rec) in (torch.Tensor, torch.nn.Parameter) and rec.is_cuda
+            and rec.dtype == torch.float32 and torch.is_grad_enabled() and not torch.compiler.is_compiling()):
+        return _ops._C.svd_orth(rec)              # C++ autograd node (csrc/pe_torch.cpp): same kernels, no Python frames
     r = _ops.svd_orth(rec)
     if r.requires_grad and not torch.compiler.is_compiling():
         _ops.tag_svd_output(r, rec)               # lets loss_frobenius(r, R_true) take the single-pass step kernel
@@ -206,7 +209,11 @@ def loss_frobenius(R_pred, R_true):
     and d loss/d x come from ONE kernel on that call's own input (``ops.frobenius_of_svd_output``): the unchanged two-call
     surface then costs 72 + 108 B/matrix instead of 360.  Same numbers as :func:`svd_frobenius_loss`."""
     if not torch.compiler.is_compiling():          # (a traced graph goes through the registered ops)
-        fused = _ops.frobenius_of_svd_output(R_pred, R_true)
+        if _ops._C is not None and type(R_pred) is torch.Tensor and type(R_true) is torch.Tensor:
+            fused = _ops._C.frobenius_of_svd_output(R_pred, R_true)     # outputs of the C++ svd_orth node
+            if fused is not None:
+                return fused
+        fused = _ops.frobenius_of_svd_output(R_pred, R_true)            # outputs of the Python svd_orth node
         if fused is not None:
             return fused
     return _ops.frobenius_mean(R_pred, R_true)

@@ -131,6 +131,23 @@ def test_c_abi_step_metrics_vector_and_caller_scratch(abi, rr):
 
 # ---------------------------------------------------------------------------------------------------------------------
 # the unchanged call surface: loss_frobenius(symmetric_orthogonalization(x), R)
+def _fused(loss):
+    """the loss came from the single-pass step: Python node `_FusedFromSvdOutputBackward` or C++ node `FusedFromSvdOutput`"""
+    return "FusedFromSvdOutput" in repr(loss)
+
+
+@pytest.fixture(params=["cpp_nodes", "python_nodes"])
+def route(request, ops, monkeypatch):
+    """the unchanged surface runs through C++ autograd nodes (csrc/pe_torch.cpp) when _pe_torch.so is built and through
+    the Python nodes of ops.py otherwise: every drop-in test runs on both"""
+    if request.param == "cpp_nodes":
+        if ops._C is None:
+            pytest.skip("_pe_torch.so not built")
+    else:
+        monkeypatch.setattr(ops, "_C", None)
+    return request.param
+
+
 def _dropin(rr, x, rt, swap=False):
     xd = x.clone().requires_grad_(True)
     r = rr.symmetric_orthogonalization(xd)
@@ -139,7 +156,7 @@ def _dropin(rr, x, rt, swap=False):
 
 
 @pytest.mark.parametrize("swap", [False, True])
-def test_dropin_route_is_the_single_pass_step(rr, abi, swap):
+def test_dropin_route_is_the_single_pass_step(rr, abi, swap, route):
     """Three launches (svd_orth fwd, step, the device-side no-op scaling) instead of four heavy ones, and the gradient is
     bit for bit that of svd_frobenius_loss.  UPNA/main.py:57 passes (R, out): both argument orders."""
     n = 5000
@@ -148,7 +165,7 @@ def test_dropin_route_is_the_single_pass_step(rr, abi, swap):
     torch.cuda.synchronize()
     before = abi.launch_count()
     xd, r, loss = _dropin(rr, x, rt, swap)
-    assert type(loss.grad_fn).__name__ == "_FusedFromSvdOutputBackward"
+    assert _fused(loss)
     loss.backward()
     assert abi.launch_count() - before == 3
     xe = x.clone().requires_grad_(True)
@@ -165,7 +182,7 @@ def test_dropin_route_is_the_single_pass_step(rr, abi, swap):
     assert rel[cond > 0.1].max() <= 1e-4
 
 
-def test_dropin_route_upstream_gradient_and_second_consumer(rr):
+def test_dropin_route_upstream_gradient_and_second_consumer(rr, route):
     """loss weighting (upstream != 1) and a second differentiable consumer of R: gradients add up exactly as on the
     unfused route."""
     n = 3001
@@ -188,7 +205,7 @@ def test_dropin_route_upstream_gradient_and_second_consumer(rr):
     assert (gf - gu).abs().max().item() <= 1e-6 * gu.abs().max().item() + 1e-9
 
 
-def test_dropin_route_retain_graph_and_fallbacks(rr, abi):
+def test_dropin_route_retain_graph_and_fallbacks(rr, abi, route):
     n = 2000
     x = torch.randn(n, 9, device="cuda")
     rt = rr.symmetric_orthogonalization(torch.randn(n, 9, device="cuda"))
@@ -204,7 +221,7 @@ def test_dropin_route_retain_graph_and_fallbacks(rr, abi):
     r = rr.symmetric_orthogonalization(xd)
     r.retain_grad()
     loss = rr.loss_frobenius(r, rt)
-    assert type(loss.grad_fn).__name__ != "_FusedFromSvdOutputBackward"
+    assert not _fused(loss)
     loss.backward()
     assert r.grad is not None and (xd.grad - g1).abs().max().item() <= 2e-6 * g1.abs().max().item()
     xd = x.clone().requires_grad_(True)
@@ -216,7 +233,7 @@ def test_dropin_route_retain_graph_and_fallbacks(rr, abi):
     assert len(seen) == 1 and seen[0].abs().max().item() > 0       # the hook saw the true dL/dR, not the zero marker
     xd = x.clone().requires_grad_(True)
     loss = rr.loss_frobenius(rr.symmetric_orthogonalization(xd).view(-1, 3, 3), rt)
-    assert type(loss.grad_fn).__name__ != "_FusedFromSvdOutputBackward"
+    assert not _fused(loss)
     with torch.no_grad():
         assert rr.loss_frobenius(rr.symmetric_orthogonalization(x), rt).grad_fn is None
     xd = x.clone().requires_grad_(True)
@@ -251,11 +268,11 @@ def test_star_import_like_the_reference_scripts():
         mae = angle_error(t_R1=outR.detach(), t_R2=R).mean().item()
         assert out.grad.shape == (64, 9) and 0 < mae < 180 and loss.item() > 0
         assert compute_rotation_matrix_from_ortho6d(torch.randn(5, 6, device='cuda')).shape == (5, 3, 3)
-        print('star-import ok', type(loss.grad_fn).__name__)
+        print('star-import ok', 'FusedFromSvdOutput' in repr(loss))
     """)
     res = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=600, cwd="/")
     assert res.returncode == 0, res.stdout + res.stderr
-    assert "star-import ok _FusedFromSvdOutputBackward" in res.stdout
+    assert "star-import ok True" in res.stdout
 
 
 def test_cpp_autograd_node_equals_the_python_node(rr, ops):

@@ -107,6 +107,16 @@ def main():
 
         row["fused_step_with_mean_angle_us"] = timed(step_with_metric, args.reps)
 
+        def unfused_python_nodes():         # the unchanged surface through the Python nodes of ops.py
+            keep, ops._C = ops._C, None
+            try:
+                x.grad = None
+                rr.loss_frobenius(rr.symmetric_orthogonalization(x), rt).backward()
+            finally:
+                ops._C = keep
+
+        row["unfused_dropin_python_nodes_us"] = timed(unfused_python_nodes, args.reps)
+
         def python_node():                  # the Python autograd.Function the C++ node (csrc/pe_torch.cpp) replaces
             x.grad = None
             ops._FusedStep.apply(x, rt, None).backward()
