@@ -258,8 +258,8 @@ class Ctx:
             self.stdout_fd = os.dup(1)
             os.dup2(2, 1)
             import datetime
-            # a mismatch in the collective sequence must fail in two minutes, not in NCCL's default ten
-            dist.init_process_group("nccl", device_id=self.dev, timeout=datetime.timedelta(seconds=120))
+            # a mismatch in the collective sequence must fail in five minutes, not in NCCL's default ten (ranks of a fresh box can start a minute apart)
+            dist.init_process_group("nccl", device_id=self.dev, timeout=datetime.timedelta(seconds=300))
         from poseestimation_b200 import _lib, launch_count
         import poseestimation_b200.rotation_representation as rr
         self.lib, self.check, self.launch_count, self.rr = _lib.lib, _lib.check, launch_count, rr

@@ -100,7 +100,7 @@ def test_product_does_not_import_the_oracle():
     pkg = os.path.join(ROOT, "poseestimation_b200")
     for dirpath, _, files in os.walk(pkg):
         for f in files:
-            if f.endswith((".py", ".cu", ".cuh", ".h")):
+            if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp")):
                 text = open(os.path.join(dirpath, f)).read()
                 assert "import oracle" not in text and "from oracle" not in text, f
                 assert "reference_port" not in text, f
