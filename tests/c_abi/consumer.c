@@ -34,6 +34,9 @@ static int cpu_checks(void) {
     CHECK(pe_frobenius_fwd((const float*)1024, (const float*)2048, (double*)(4096 + 4), 1, NULL) == PE_ERR_BAD_ARG,
           "misaligned accumulator");
     CHECK(pe_kabsch_fwd(NULL, NULL, 4, 0, NULL, NULL, NULL) == PE_ERR_BAD_ARG, "empty clouds");
+    CHECK(pe_frobenius_fwd_static((const float*)1024, (const float*)2048, (double*)4096, (int64_t)PE_STATIC_MAX_RECORDS + 1,
+                                  NULL) == PE_ERR_BAD_ARG, "static scratch limit");
+    CHECK(strstr(pe_last_error(), "PE_STATIC_MAX_RECORDS") != NULL, "static scratch limit message");
     printf("consumer: cpu checks ok (version %d)\n", pe_version());
     return 0;
 }
@@ -80,6 +83,23 @@ static int gpu_checks(void) {
     CHECK(pe_svd_orth_frobenius_fwd(d_m, 9, d_r, d_t, d_sum, N, NULL) == 0, "pe_svd_orth_frobenius_fwd");
     CHECK(cudaMemcpy(&h_sum, d_sum, sizeof h_sum, cudaMemcpyDeviceToHost) == cudaSuccess, "D2H");
     CHECK(fabs(h_sum) < 1e-5, "loss(R, R) = 0");
+    /* round 2: explicit set-up, the step with its metric ([sum |.|_F, sum angle, flag]), the allocation-free loss */
+    {
+        double h3[3] = {-1.0, -1.0, -1.0}, h_a = -1.0, h_b = -2.0;
+        double* d3 = NULL;
+        CHECK(pe_init(-1) == 0 && pe_init(-1) == 0, "pe_init (idempotent)");
+        CHECK(cudaMalloc((void**)&d3, sizeof h3) == cudaSuccess, "cudaMalloc");
+        CHECK(pe_svd_orth_frobenius_step_metrics(d_m, 9, d_r, 1.0f / N, d_t, d3, NULL, NULL, NULL, NULL, N, NULL) == 0,
+              "pe_svd_orth_frobenius_step_metrics");
+        CHECK(cudaMemcpy(h3, d3, sizeof h3, cudaMemcpyDeviceToHost) == cudaSuccess, "D2H");
+        CHECK(fabs(h3[0]) < 1e-5 && h3[1] >= 0.0 && h3[1] < 0.05 * N && h3[2] == 0.0, "step metrics of (M, svd_orth(M))");
+        CHECK(pe_frobenius_fwd(d_m, d_r, d_sum, N, NULL) == 0, "pe_frobenius_fwd");
+        CHECK(cudaMemcpy(&h_a, d_sum, sizeof h_a, cudaMemcpyDeviceToHost) == cudaSuccess, "D2H");
+        CHECK(pe_frobenius_fwd_static(d_m, d_r, d_sum, N, NULL) == 0, "pe_frobenius_fwd_static");
+        CHECK(cudaMemcpy(&h_b, d_sum, sizeof h_b, cudaMemcpyDeviceToHost) == cudaSuccess, "D2H");
+        CHECK(h_a > 1.0 && fabs(h_a - h_b) < 1e-9 * N, "static-scratch loss equals the slot-based one");
+        cudaFree(d3);
+    }
     CHECK(pe_launch_count() >= 2, "launch counter");
     cudaFree(d_m); cudaFree(d_r); cudaFree(d_t); cudaFree(d_d); cudaFree(d_sum);
     printf("consumer: gpu checks ok (%lld launches)\n", pe_launch_count());
