@@ -53,6 +53,14 @@ def test_static_scratch_entry_point_matches_pe_frobenius_fwd_twice_in_a_row(abi,
     # against plain torch in float64 as well (the mean of loss_frobenius, Comparison/main.py:12-16, to 1e-6)
     direct = (a.double() - b.double()).view(n, 9).norm(dim=1).sum().item()
     assert abs(got[0].item() - direct) / n <= 1e-6
+    # arrays that are only 4-byte aligned take the scalar-load path of the kernel: same sum, bit for bit
+    if n <= 1 << 20:
+        ao = torch.empty(n * 9 + 1, device="cuda")[1:].view(n, 9).copy_(a)
+        bo = torch.empty(n * 9 + 1, device="cuda")[1:].view(n, 9).copy_(b)
+        odd = torch.zeros(1, dtype=torch.float64, device="cuda")
+        assert lib.pe_frobenius_fwd_static(ao.data_ptr(), bo.data_ptr(), odd.data_ptr(), n, st) == 0
+        torch.cuda.synchronize()
+        assert odd.item() == got[0].item()
     # a different batch right after: nothing of the previous call's partials leaks into it
     m = max(1, n // 3)
     small = torch.full((1,), -7.0, dtype=torch.float64, device="cuda")
