@@ -229,8 +229,15 @@ struct PairSrcWide {
     }
 };
 
+// A wide stage is 21 words per record: two CTAs fit an SM whatever the register count, so the wide instantiations are
+// compiled for two (up to 128 registers: no spills) instead of the dense kernels' three (80 registers).
+#ifndef PE_WIDE_MINB
+#define PE_WIDE_MINB 2
+#endif
+template <class Op, bool WIDE>
+constexpr int tma_min_blocks() { return WIDE && Op::MINB > PE_WIDE_MINB ? PE_WIDE_MINB : Op::MINB; }
 template <class Op, bool WIDE = false>
-__global__ void __launch_bounds__(kTile, Op::MINB) stream_tma_kernel(const Params<Op> p) {
+__global__ void __launch_bounds__(kTile, (tma_min_blocks<Op, WIDE>())) stream_tma_kernel(const Params<Op> p) {
     using G = Geometry<Op, WIDE>;
     constexpr int T = kTile, TR = G::TR, S = G::STAGES;
     constexpr bool IP = G::IN_PLACE;  // the output record overwrites the thread's own in[0] (wide: in[1]) record in the stage

@@ -291,3 +291,48 @@ def test_refiner_losses_large_meshes(it, pc):
     scale = float(tp2.grad[:, :3].abs().max())
     # (autograd sums 8192 float32 terms of 1/(3 N B) per entry; the kernel counts signs exactly and scales once)
     assert float((tp.grad[:, :3] - tp2.grad[:, :3]).abs().max()) <= 5e-4 * scale
+
+
+def test_config2_training_step_with_metric_full_size(rr):
+    """BASELINE config 2 size (2^24 matrices): the step with its fused metric against the separate kernels (checksum of
+    checksums), its known expectations, the unchanged two-call surface against the fused call, and a sample against the
+    float64 oracle.  Dense and on the out[:, :9] view of a (2^24, 12) output."""
+    n = N3
+    g = torch.Generator(device="cuda").manual_seed(2)
+    wide = torch.randn(n, 12, device="cuda", generator=g)
+    rt = rr.compute_rotation_matrix_from_quaternion(torch.randn(n, 4, device="cuda", generator=g))
+    x = wide[:, :9].contiguous().requires_grad_(True)
+    loss, ang = rr.svd_frobenius_loss(x, rt, with_angle=True)
+    loss.backward()
+    r = rr.symmetric_orthogonalization(x.detach())
+    assert abs(loss.item() - rr.loss_frobenius(r, rt).item()) <= 1e-6
+    assert abs(ang.item() - rr.mean_angle_error(r, rt).item()) <= 1e-7          # fused float32 tail vs all-float64 kernel
+    # uniformly random pairs of rotations: E[angle] = pi/2 + 2/pi rad = 126.476 degrees (sigma ~ 37 degrees / sqrt(n))
+    assert abs(ang.item() - math.degrees(math.pi / 2 + 2 / math.pi)) <= 0.06
+    # gradient rows are tangent at R:  R^T dM is skew-symmetric (dM = R [y]_x)
+    gm = x.grad.view(n, 3, 3)
+    s = torch.bmm(r.transpose(1, 2), gm)
+    scale = gm.abs().amax(dim=(1, 2)).clamp_min(1e-30)
+    assert ((s + s.transpose(1, 2)).abs().amax(dim=(1, 2)) / scale).max().item() <= 1e-4
+    # the reference's own two calls give the same loss and, bit for bit, the same gradient
+    x2 = x.detach().clone().requires_grad_(True)
+    l2 = rr.loss_frobenius(rr.symmetric_orthogonalization(x2), rt)
+    l2.backward()
+    assert abs(l2.item() - loss.item()) <= 1e-7 and torch.equal(x2.grad, x.grad)
+    # the strided view (wide TMA stage): same numbers
+    wl = wide.clone().requires_grad_(True)
+    lw, aw = rr.svd_frobenius_loss(wl[:, :9], rt, with_angle=True)
+    lw.backward()
+    assert abs(lw.item() - loss.item()) <= 1e-7 and abs(aw.item() - ang.item()) <= 1e-9
+    assert torch.equal(wl.grad[:, :9], x.grad) and not wl.grad[:, 9:].any()
+    # a strided sample against the float64 oracle (gradient of the batch mean: scaled back by n)
+    idx = torch.arange(0, n, n // 2048, device="cuda")[:2048]
+    xs = x.detach()[idx].cpu().double().requires_grad_(True)
+    rs = rt[idx].cpu().double()
+    O.loss_frobenius(O.symmetric_orthogonalization(xs), rs).backward()
+    want = xs.grad.numpy() * len(idx)
+    got = x.grad[idx].cpu().double().numpy() * n
+    cond = O.svd_orth_conditioning(x.detach()[idx].cpu()).numpy()
+    sc = np.abs(want).max(1)
+    rel = np.abs(got - want).max(1) / np.maximum(sc, 0.1 * np.median(sc))
+    assert rel[cond > 0.1].max() <= 1e-4

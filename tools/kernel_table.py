@@ -72,6 +72,7 @@ def main():
     w12 = rnd(n, 12)
     add("svd_orth_fwd on out[:, :9] of (n, 12) (wide TMA stage)", 72, lambda: check(lib.pe_svd_orth_fwd(P(w12), 12, P(o9), None, n, st), ""))
     add("svd_orth_bwd (recompute) on the (n, 12) view", 108, lambda: check(lib.pe_svd_orth_bwd(P(w12), 12, None, P(g9), P(o9b), n, st), ""))
+    add("svd_orth_frobenius_step on the (n, 12) view", 108, lambda: check(lib.pe_svd_orth_frobenius_step(P(w12), 12, P(r1), 1.0 / n, P(o9b), P(sums), n, st), ""))
     add("step_metrics on the (n, 12) view", 108, lambda: check(lib.pe_svd_orth_frobenius_step_metrics(P(w12), 12, P(r1), 1.0 / n, P(o9b), P(sums3), None, None, None, None, n, st), ""))
     del w12
     add("scale_by_scalar (backward of the step)", 72, lambda: check(lib.pe_scale_by_scalar(P(o9b), P(one), P(o9), 9 * n, st), ""))
