@@ -651,7 +651,13 @@ def run_native(args):
                 "achieved": achieved, "peak": c.peak, "unit": "GB/s", "frac": achieved / c.peak,
                 "traffic": TRAFFIC_STEP * n / N_DEFAULT, "traffic_source": TRAFFIC_SOURCE,
                 "peak_source": c.peak_src, "bytes_per_matrix": BYTES_STEP, "ms": r["kernel_ms"],
-                "step_frac": BYTES_STEP * n / (ms_per_step * 1e-3) / 1e9 / c.peak}
+                "step_frac": BYTES_STEP * n / (ms_per_step * 1e-3) / 1e9 / c.peak,
+                # informational: this HBM reads faster than it writes (tools/ubench/mix_rw.cu, profiles/r2p_mix_rw.txt:
+                # read only 7111 GB/s, write only 6000 GB/s from plain streaming kernels); the additive bound for the
+                # step's 72 B read + 36 B written per matrix.  `frac` above stays on the driver's 1:1 copy figure.
+                "mix_aware": {"read_gbs": 7111.0, "write_gbs": 6000.0, "source": "profiles/r2p_mix_rw.txt",
+                              "bound_ms": n * (72 / 7111.0 + 36 / 6000.0) * 1e-6,
+                              "frac": n * (72 / 7111.0 + 36 / 6000.0) * 1e-6 / r["kernel_ms"]}}
     also = {"step_kernel_ms": r["kernel_ms"], "backward_upstream_one_ms": r["bwd_ms"], "loss": r["loss"],
             "mean_angle_error_deg": r["mean_angle_error_deg"], "range_flag": r["range_flag"]}
 
