@@ -50,8 +50,9 @@ at::Tensor records9(const at::Tensor& x, int64_t* stride) {
     return x;
 }
 
-at::Tensor matrices9(const at::Tensor& r, int64_t n) {
+at::Tensor matrices9(const at::Tensor& r, int64_t n, const at::Tensor& like) {
     TORCH_CHECK(r.is_cuda() && r.scalar_type() == at::kFloat, "expected float32 CUDA rotation targets");
+    TORCH_CHECK(r.device() == like.device(), "tensors on different devices: ", like.device(), " and ", r.device());
     TORCH_CHECK((r.dim() == 3 && r.size(1) == 3 && r.size(2) == 3) || (r.dim() == 2 && r.size(1) == 9),
                 "expected (n, 3, 3) matrices, got ", r.sizes());
     TORCH_CHECK(r.size(0) == n, "batch mismatch: ", n, " records but ", r.size(0), " target rotations");
@@ -65,7 +66,7 @@ struct FusedStep : public torch::autograd::Function<FusedStep> {
         int64_t stride = 9;
         at::Tensor x = records9(x_in, &stride);
         const int64_t n = x.size(0);
-        at::Tensor rt = matrices9(r_true, n);
+        at::Tensor rt = matrices9(r_true, n, x);
         const c10::cuda::CUDAGuard guard(x.device());
         ensure_init(x.device().index());
         auto f32 = x.options().requires_grad(false);
@@ -223,7 +224,7 @@ struct FusedFromSvdOutput : public torch::autograd::Function<FusedFromSvdOutput>
     static at::Tensor forward(torch::autograd::AutogradContext* ctx, const at::Tensor& r, const at::Tensor& r_true,
                               const at::Tensor& x, int64_t stride, c10::IValue park) {
         const int64_t n = x.size(0);
-        at::Tensor rt = matrices9(r_true, n);
+        at::Tensor rt = matrices9(r_true, n, x);
         const c10::cuda::CUDAGuard guard(x.device());
         auto f32 = x.options().requires_grad(false);
         at::Tensor dx = at::empty({n, 9}, f32), loss;

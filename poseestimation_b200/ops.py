@@ -147,12 +147,28 @@ def _p(t: Tensor | None) -> int | None:
     return None if t is None else t.data_ptr()
 
 
-def _mat_n(x: Tensor, n: int, what: str) -> Tensor:
-    """dense (n, 9) batch that must hold exactly n matrices (the kernel reads n records of it)."""
+def _mat_n(x: Tensor, n: int, what: str, like: Tensor | None = None) -> Tensor:
+    """dense (n, 9) batch that must hold exactly n matrices (the kernel reads n records of it) and live on the device of
+    ``like`` (the kernel runs there and would be handed a foreign pointer otherwise)."""
     x = _mat(x)
     if x.shape[0] != n:
         raise ValueError(f"batch mismatch: {n} records but {x.shape[0]} {what}")
+    if like is not None and x.device != like.device:
+        raise ValueError(f"tensors on different devices: {like.device} and {x.device} ({what})")
     return x
+
+
+def _same_device(*ts) -> None:
+    """every tensor argument of a launch lives on one device (a kernel runs on the first one's device and would be
+    handed foreign pointers otherwise)"""
+    dev = None
+    for t in ts:
+        if t is None:
+            continue
+        if dev is None:
+            dev = t.device
+        elif t.device != dev:
+            raise ValueError(f"tensors on different devices: {dev} and {t.device}")
 
 
 def _mat_pair(a: Tensor, b: Tensor) -> tuple[Tensor, Tensor]:
@@ -188,7 +204,7 @@ def svd_orth_bwd(x: Tensor, r: Tensor, g: Tensor) -> Tensor:
     """dL/dx from g = dL/dr; r is the saved forward output."""
     x, stride = _rec(x, 9)
     n = x.shape[0]
-    r, g = _mat_n(r, n, "saved rotations"), _mat_n(g, n, "upstream gradients")
+    r, g = _mat_n(r, n, "saved rotations", x), _mat_n(g, n, "upstream gradients", x)
     dx = torch.empty((n, 9), dtype=torch.float32, device=x.device)
     with torch.cuda.device(x.device):
         check(lib.pe_svd_orth_bwd(x.data_ptr(), stride, r.data_ptr(), g.data_ptr(), dx.data_ptr(), n, _stream()),
@@ -206,7 +222,7 @@ def svd_orth_bwd_recompute(x: Tensor, g: Tensor) -> Tensor:
     """Same pullback, recomputing r from x inside the kernel (reads 72 B/matrix instead of 108)."""
     x, stride = _rec(x, 9)
     n = x.shape[0]
-    g = _mat_n(g, n, "upstream gradients")
+    g = _mat_n(g, n, "upstream gradients", x)
     dx = torch.empty((n, 9), dtype=torch.float32, device=x.device)
     with torch.cuda.device(x.device):
         check(lib.pe_svd_orth_bwd(x.data_ptr(), stride, None, g.data_ptr(), dx.data_ptr(), n, _stream()),
@@ -285,7 +301,7 @@ def _make_map(name: str, w: int):
     def bwd(x: Tensor, g: Tensor) -> Tensor:
         x, stride = _rec(x, w)
         n = x.shape[0]
-        g = _mat_n(g, n, "upstream gradients")
+        g = _mat_n(g, n, "upstream gradients", x)
         dx = torch.empty((n, w), dtype=torch.float32, device=x.device)
         with torch.cuda.device(x.device):
             check(bwd_c(x.data_ptr(), stride, g.data_ptr(), dx.data_ptr(), n, _stream()), f"pe_{name}_bwd")
@@ -335,7 +351,7 @@ def _(x, eps):
 def expmap_eps_bwd(x: Tensor, g: Tensor, eps: float) -> Tensor:
     x, stride = _rec(x, 3)
     n = x.shape[0]
-    g = _mat_n(g, n, "upstream gradients")
+    g = _mat_n(g, n, "upstream gradients", x)
     dx = torch.empty((n, 3), dtype=torch.float32, device=x.device)
     with torch.cuda.device(x.device):
         check(lib.pe_expmap_eps_bwd(x.data_ptr(), stride, g.data_ptr(), eps, dx.data_ptr(), n, _stream()),
@@ -584,10 +600,8 @@ def map_metric_sum(x: Tensor, r_true: Tensor, map_id: int, width: int, metric_id
                    hi: float) -> tuple[Tensor, Tensor]:
     """(sum (1,) float64, flag (1,) int32: bit 0 = an angle_error cosine out of range; 0 for the other metrics)."""
     x, stride = _rec(x, width)
-    rt = _mat(r_true)
     n = x.shape[0]
-    if rt.shape[0] != n:
-        raise ValueError(f"{n} records but {rt.shape[0]} target rotations")
+    rt = _mat_n(r_true, n, "target rotations", x)
     s = torch.empty((1,), dtype=torch.float64, device=x.device)
     flag = torch.zeros((1,), dtype=torch.int32, device=x.device)
     with torch.cuda.device(x.device):
@@ -609,9 +623,7 @@ def svd_orth_frobenius_sum(x: Tensor, r_true: Tensor, write_r: bool) -> tuple[Te
     """(sum_b |r_true_b - svd_orth(x_b)|_F as (1,) float64, r (n, 3, 3) or an empty tensor)."""
     x, stride = _rec(x, 9)
     n = x.shape[0]
-    rt = _mat(r_true)
-    if rt.shape[0] != n:
-        raise ValueError("batch mismatch")
+    rt = _mat_n(r_true, n, "target rotations", x)
     s = torch.empty((1,), dtype=torch.float64, device=x.device)
     r = torch.empty((n, 3, 3) if write_r else (0,), dtype=torch.float32, device=x.device)
     with torch.cuda.device(x.device):
@@ -643,7 +655,7 @@ def _(x, r_true):
 def svd_orth_frobenius_bwd(x: Tensor, r_true: Tensor, gout: Tensor) -> Tensor:
     x, stride = _rec(x, 9)
     n = x.shape[0]
-    rt = _mat_n(r_true, n, "target rotations")
+    rt = _mat_n(r_true, n, "target rotations", x)
     gout = _scalar32(gout)
     dx = torch.empty((n, 9), dtype=torch.float32, device=x.device)
     if n:
@@ -676,7 +688,7 @@ def _step_launch(x: Tensor, r_true: Tensor, with_angle: bool):
     """-> (loss 0-d f32, mean angle 0-d f64 | None, flag (1,) i32 | None, dx (n, 9)) from ONE launch."""
     x, stride = _rec(x, 9)
     n = x.shape[0]
-    rt = _mat_n(r_true, n, "target rotations")
+    rt = _mat_n(r_true, n, "target rotations", x)
     dev = x.device
     dx = torch.empty((n, 9), dtype=torch.float32, device=dev)
     if not n:        # the mean of an empty batch is NaN, as torch's; nothing to launch
@@ -909,6 +921,7 @@ def kabsch(p: Tensor, q: Tensor) -> tuple[Tensor, Tensor]:
         raise TypeError("pe_b200 ops compute in float32")
     if p.dim() != 3 or p.shape[2] != 3 or p.shape != q.shape:
         raise ValueError(f"expected two (B, N, 3) clouds, got {tuple(p.shape)} and {tuple(q.shape)}")
+    _same_device(p, q)
     p, q = p.contiguous(), q.contiguous()
     b, npts = p.shape[0], p.shape[1]
     r = torch.empty((b, 3, 3), dtype=torch.float32, device=p.device)
@@ -937,6 +950,7 @@ def _clouds(p: Tensor) -> Tensor:
 
 def _affine_launch(a: Tensor, t: Tensor | None, p: Tensor, transpose: bool) -> Tensor:
     """a: (B, 3, 3) view with unit inner stride (e.g. T[:, :3, :3]); t: (B, 3) view or None (e.g. T[:, :3, 3])."""
+    _same_device(p, a, t)
     b, npts = p.shape[0], p.shape[1]
     if a.dtype != torch.float32 or a.shape != (b, 3, 3):
         raise ValueError(f"expected a float32 ({b}, 3, 3) matrix batch, got {a.dtype} {tuple(a.shape)}")
@@ -974,6 +988,7 @@ def cloud_outer_sum(g: Tensor, p: Tensor) -> tuple[Tensor, Tensor]:
     g, p = _clouds(g), _clouds(p)
     if g.shape != p.shape:
         raise ValueError("cloud shapes differ")
+    _same_device(g, p)
     b, npts = p.shape[0], p.shape[1]
     m = torch.zeros((b, 3, 3), dtype=torch.float32, device=p.device)
     s = torch.zeros((b, 3), dtype=torch.float32, device=p.device)
@@ -1020,6 +1035,7 @@ _register(affine_points, _affine_backward, _affine_setup)
 @torch.library.custom_op(f"{NS}::kabsch_ctx", mutates_args=(), device_types="cuda")
 def kabsch_ctx(p: Tensor, q: Tensor) -> tuple[Tensor, Tensor, Tensor]:
     p, q = _clouds(p), _clouds(q)
+    _same_device(p, q)
     if p.shape != q.shape:
         raise ValueError(f"expected two (B, N, 3) clouds, got {tuple(p.shape)} and {tuple(q.shape)}")
     b, npts = p.shape[0], p.shape[1]
@@ -1042,6 +1058,7 @@ def _(p, q):
 @torch.library.custom_op(f"{NS}::kabsch_bwd", mutates_args=(), device_types="cuda")
 def kabsch_bwd(p: Tensor, q: Tensor, r: Tensor, c: Tensor, g_r: Tensor, g_t: Tensor) -> tuple[Tensor, Tensor]:
     p, q = _clouds(p), _clouds(q)
+    _same_device(p, q, r, c, g_r, g_t)
     b, npts = p.shape[0], p.shape[1]
     g = torch.cat([g_r.reshape(b, 9), g_t.reshape(b, 3)], dim=1).to(torch.float32).contiguous()
     cq = torch.empty((b, 12), dtype=torch.float32, device=p.device)
@@ -1094,6 +1111,7 @@ def _weights(w: Tensor, b: int, npts: int) -> Tensor:
 @torch.library.custom_op(f"{NS}::kabsch_weighted_ctx", mutates_args=(), device_types="cuda")
 def kabsch_weighted_ctx(p: Tensor, q: Tensor, w: Tensor) -> tuple[Tensor, Tensor, Tensor]:
     p, q = _clouds(p), _clouds(q)
+    _same_device(p, q, w)
     if p.shape != q.shape:
         raise ValueError(f"expected two (B, N, 3) clouds, got {tuple(p.shape)} and {tuple(q.shape)}")
     b, npts = p.shape[0], p.shape[1]
@@ -1119,6 +1137,7 @@ def kabsch_weighted_bwd(p: Tensor, q: Tensor, w: Tensor, r: Tensor, c: Tensor, g
                         need_q: bool, need_w: bool) -> tuple[Tensor, Tensor, Tensor]:
     """Gradients that are not needed come back as empty (0,) tensors and are neither computed nor written."""
     p, q = _clouds(p), _clouds(q)
+    _same_device(p, q, w, r, c, g_r, g_t)
     b, npts = p.shape[0], p.shape[1]
     w = _weights(w, b, npts)
     g = torch.cat([g_r.reshape(b, 9), g_t.reshape(b, 3)], dim=1).to(torch.float32).contiguous()
@@ -1176,6 +1195,7 @@ def axis_angle_matrix(theta: Tensor, axis: Tensor) -> Tensor:
     n = theta.numel()
     if axis.shape != (n, 3):
         raise ValueError(f"expected axis of shape ({n}, 3), got {tuple(axis.shape)}")
+    _same_device(theta, axis)
     theta, axis = theta.reshape(n).contiguous(), axis.contiguous()
     r = torch.empty((n, 3, 3), dtype=torch.float32, device=theta.device)
     if n:
@@ -1207,6 +1227,7 @@ def pose_update(out: Tensor, t_init: Tensor, fx: float, fy: float) -> Tensor:
     n = out.shape[0]
     if ti.shape[0] != n:
         raise ValueError("batch mismatch")
+    _same_device(out, ti)
     tp = torch.empty((n, 4, 4), dtype=torch.float32, device=out.device)
     if n:
         with torch.cuda.device(out.device):
@@ -1225,6 +1246,9 @@ def pose_update_bwd(out: Tensor, t_init: Tensor, g: Tensor, fx: float, fy: float
     out, stride = _rec(out, 12)
     ti, g = _poses(t_init), _poses(g)
     n = out.shape[0]
+    if ti.shape[0] != n or g.shape[0] != n:
+        raise ValueError("batch mismatch")
+    _same_device(out, ti, g)
     d = torch.empty((n, 12), dtype=torch.float32, device=out.device)
     if n:
         with torch.cuda.device(out.device):
@@ -1260,6 +1284,7 @@ def add_l1(t_gt: Tensor, t_pred: Tensor, points: Tensor, disentangled: bool) -> 
     b, npts = pts.shape[0], pts.shape[1]
     if tg.shape[0] != b or tp.shape[0] != b:
         raise ValueError("batch mismatch")
+    _same_device(pts, tg, tp)
     item = torch.empty((b,), dtype=torch.float32, device=pts.device)
     s = torch.zeros((1,), dtype=torch.float64, device=pts.device)
     grad = torch.empty((b, 3, 4), dtype=torch.float32, device=pts.device)

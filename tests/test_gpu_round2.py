@@ -572,3 +572,34 @@ def test_mismatched_batches_raise_instead_of_reading_past_the_end(rr, ops):
         ops.svd_orth_bwd_recompute(torch.randn(100, 9, device="cuda"), b)
     with pytest.raises(ValueError, match="batch mismatch"):
         ops.ortho6d_bwd(torch.randn(100, 6, device="cuda"), b)
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_second_device_and_tensors_on_two_devices(rr, ops):
+    """Per-device set-up (launch slots, kernel attributes) on a device other than the current one, and arguments that
+    live on different devices: an error, not a kernel handed a foreign pointer."""
+    g = torch.Generator().manual_seed(3)
+    x = torch.randn(5000, 9, generator=g)
+    rt = O.symmetric_orthogonalization(torch.randn(5000, 9, generator=g).double()).float()
+    outs = []
+    for dev in ("cuda:0", "cuda:1"):
+        xd = x.to(dev).requires_grad_(True)
+        loss, ang = rr.svd_frobenius_loss(xd, rt.to(dev), with_angle=True)      # current device stays cuda:0
+        loss.backward()
+        l2 = rr.loss_frobenius(rr.symmetric_orthogonalization(xd), rt.to(dev))
+        outs.append((loss.item(), ang.item(), l2.item(), xd.grad.cpu()))
+    assert outs[0][:3] == outs[1][:3] and torch.equal(outs[0][3], outs[1][3])
+    a = rr.symmetric_orthogonalization(x.to("cuda:0"))
+    b = rt.to("cuda:1")
+    for fn in (rr.loss_frobenius, rr.angle_error, rr.mean_angle_error, rr.geodesic,
+               rr.compute_geodesic_distance_from_two_matrices):
+        with pytest.raises(ValueError, match="different devices"):
+            fn(a, b)
+    with pytest.raises((ValueError, RuntimeError), match="different devices"):
+        rr.svd_frobenius_loss(x.to("cuda:0").requires_grad_(True), b)
+    with pytest.raises(ValueError, match="different devices"):
+        rr.svd_frobenius_loss(x.to("cuda:0"), b)
+    with pytest.raises(ValueError, match="different devices"):
+        rr.map_metric("SVD", x.to("cuda:0"), b)
+    with pytest.raises(ValueError, match="different devices"):
+        rr.kabsch(torch.rand(4, 64, 3, device="cuda:0"), torch.rand(4, 64, 3, device="cuda:1"))
