@@ -12,8 +12,8 @@ import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-SOURCES = ["pe_api.cu", "pe_kabsch.cu", "pe_cloud.cu", "pe_addl1.cu", "pe_static.cu"]
-HEADERS = ["pe_common.h", "pe_math.cuh", "pe_stage.cuh", "pe_stream.cuh", "pe_lanes.cuh", "pe_ops.cuh",
+SOURCES = ["pe_api.cu", "pe_api_svd.cu", "pe_api_step.cu", "pe_api_metric.cu", "pe_kabsch.cu", "pe_cloud.cu", "pe_addl1.cu", "pe_static.cu"]
+HEADERS = ["pe_common.h", "pe_math.cuh", "pe_stage.cuh", "pe_stream.cuh", "pe_lanes.cuh", "pe_ops.cuh", "pe_api_run.cuh",
            os.path.join("..", "..", "include", "pe_rotation.h")]
 OUT = os.path.join(HERE, "libpe_rotation.so")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]

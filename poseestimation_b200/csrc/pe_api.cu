@@ -1,77 +1,11 @@
-// extern "C" entry points of libpe_rotation.so (declared in include/pe_rotation.h) for the per-record ops.
-#include "pe_ops.cuh"
+// extern "C" entry points of libpe_rotation.so (declared in include/pe_rotation.h): library state, the light per-record
+// ops (maps, losses, angle_error, pose update, Kabsch backward coefficients) and the scale kernels.  The SVD entry points
+// are in pe_api_svd.cu, the single-pass step in pe_api_step.cu, pe_map_metric_fwd in pe_api_metric.cu.
+#include "pe_api_run.cuh"
 
 using namespace pe;
 
 namespace {
-
-template <class Op>
-Params<Op> make_params(const float* i0, long long stride0, const float* i1, const float* i2, float* o0, float* o1,
-                       long long n, double* sums, int* flag, typename Op::Extra ex) {
-    Params<Op> p;
-    p.in[0] = i0; p.in[1] = i1; p.in[2] = i2;
-    p.out[0] = o0; p.out[1] = o1;
-    p.n = n;
-    p.in0_stride = stride0;
-    p.sums = sums;
-    p.mean32 = nullptr;
-    p.mean_scale = 0.0;
-    p.mean64 = nullptr;
-    p.flag = flag;
-    p.flag_to_sums = 0;
-    p.sched = nullptr;  // assigned by stream_launch
-    p.ex = ex;
-    return p;
-}
-
-template <class Op>
-int run(const float* i0, long long stride0, const float* i1, const float* i2, float* o0, float* o1, long long n,
-        double* sums, int* flag, typename Op::Extra ex, void* stream, float* mean32 = nullptr, double mean_scale = 0.0,
-        double* mean64 = nullptr, void* scratch = nullptr, bool flag_to_sums = false) {
-    cudaStream_t st = static_cast<cudaStream_t>(stream);
-    if (n < 0) return fail(PE_ERR_BAD_ARG, "negative record count");
-    // natural alignment of every array (a misaligned access would be a sticky device fault, not an error code)
-    if ((reinterpret_cast<uintptr_t>(i0) | reinterpret_cast<uintptr_t>(i1) | reinterpret_cast<uintptr_t>(i2) |
-         reinterpret_cast<uintptr_t>(o0) | reinterpret_cast<uintptr_t>(o1) | reinterpret_cast<uintptr_t>(flag)) & 3u)
-        return fail(PE_ERR_BAD_ARG, "array not aligned to 4 bytes");
-    if (reinterpret_cast<uintptr_t>(sums) & 7u) return fail(PE_ERR_BAD_ARG, "float64 accumulator not aligned to 8 bytes");
-    if (Op::NRED > 0) {
-        if (!sums) return fail(PE_ERR_BAD_ARG, "null accumulator pointer");
-        if (n == 0) {  // an empty batch still defines its sums; otherwise the kernel's last CTA writes them
-            cudaError_t e = cudaMemsetAsync(sums, 0, sizeof(double) * Op::NRED, st);
-            if (e != cudaSuccess) return fail_cuda(e, "cudaMemsetAsync(sum)");
-        }
-    }
-    if (Op::FLAG) {
-        if (!flag && !flag_to_sums) return fail(PE_ERR_BAD_ARG, "null flag pointer");
-        if (n == 0) {  // otherwise the kernel's last CTA writes the flag (its bits meet in the launch slot)
-            cudaError_t e = flag ? cudaMemsetAsync(flag, 0, sizeof(int), st) : cudaSuccess;
-            if (e == cudaSuccess && flag_to_sums) e = cudaMemsetAsync(sums + Op::NRED, 0, sizeof(double), st);
-            if (e != cudaSuccess) return fail_cuda(e, "cudaMemsetAsync(flag)");
-        }
-    }
-    Params<Op> p = make_params<Op>(i0, stride0, i1, i2, o0, o1, n, sums, flag, ex);
-    p.flag_to_sums = flag_to_sums ? 1 : 0;
-    if (mean32) {
-        if (reinterpret_cast<uintptr_t>(mean32) & 3u) return fail(PE_ERR_BAD_ARG, "array not aligned to 4 bytes");
-        if (n == 0) {  // the mean of an empty batch is NaN, as torch's (all-ones bits are a quiet NaN)
-            cudaError_t e = cudaMemsetAsync(mean32, 0xFF, sizeof(float), st);
-            if (e != cudaSuccess) return fail_cuda(e, "cudaMemsetAsync(mean)");
-        }
-        p.mean32 = mean32;
-        p.mean_scale = mean_scale;
-    }
-    if (mean64) {
-        if (reinterpret_cast<uintptr_t>(mean64) & 7u) return fail(PE_ERR_BAD_ARG, "float64 mean not aligned to 8 bytes");
-        if (n == 0) {
-            cudaError_t e = cudaMemsetAsync(mean64, 0xFF, sizeof(double), st);
-            if (e != cudaSuccess) return fail_cuda(e, "cudaMemsetAsync(mean)");
-        }
-        p.mean64 = mean64;
-        p.mean_scale = mean_scale;
-    }
-    return stream_launch<Op>(p, st, scratch);
-}
 
 // y = x * (*g): the backward of a single-pass step (the gradient for a unit upstream gradient times the upstream
 // scalar, read on the device so that no host synchronisation is needed).  Pure stream: 8 B per word.
@@ -112,22 +46,6 @@ __global__ void __launch_bounds__(1024) scale_inplace_kernel(float4* __restrict_
 
 }  // namespace
 
-namespace {
-template <template <int> class Op>
-int map_metric(int metric, const float* x, int64_t stride, const float* rt, Clamp c, double* sum, int* flag, int64_t n,
-               void* stream) {
-    switch (metric) {
-        case PE_METRIC_FROBENIUS:
-            return run<Op<0>>(x, stride, rt, nullptr, nullptr, nullptr, n, sum, nullptr, c, stream);
-        case PE_METRIC_GEODESIC:
-            return run<Op<1>>(x, stride, rt, nullptr, nullptr, nullptr, n, sum, nullptr, c, stream);
-        case PE_METRIC_ANGLE_DEG:
-            return run<Op<2>>(x, stride, rt, nullptr, nullptr, nullptr, n, sum, flag, c, stream);
-    }
-    return fail(PE_ERR_BAD_ARG, "unknown metric");
-}
-}  // namespace
-
 extern "C" {
 
 int pe_version(void) { return PE_VERSION; }
@@ -140,16 +58,6 @@ int pe_init(int device) {
         if (e != cudaSuccess) return fail_cuda(e, "cudaGetDevice");
     }
     return slots_init(dev);
-}
-
-int pe_svd_orth_fwd(const float* m, int64_t m_stride, float* r, float* det_sign, int64_t n, void* stream) {
-    if (det_sign) return run<SvdFwd<true>>(m, m_stride, nullptr, nullptr, r, det_sign, n, nullptr, nullptr, {}, stream);
-    return run<SvdFwd<false>>(m, m_stride, nullptr, nullptr, r, nullptr, n, nullptr, nullptr, {}, stream);
-}
-int pe_svd_orth_bwd(const float* m, int64_t m_stride, const float* r, const float* g, float* dm, int64_t n,
-                    void* stream) {
-    if (r) return run<SvdBwdSaved>(m, m_stride, r, g, dm, nullptr, n, nullptr, nullptr, {}, stream);
-    return run<SvdBwdRecompute>(m, m_stride, g, nullptr, dm, nullptr, n, nullptr, nullptr, {}, stream);
 }
 
 #define PE_MAP_API(fn, Tag)                                                                                      \
@@ -223,33 +131,6 @@ int pe_angle_error_fwd(const float* r1, const float* r2, double* deg, double* su
     return fail(PE_ERR_BAD_ARG, "both outputs are null");
 }
 
-int pe_svd_orth_frobenius_fwd(const float* m, int64_t m_stride, const float* r_true, float* r, double* sum,
-                              int64_t n, void* stream) {
-    if (r) return run<SvdFrobFwd<true>>(m, m_stride, r_true, nullptr, r, nullptr, n, sum, nullptr, {}, stream);
-    return run<SvdFrobFwd<false>>(m, m_stride, r_true, nullptr, nullptr, nullptr, n, sum, nullptr, {}, stream);
-}
-int pe_svd_orth_frobenius_bwd(const float* m, int64_t m_stride, const float* r_true, const float* gout,
-                              float inv_n, float* dm, int64_t n, void* stream) {
-    if (!gout) return fail(PE_ERR_BAD_ARG, "null upstream-gradient pointer");
-    return run<SvdFrobBwd>(m, m_stride, r_true, nullptr, dm, nullptr, n, nullptr, nullptr, {gout, inv_n}, stream);
-}
-
-int pe_svd_orth_frobenius_step(const float* m, int64_t m_stride, const float* r_true, float inv_n, float* dm,
-                               double* sum, int64_t n, void* stream) {
-    return run<SvdFrobStep>(m, m_stride, r_true, nullptr, dm, nullptr, n, sum, nullptr, {inv_n}, stream);
-}
-int pe_svd_orth_frobenius_step_mean(const float* m, int64_t m_stride, const float* r_true, float inv_n, float* dm,
-                                    double* sum, float* mean, int64_t n, void* stream) {
-    if (!mean) return fail(PE_ERR_BAD_ARG, "null mean pointer");
-    return run<SvdFrobStep>(m, m_stride, r_true, nullptr, dm, nullptr, n, sum, nullptr, {inv_n}, stream, mean,
-                            n > 0 ? 1.0 / (double)n : 0.0);
-}
-int pe_svd_orth_frobenius_step_metrics(const float* m, int64_t m_stride, const float* r_true, float inv_n, float* dm,
-                                       double* sums, float* loss_mean, double* angle_mean, int* flag, void* scratch,
-                                       int64_t n, void* stream) {
-    return run<SvdFrobStepMetrics>(m, m_stride, r_true, nullptr, dm, nullptr, n, sums, flag, {inv_n}, stream, loss_mean,
-                                   n > 0 ? 1.0 / (double)n : 0.0, angle_mean, scratch, true);
-}
 int pe_axis_angle_fwd(const float* theta, const float* axis, float* r, int64_t n, void* stream) {
     return run<AxisAngleFwd>(theta, 1, axis, nullptr, r, nullptr, n, nullptr, nullptr, {}, stream);
 }
@@ -261,19 +142,6 @@ int pe_kabsch_bwd_coeffs(const float* ctx, const float* r, const float* g, int64
 int pe_kabsch_weighted_bwd_coeffs(const float* ctx, const float* r, const float* g, float* coef_q, float* coef_p,
                                   int64_t b, void* stream) {
     return run<KabschBwdCoeffsW>(ctx, 16, r, g, coef_q, coef_p, b, nullptr, nullptr, {}, stream);
-}
-int pe_map_metric_fwd(int map, int metric, const float* x, int64_t x_stride, const float* r_true, float lo, float hi,
-                      double* sum, int* flag, int64_t n, void* stream) {
-    const Clamp c{lo, hi};
-    switch (map) {
-        case PE_MAP_SVD: return map_metric<SvdMetric>(metric, x, x_stride, r_true, c, sum, flag, n, stream);
-        case PE_MAP_ORTHO6D: return map_metric<Ortho6dMetric>(metric, x, x_stride, r_true, c, sum, flag, n, stream);
-        case PE_MAP_QUAT: return map_metric<QuatMetric>(metric, x, x_stride, r_true, c, sum, flag, n, stream);
-        case PE_MAP_EULER: return map_metric<EulerMetric>(metric, x, x_stride, r_true, c, sum, flag, n, stream);
-        case PE_MAP_ORTHO5D: return map_metric<Ortho5dMetric>(metric, x, x_stride, r_true, c, sum, flag, n, stream);
-        case PE_MAP_EXPMAP: return map_metric<ExpmapMetric>(metric, x, x_stride, r_true, c, sum, flag, n, stream);
-    }
-    return fail(PE_ERR_BAD_ARG, "unknown map");
 }
 int pe_pose_update_fwd(const float* out, int64_t out_stride, const float* t_init, float fx, float fy, float* t_pred,
                        int64_t n, void* stream) {
