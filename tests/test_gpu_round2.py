@@ -499,6 +499,38 @@ def test_wide_rows_whose_storage_ends_with_the_last_matrix(ops, rr, n):
     assert abs(float(rr.map_metric("SVD", view, rt)) - float(rr.map_metric("SVD", dense, rt))) <= 1e-9 * 180
 
 
+@pytest.mark.parametrize("stride,offset", [(9, 1), (9, 3), (10, 0), (11, 2), (13, 1), (16, 0), (31, 5), (12, 1), (12, 4)])
+@pytest.mark.parametrize("n", [1, 511, 512, 513, 4097, 150001])
+def test_rows_of_any_stride_at_any_base(ops, rr, n, stride, offset):
+    """ANY row stride and any 4-byte aligned base of the input matrix array: dense rows that start `offset` words into
+    their storage, rows of 10..31 words (direct kernel), 12-word rows (wide stage when 16-byte aligned, else direct).
+    Every SVD-family op must return what it returns on a contiguous copy, bit for bit, whatever the route."""
+    g = torch.Generator(device="cuda").manual_seed(n * 64 + stride)
+    base = torch.randn(offset + n * stride, device="cuda", generator=g)
+    view = base.as_strided((n, 9), (stride, 1), offset)
+    dense = view.contiguous()
+    assert view.data_ptr() % 16 == (4 * offset) % 16
+    rt = rr.symmetric_orthogonalization(torch.randn(n, 9, device="cuda", generator=g))
+    up = torch.randn(n, 3, 3, device="cuda", generator=g)
+    r_v, d_v = ops.svd_orth_det(view)
+    r_d, d_d = ops.svd_orth_det(dense)
+    assert torch.equal(r_v, r_d) and torch.equal(d_v, d_d)
+    assert torch.equal(ops.svd_orth(view), r_d)
+    assert torch.equal(ops.svd_orth_bwd_recompute(view, up), ops.svd_orth_bwd_recompute(dense, up))
+    lv, gv = ops.svd_orth_frobenius_step(view, rt)
+    ld, gd = ops.svd_orth_frobenius_step(dense, rt)
+    assert torch.equal(gv, gd) and abs(lv.item() - ld.item()) <= 1e-6
+    sv, rv = ops.svd_orth_frobenius_sum(view, rt, True)
+    sd, rd = ops.svd_orth_frobenius_sum(dense, rt, True)
+    assert torch.equal(rv, rd) and abs(sv.item() - sd.item()) <= 1e-9 * abs(sd.item())
+    one = torch.ones((), device="cuda")
+    assert torch.equal(ops.svd_orth_frobenius_bwd(view, rt, one), ops.svd_orth_frobenius_bwd(dense, rt, one))
+    for metric in ("frobenius", "geodesic", "angle"):
+        a = float(rr.map_metric("SVD", view, rt, metric)) if metric != "angle" else float(rr.map_metric("SVD", view, rt))
+        b = float(rr.map_metric("SVD", dense, rt, metric)) if metric != "angle" else float(rr.map_metric("SVD", dense, rt))
+        assert abs(a - b) <= 1e-9 * 180
+
+
 def test_wide_route_is_taken_and_can_be_switched_off(rr):
     """PE_NO_WIDE=1 (A/B hook) sends the same view through the direct kernel: same numbers either way."""
     code = textwrap.dedent(f"""

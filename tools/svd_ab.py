@@ -19,10 +19,15 @@ def t(fn, reps=20):
     for _ in range(reps): fn()
     b.record(); torch.cuda.synchronize()
     return round(a.elapsed_time(b) / reps, 4)
+wide = torch.randn(n, 12, device=dev, generator=g)          # the out[:, :9] view of a (B, 12) network output
 res = {"lib": os.path.basename(_lib.LIB_PATH)}
 for rep in range(2):
     res[f"fwd_{rep}"] = t(lambda: lib.pe_svd_orth_fwd(P(x), 9, P(out), None, n, st))
     res[f"bwd_{rep}"] = t(lambda: lib.pe_svd_orth_bwd(P(x), 9, None, P(up), P(out), n, st))
     res[f"step_{rep}"] = t(lambda: lib.pe_svd_orth_frobenius_step(P(x), 9, P(rt), 1.0 / n, P(out), P(sums), n, st))
     res[f"stepm_{rep}"] = t(lambda: lib.pe_svd_orth_frobenius_step_metrics(P(x), 9, P(rt), 1.0 / n, P(out), P(sums), None, None, None, None, n, st))
+    res[f"wfwd_{rep}"] = t(lambda: lib.pe_svd_orth_fwd(P(wide), 12, P(out), None, n, st))
+    res[f"wbwd_{rep}"] = t(lambda: lib.pe_svd_orth_bwd(P(wide), 12, None, P(up), P(out), n, st))
+    res[f"wstep_{rep}"] = t(lambda: lib.pe_svd_orth_frobenius_step(P(wide), 12, P(rt), 1.0 / n, P(out), P(sums), n, st))
+    res[f"wstepm_{rep}"] = t(lambda: lib.pe_svd_orth_frobenius_step_metrics(P(wide), 12, P(rt), 1.0 / n, P(out), P(sums), None, None, None, None, n, st))
 print(json.dumps(res))
