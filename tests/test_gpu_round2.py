@@ -522,7 +522,9 @@ def test_rows_of_any_stride_at_any_base(ops, rr, n, stride, offset):
     assert torch.equal(gv, gd) and abs(lv.item() - ld.item()) <= 1e-6
     sv, rv = ops.svd_orth_frobenius_sum(view, rt, True)
     sd, rd = ops.svd_orth_frobenius_sum(dense, rt, True)
-    assert torch.equal(rv, rd) and abs(sv.item() - sd.item()) <= 1e-9 * abs(sd.item())
+    # the two lanes of a thread meet in one float32 add before the float64 accumulation, and the routes pair the records
+    # differently (t, t + 256 of a tile / i, i + ceil(n/2)): the sums agree to float32 rounding of those pair sums
+    assert torch.equal(rv, rd) and abs(sv.item() - sd.item()) <= 1e-8 * abs(sd.item())
     one = torch.ones((), device="cuda")
     assert torch.equal(ops.svd_orth_frobenius_bwd(view, rt, one), ops.svd_orth_frobenius_bwd(dense, rt, one))
     for metric in ("frobenius", "geodesic", "angle"):
