@@ -116,8 +116,8 @@ struct SvdBwdRecompute {
                                                double*, int&, const Extra&) {
         body<float>(RegSrc<9>{m}, RegSrc<9>{g}, dm);
     }
-    template <class S0>
-    __device__ static __forceinline__ void run2(const S0& m, const PairSrc<9>& g, const PairSrc<0>&, F2* dm, F2*,
+    template <class S0, class S1>  // S1: PairSrc<9>, or PairSrcLate<9> (split wide ring: the load waits for the tile)
+    __device__ static __forceinline__ void run2(const S0& m, const S1& g, const PairSrc<0>&, F2* dm, F2*,
                                                 double*, int&, bool, bool, const Extra&) { body<F2>(m, g, dm); }
 };
 
@@ -302,8 +302,8 @@ struct SvdFrobFwd {
                                                double* red, int&, const Extra&) {
         red[0] += (double)body<float>(RegSrc<9>{m}, RegSrc<9>{rt}, r);
     }
-    template <class S0>
-    __device__ static __forceinline__ void run2(const S0& m, const PairSrc<9>& rt, const PairSrc<0>&, F2* r, F2*,
+    template <class S0, class S1>  // S1: PairSrc<9>, or PairSrcLate<9> (split wide ring: the load waits for the tile)
+    __device__ static __forceinline__ void run2(const S0& m, const S1& rt, const PairSrc<0>&, F2* r, F2*,
                                                 double* red, int&, bool v0, bool v1, const Extra&) {
         F2 f = body<F2>(m, rt, r);
         red[0] += (double)((v0 ? f.x : 0.f) + (v1 ? f.y : 0.f));
@@ -327,8 +327,8 @@ struct SvdFrobBwd {
                                                double*, int&, const Extra& ex) {
         body<float>(RegSrc<9>{m}, RegSrc<9>{rt}, dm, __ldg(ex.gout) * ex.mul);
     }
-    template <class S0>
-    __device__ static __forceinline__ void run2(const S0& m, const PairSrc<9>& rt, const PairSrc<0>&, F2* dm, F2*,
+    template <class S0, class S1>  // S1: PairSrc<9>, or PairSrcLate<9> (split wide ring: the load waits for the tile)
+    __device__ static __forceinline__ void run2(const S0& m, const S1& rt, const PairSrc<0>&, F2* dm, F2*,
                                                 double*, int&, bool, bool, const Extra& ex) {
         body<F2>(m, rt, dm, __ldg(ex.gout) * ex.mul);
     }
@@ -481,8 +481,8 @@ struct SvdFrobStepT {
         red[0] += (double)body<float>(RegSrc<9>{m}, RegSrc<9>{rt}, dm, ex.mul, seed);
         if constexpr (ANGLE) finish<float>(seed, red, flag, true, false);
     }
-    template <class S0>
-    __device__ static __forceinline__ void run2(const S0& m, const PairSrc<9>& rt, const PairSrc<0>&, F2* dm, F2*,
+    template <class S0, class S1>  // S1: PairSrc<9>, or PairSrcLate<9> (split wide ring: the load waits for the tile)
+    __device__ static __forceinline__ void run2(const S0& m, const S1& rt, const PairSrc<0>&, F2* dm, F2*,
                                                 double* red, int& flag, bool v0, bool v1, const Extra& ex) {
         AngleSeed<F2> seed;
         F2 f = body<F2>(m, rt, dm, ex.mul, seed);
@@ -545,8 +545,8 @@ struct SvdMetric {
         svd_from<float>(RegSrc<9>{m}, r, ds);
         metric_accumulate<METRIC>(r, rt, red, flag, ex);
     }
-    template <class S0>
-    __device__ static __forceinline__ void run2(const S0& m, const PairSrc<9>& rts, const PairSrc<0>&, F2*, F2*,
+    template <class S0, class S1>  // S1: PairSrc<9>, or PairSrcLate<9> (split wide ring: the load waits for the tile)
+    __device__ static __forceinline__ void run2(const S0& m, const S1& rts, const PairSrc<0>&, F2*, F2*,
                                                 double* red, int& flag, bool v0, bool v1, const Extra& ex) {
         F2 r[9], rt[9], ds;
         svd_from<F2>(m, r, ds);

@@ -74,25 +74,45 @@ constexpr int stages_for(int witot, int wotot, int budget = 54 * 1024, int nbuf 
 // a quarter-warp covers all 32 banks) and uses the first nine words.  33 % more read bytes on that one array instead of
 // the direct kernel's per-thread 36-byte-strided loads.
 constexpr int kWideRow = 12;
+// PE_WIDE_SPLIT=1 (default): a wide op that has a second input (R_true, the upstream gradient) does not keep it in the
+// stages.  That input is only read AFTER the decomposition, two thirds into a tile's arithmetic, so it lives in ONE
+// buffer of its own: its bulk copy is issued at the top of the iteration that needs it and awaited by the lazy source
+// itself (PairSrcLate); the in-place output is written over it and stored from there.  The ring then holds 12-word rows
+// only: 2 x 24.5 KB + 18.4 KB = 67 KB per CTA instead of 2 x 43 KB, i.e. three CTAs per SM like the dense kernels.
+#ifndef PE_WIDE_SPLIT
+#define PE_WIDE_SPLIT 1
+#endif
 template <class Op, bool WIDE = false>
 struct Geometry {
+    static constexpr bool SPLIT = WIDE && (PE_WIDE_SPLIT != 0) && Op::WI1 > 0 && Op::WI2 == 0;
     __host__ __device__ static constexpr int wi(int k) { return k == 0 ? Op::WI0 : (k == 1 ? Op::WI1 : Op::WI2); }
     __host__ __device__ static constexpr int wo(int k) { return k == 0 ? Op::WO0 : Op::WO1; }
     // words per record INSIDE A STAGE (differs from wi only for the wide in[0])
     __host__ __device__ static constexpr int sw(int k) { return (k == 0 && WIDE) ? kWideRow : wi(k); }
     static constexpr int WITOT = sw(0) + sw(1) + sw(2);
+    static constexpr int SWTOT = SPLIT ? sw(0) : WITOT;        // words per record inside a stage of the ring
+    static constexpr int LATEW = SPLIT ? sw(1) : 0;             // words per record in the one-deep buffer of in[1]
     static constexpr int WOTOT = Op::WO0 + Op::WO1;
     // in-place output: the op's single output record replaces, inside the stage, the thread's own record of in[0] -
     // or, when in[0] is wide, of in[1] (R_true or the upstream gradient: same width as the output, read once, by
     // the thread that owns the record)
     static constexpr bool IN_PLACE0 = !WIDE && Op::RPT == 2 && Op::WO0 == Op::WI0 && Op::WO1 == 0;
     static constexpr bool IN_PLACE1 = WIDE && Op::RPT == 2 && Op::WO0 == Op::WI1 && Op::WO1 == 0;
-    static constexpr bool IN_PLACE = IN_PLACE0 || IN_PLACE1;
+    // a wide op WITHOUT a second input (the forward): the dense output tile is written over the head of the stage the
+    // rows came in - other threads' rows, hence one more CTA barrier between the last read and the first write - and
+    // stored from there: no output ring, three stages of rows, three CTAs per SM
+    static constexpr bool IN_PLACE0W = WIDE && (PE_WIDE_SPLIT != 0) && Op::RPT == 2 && Op::WI1 == 0 && Op::WI2 == 0 &&
+                                       Op::WO0 > 0 && Op::WO0 <= kWideRow && Op::WO1 == 0;
+    static constexpr bool IN_PLACE = IN_PLACE0 || IN_PLACE1 || IN_PLACE0W;
     static constexpr int OUTBUFS = WIDE ? 3 : Op::OUTBUFS;
     static constexpr int NOBUF = (WOTOT > 0 && !IN_PLACE) ? OUTBUFS : 0;
     // wide stages are 21 words per record pair-half: two CTAs per SM (110 KB each)
     static constexpr int STAGES =
-        WIDE ? stages_for(Op::RPT * WITOT, IN_PLACE ? 0 : Op::RPT * WOTOT, 110 * 1024, NOBUF >= 3 ? NOBUF : 2) : Op::STAGES;
+        SPLIT  ? stages_for(Op::RPT * SWTOT, 0, 75 * 1024 - kTile * Op::RPT * 4 * LATEW, 2)
+        : IN_PLACE0W ? stages_for(Op::RPT * WITOT, 0, 75 * 1024, 2)
+        : WIDE ? stages_for(Op::RPT * WITOT, IN_PLACE ? 0 : Op::RPT * WOTOT, 110 * 1024, NOBUF >= 3 ? NOBUF : 2)
+               : Op::STAGES;
+    static_assert(!SPLIT || IN_PLACE1 || WOTOT == 0, "a split wide op stores in place or not at all");
     // How an output tile leaves shared memory (one-barrier path).  TMA bulk store, except for read-heavy ops whose output
     // is less than half of their input: there every thread drains the tile with plain 128-bit streaming stores.
     // Measured on one box, two repetitions each (r1m): angle_error_fwd with per-record float64 output 0.218 -> 0.203 ms,
@@ -106,9 +126,11 @@ struct Geometry {
     static constexpr bool DYNAMIC = Op::RPT == 2;  // tiles drawn from a global counter (see stream_tma_kernel)
     static constexpr bool SLOT = DYNAMIC || Op::NRED > 0 || Op::FLAG;  // the launch needs a slot (scheduler / accumulators / flag)
     static constexpr int kBarBytes = 128;
-    static constexpr int kStageBytes = TR * 4 * WITOT;
+    static constexpr int kStageBytes = TR * 4 * SWTOT;
+    static constexpr int kLateBytes = TR * 4 * LATEW;
     static constexpr int kOutBytes = TR * 4 * WOTOT;
-    static constexpr int kSmemBytes = kBarBytes + STAGES * kStageBytes + NOBUF * kOutBytes + 32 * 8 * (Op::NRED > 0 ? Op::NRED : 1);
+    static constexpr int kSmemBytes =
+        kBarBytes + STAGES * kStageBytes + kLateBytes + NOBUF * kOutBytes + 32 * 8 * (Op::NRED > 0 ? Op::NRED : 1);
 };
 
 template <int N>
@@ -229,13 +251,32 @@ struct PairSrcWide {
     }
 };
 
-// A wide stage is 21 words per record: two CTAs fit an SM whatever the register count, so the wide instantiations are
-// compiled for two (up to 128 registers: no spills) instead of the dense kernels' three (80 registers).
+// in[1] of a split wide op: the tile arrives in a buffer of its own while the decomposition runs; the first load waits
+// for it (every thread by itself - an mbarrier wait is a shared-memory poll, no CTA barrier)
+template <int W>
+struct PairSrcLate {
+    const float* s;
+    int t, stride;
+    uint64_t* bar;
+    uint32_t parity;
+    bool wait;  // false for the ragged last tile, which was written with plain loads
+    __device__ __forceinline__ void load(F2* dst) const {
+        if (wait) mbar_wait(bar, parity);
+        lds_pair<W>(s, t, stride, dst);
+    }
+};
+
+// A wide stage WITH in[1] inside (PE_WIDE_SPLIT=0, or no second input) is up to 21 words per record: two CTAs fit an SM
+// whatever the register count, so those instantiations are compiled for two (up to 128 registers: no spills) instead
+// of the dense kernels' three (80 registers).
 #ifndef PE_WIDE_MINB
 #define PE_WIDE_MINB 2
 #endif
 template <class Op, bool WIDE>
-constexpr int tma_min_blocks() { return WIDE && Op::MINB > PE_WIDE_MINB ? PE_WIDE_MINB : Op::MINB; }
+constexpr int tma_min_blocks() {
+    return WIDE && !Geometry<Op, WIDE>::SPLIT && !Geometry<Op, WIDE>::IN_PLACE0W && Op::MINB > PE_WIDE_MINB ? PE_WIDE_MINB
+                                                                                                              : Op::MINB;
+}
 template <class Op, bool WIDE = false>
 __global__ void __launch_bounds__(kTile, (tma_min_blocks<Op, WIDE>())) stream_tma_kernel(const Params<Op> p) {
     using G = Geometry<Op, WIDE>;
@@ -246,7 +287,9 @@ __global__ void __launch_bounds__(kTile, (tma_min_blocks<Op, WIDE>())) stream_tm
     extern __shared__ __align__(128) unsigned char smem_raw[];
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw);
     float* s_in = reinterpret_cast<float*>(smem_raw + G::kBarBytes);
-    float* s_out = s_in + S * TR * G::WITOT;
+    float* s_late = s_in + S * TR * G::SWTOT;                 // SPLIT: the one buffer of in[1] (and of the in-place output)
+    float* s_out = s_late + TR * G::LATEW;
+    uint64_t* bar_late = &bars[S];
     double* s_red = reinterpret_cast<double*>(s_out + G::NOBUF * TR * G::WOTOT);
 
     const int tid = threadIdx.x;
@@ -276,10 +319,10 @@ __global__ void __launch_bounds__(kTile, (tma_min_blocks<Op, WIDE>())) stream_tm
     auto issue = [&](int s, long long tile) {
         // one elected thread: arm the barrier with the byte count, then one bulk copy per input array
         mbar_arrive_expect_tx(&bars[s], (uint32_t)G::kStageBytes);
-        float* dst = s_in + s * TR * G::WITOT;
+        float* dst = s_in + s * TR * G::SWTOT;
         int off = 0;
 #pragma unroll
-        for (int k = 0; k < 3; ++k) {
+        for (int k = 0; k < (G::SPLIT ? 1 : 3); ++k) {
             if (G::sw(k) > 0) {
                 bulk_g2s(dst + off, p.in[k] + tile * TR * G::sw(k), (uint32_t)(TR * 4 * G::sw(k)), &bars[s], policy);
                 off += TR * G::sw(k);
@@ -287,10 +330,16 @@ __global__ void __launch_bounds__(kTile, (tma_min_blocks<Op, WIDE>())) stream_tm
         }
     };
 
+    auto issue_late = [&](long long tile) {  // SPLIT: in[1] of the tile that is being worked on
+        mbar_arrive_expect_tx(bar_late, (uint32_t)G::kLateBytes);
+        bulk_g2s(s_late, p.in[1] + tile * TR * G::sw(1), (uint32_t)G::kLateBytes, bar_late, policy);
+    };
+
     if (tid == 0) {
         policy = l2_evict_first_policy();
 #pragma unroll
         for (int s = 0; s < S; ++s) mbar_init(&bars[s], 1);
+        if constexpr (G::SPLIT) mbar_init(bar_late, 1);
         mbar_init_fence();
 #pragma unroll
         for (int s = 0; s < S; ++s) {
@@ -312,6 +361,7 @@ __global__ void __launch_bounds__(kTile, (tma_min_blocks<Op, WIDE>())) stream_tm
 
     int s = 0;
     uint32_t parity = 0;
+    uint32_t late_parity = 0;
     int obuf = 0;
     bool refill = false;         // IP mode: the stage vacated by the previous iteration awaits its next tile
     unsigned int refill_tile = 0;
@@ -327,10 +377,20 @@ __global__ void __launch_bounds__(kTile, (tma_min_blocks<Op, WIDE>())) stream_tm
         const long long base = tile * TR;
         const bool full = tile < nfull;
         const int cnt = full ? TR : (int)(n - base);
-        float* si = s_in + s * TR * G::WITOT;
-        float* so = G::IN_PLACE0 ? si : (G::IN_PLACE1 ? si + TR * G::sw(0) : s_out + obuf * TR * G::WOTOT);
+        float* si = s_in + s * TR * G::SWTOT;
+        float* so = (G::IN_PLACE0 || G::IN_PLACE0W) ? si
+                                 : (G::IN_PLACE1 ? (G::SPLIT ? s_late : si + TR * G::sw(0)) : s_out + obuf * TR * G::WOTOT);
 
-        if constexpr (IP) {
+        if constexpr (G::SPLIT) {
+            // in[1] of THIS tile: its buffer is free once the store of the previous tile has read it (in-place ops; the
+            // others left it behind barrier (A)).  It is needed after the decomposition, microseconds from now.
+            if (tid == 0) {
+                if constexpr (IP) {
+                    if (refill) bulk_wait_read<0>();
+                }
+                if (full) issue_late(tile);
+            }
+        } else if constexpr (IP) {
             // the stage used one iteration ago was stored from in place: once the TMA store has finished reading
             // it, refill it (prefetch distance: S - 1 tiles)
             if (tid == 0 && refill) {
@@ -343,20 +403,22 @@ __global__ void __launch_bounds__(kTile, (tma_min_blocks<Op, WIDE>())) stream_tm
             mbar_wait(&bars[s], parity);
         } else {
             // ragged tail: plain coalesced word copies into the same shared-memory layout
+            if constexpr (G::SPLIT && IP) __syncthreads();  // thread 0 has waited for the store that was reading s_late
             int off = 0;
 #pragma unroll
             for (int k = 0; k < 3; ++k) {
                 if (G::sw(k) > 0) {
                     const float* src = p.in[k] + base * G::sw(k);
+                    float* dst = (G::SPLIT && k == 1) ? s_late : si + off;
                     const int words = cnt * G::sw(k) - (G::sw(k) - G::wi(k));  // wide: not past the last matrix
-                    for (int w = tid; w < words; w += T) si[off + w] = src[w];
+                    for (int w = tid; w < words; w += T) dst[w] = src[w];
                     off += TR * G::sw(k);
                 }
             }
             __syncthreads();
         }
 
-        const float* si1 = si + TR * G::sw(0);
+        const float* si1 = G::SPLIT ? s_late : si + TR * G::sw(0);
         const float* si2 = si + TR * (G::sw(0) + G::sw(1));
         RegArr<Op::WO0 * Op::RPT> o0;
         RegArr<Op::WO1 * Op::RPT> o1;
@@ -372,7 +434,10 @@ __global__ void __launch_bounds__(kTile, (tma_min_blocks<Op, WIDE>())) stream_tm
             // two records per thread (tid and tid + T), one in each half of a packed fp32x2 register pair
             PairArr<Op::WO0> q0;
             PairArr<Op::WO1> q1;
-            if constexpr (WIDE)
+            if constexpr (G::SPLIT)
+                Op::run2(PairSrcWide{si, tid, T}, PairSrcLate<Op::WI1>{si1, tid, T, bar_late, late_parity, full},
+                         PairSrc<Op::WI2>{si2, tid, T}, q0.v, q1.v, red, flag, tid < cnt, tid + T < cnt, p.ex);
+            else if constexpr (WIDE)
                 Op::run2(PairSrcWide{si, tid, T}, PairSrc<Op::WI1>{si1, tid, T}, PairSrc<Op::WI2>{si2, tid, T}, q0.v, q1.v,
                          red, flag, tid < cnt, tid + T < cnt, p.ex);
             else
@@ -453,7 +518,8 @@ __global__ void __launch_bounds__(kTile, (tma_min_blocks<Op, WIDE>())) stream_tm
         }
         if constexpr (G::WOTOT > 0) {
             // IP: a thread only ever reads its OWN records of in[0], and it has finished reading them, so it may
-            // overwrite them without a barrier in between
+            // overwrite them without a barrier in between (wide rows: the dense output lands on other threads' rows)
+            if constexpr (G::IN_PLACE0W) __syncthreads();
 #pragma unroll
             for (int rr = 0; rr < Op::RPT; ++rr) {
                 if constexpr (Op::WO0 > 0) sts_record<Op::WO0>(so, tid + rr * T, o0.v + rr * Op::WO0);
@@ -481,6 +547,17 @@ __global__ void __launch_bounds__(kTile, (tma_min_blocks<Op, WIDE>())) stream_tm
             }
             obuf ^= 1;
         }
+        }
+        if constexpr (G::SPLIT) {
+            if (full) late_parity ^= 1;
+            if constexpr (IP) {
+                // the rows of this stage have been read by everybody (barrier (B) / the tail's barrier is behind us) and the
+                // store reads s_late, not the stage: refill it now, a whole tile ahead
+                if (tid == 0) {
+                    if constexpr (DYN) s_tile[s] = drawn;
+                    if (drawn < nfull) issue(s, drawn);
+                }
+            }
         }
         if constexpr (IP) {
             refill = true;
