@@ -43,6 +43,8 @@ def main():
     if "wide" in args.which:
         wide = torch.randn(n, 12, device=dev, generator=g)
         calls["widefwd"] = lambda: lib.pe_svd_orth_fwd(P(wide), 12, P(out), None, n, st)
+        calls["widebwd"] = lambda: lib.pe_svd_orth_bwd(P(wide), 12, None, P(rt), P(out), n, st)
+        calls["widestep0"] = lambda: lib.pe_svd_orth_frobenius_step(P(wide), 12, P(rt), 1.0 / n, P(out), P(sums), n, st)
         calls["widestep"] = lambda: lib.pe_svd_orth_frobenius_step_metrics(P(wide), 12, P(rt), 1.0 / n, P(out), P(sums3),
                                                                            None, None, None, None, n, st)
     if "quatangle" in args.which or "eulerangle" in args.which:
