@@ -112,6 +112,11 @@ int pe_frobenius_fwd_static(const float* a, const float* b, double* sum, int64_t
  * nullable; sum receives sum_b theta_b. */
 int pe_geodesic_fwd(const float* m1, const float* m2, float lo, float hi, float* theta, double* sum, int64_t n,
                     void* stream);
+/* geodesic(R1, R2, reduction='mean' | 'sum') in ONE launch (point_cloud/main.py:70-73): sum as above and
+ * *out = (float)(sum * scale), scale = 1/n for the mean, 1 for the sum.  n == 0 stores NaN (the mean of an empty
+ * batch, as torch's); the caller owns the empty 'sum'. */
+int pe_geodesic_reduce_fwd(const float* m1, const float* m2, float lo, float hi, double* sum, float* out,
+                           double scale, int64_t n, void* stream);
 /* g: n upstream gradients (g_is_scalar = 0) or one device scalar broadcast to all records, times gmul
  * (reduction='mean': g_is_scalar = 1, gmul = 1/n).  d1 or d2 may be NULL.  Gradient is 0 where the clamp is
  * active, as torch.clamp's is. */

@@ -15,6 +15,7 @@ _f = ctypes.c_void_p      # device pointers travel as integers
 _i64 = ctypes.c_int64
 _flt = ctypes.c_float
 _int = ctypes.c_int
+_dbl = ctypes.c_double
 
 # name -> argtypes; every compute entry point returns int (0 = ok).  Mirrors include/pe_rotation.h one to one;
 # tests/test_abi.py checks the two against each other.
@@ -38,6 +39,7 @@ SIGNATURES = {
     "pe_frobenius_fwd_static": [_f, _f, _f, _i64, _f],
     "pe_frobenius_bwd": [_f, _f, _f, _flt, _f, _f, _i64, _f],
     "pe_geodesic_fwd": [_f, _f, _flt, _flt, _f, _f, _i64, _f],
+    "pe_geodesic_reduce_fwd": [_f, _f, _flt, _flt, _f, _f, _dbl, _i64, _f],
     "pe_geodesic_bwd": [_f, _f, _flt, _flt, _f, _int, _flt, _f, _f, _i64, _f],
     "pe_angle_error_fwd": [_f, _f, _f, _f, _f, _i64, _f],
     "pe_svd_orth_frobenius_fwd": [_f, _i64, _f, _f, _f, _i64, _f],

@@ -106,6 +106,12 @@ int pe_geodesic_fwd(const float* m1, const float* m2, float lo, float hi, float*
     if (sum) return run<GeoFwd<false, true>>(m1, 9, m2, nullptr, nullptr, nullptr, n, sum, nullptr, c, stream);
     return fail(PE_ERR_BAD_ARG, "both outputs are null");
 }
+int pe_geodesic_reduce_fwd(const float* m1, const float* m2, float lo, float hi, double* sum, float* out,
+                           double scale, int64_t n, void* stream) {
+    if (!out) return fail(PE_ERR_BAD_ARG, "null output pointer");
+    Clamp c{lo, hi};
+    return run<GeoFwd<false, true>>(m1, 9, m2, nullptr, nullptr, nullptr, n, sum, nullptr, c, stream, out, scale);
+}
 int pe_geodesic_bwd(const float* m1, const float* m2, float lo, float hi, const float* g, int g_is_scalar,
                     float gmul, float* d1, float* d2, int64_t n, void* stream) {
     if (!g) return fail(PE_ERR_BAD_ARG, "null upstream-gradient pointer");

@@ -87,13 +87,13 @@ struct FusedStep : public torch::autograd::Function<FusedStep> {
                 angle = at::empty({}, f32.dtype(at::kDouble));
                 flag = at::empty({1}, f32.dtype(at::kInt));
                 check_rc(pe_svd_orth_frobenius_step_metrics(x.data_ptr<float>(), stride, rt.data_ptr<float>(),
-                                                            1.0f / (float)n, dx.data_ptr<float>(), sums.data_ptr<double>(),
+                                                            (float)(1.0 / (double)n), dx.data_ptr<float>(), sums.data_ptr<double>(),
                                                             loss.data_ptr<float>(), angle.data_ptr<double>(),
                                                             flag.data_ptr<int>(), nullptr, n, st),
                          "pe_svd_orth_frobenius_step_metrics");
             } else {
                 at::Tensor sum = at::empty({1}, f32.dtype(at::kDouble));
-                check_rc(pe_svd_orth_frobenius_step_mean(x.data_ptr<float>(), stride, rt.data_ptr<float>(), 1.0f / (float)n,
+                check_rc(pe_svd_orth_frobenius_step_mean(x.data_ptr<float>(), stride, rt.data_ptr<float>(), (float)(1.0 / (double)n),
                                                          dx.data_ptr<float>(), sum.data_ptr<double>(),
                                                          loss.data_ptr<float>(), n, st),
                          "pe_svd_orth_frobenius_step_mean");
@@ -136,7 +136,7 @@ torch::autograd::variable_list FusedStep::backward(torch::autograd::AutogradCont
         dx = at::empty({n, 9}, x.options().requires_grad(false));
         const int64_t stride = ctx->saved_data["stride"].toInt();
         if (n) check_rc(pe_svd_orth_frobenius_bwd(x.data_ptr<float>(), stride, rt.data_ptr<float>(), g.data_ptr<float>(),
-                                                  1.0f / (float)n, dx.data_ptr<float>(), n, st),
+                                                  (float)(1.0 / (double)n), dx.data_ptr<float>(), n, st),
                         "pe_svd_orth_frobenius_bwd");
     }
     return {dx, at::Tensor(), at::Tensor()};
@@ -234,7 +234,7 @@ struct FusedFromSvdOutput : public torch::autograd::Function<FusedFromSvdOutput>
             void* st = c10::cuda::getCurrentCUDAStream(x.device().index()).stream();
             loss = at::empty({}, f32);
             at::Tensor sum = at::empty({1}, f32.dtype(at::kDouble));
-            check_rc(pe_svd_orth_frobenius_step_mean(x.data_ptr<float>(), stride, rt.data_ptr<float>(), 1.0f / (float)n,
+            check_rc(pe_svd_orth_frobenius_step_mean(x.data_ptr<float>(), stride, rt.data_ptr<float>(), (float)(1.0 / (double)n),
                                                      dx.data_ptr<float>(), sum.data_ptr<double>(), loss.data_ptr<float>(), n, st),
                      "pe_svd_orth_frobenius_step_mean");
         }
@@ -263,7 +263,7 @@ struct FusedFromSvdOutput : public torch::autograd::Function<FusedFromSvdOutput>
         at::Tensor gl = scalar32(grads[0]);
         at::Tensor rc = r.contiguous();
         at::Tensor da = at::empty(r.sizes(), r.options().requires_grad(false));
-        if (n) check_rc(pe_frobenius_bwd(rc.data_ptr<float>(), rt.data_ptr<float>(), gl.data_ptr<float>(), 1.0f / (float)n,
+        if (n) check_rc(pe_frobenius_bwd(rc.data_ptr<float>(), rt.data_ptr<float>(), gl.data_ptr<float>(), (float)(1.0 / (double)n),
                                          da.data_ptr<float>(), nullptr, n, st), "pe_frobenius_bwd");
         return {da, at::Tensor(), at::Tensor(), at::Tensor(), at::Tensor()};
     }
@@ -301,6 +301,225 @@ c10::optional<at::Tensor> frobenius_of_svd_output(const at::Tensor& a, const at:
     return c10::nullopt;
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// The other representations and the generic losses (Comparison/main.py at batch 64: map -> loss_frobenius -> backward
+// took ~186 us through the registered Python ops; these nodes call the same entry points without Python frames).
+
+// (n, w) float32 records with unit inner stride: a view when the rows are dense or wider, else a copy
+at::Tensor records_w(const at::Tensor& x, int64_t w, int64_t* stride) {
+    TORCH_CHECK(x.is_cuda(), "pe_b200 ops compute on CUDA tensors; there is no CPU path");
+    TORCH_CHECK(x.scalar_type() == at::kFloat, "pe_b200 ops compute in float32; got ", x.scalar_type());
+    TORCH_CHECK(x.dim() == 2 && x.size(1) == w, "expected a (n, ", w, ") tensor, got ", x.sizes());
+    *stride = w;
+    if (x.size(0) <= 1 || x.stride(1) != 1 || x.stride(0) < w) return x.contiguous();
+    *stride = x.stride(0);
+    return x;
+}
+
+using MapFwdFn = int (*)(const float*, int64_t, float*, int64_t, void*);
+using MapBwdFn = int (*)(const float*, int64_t, const float*, float*, int64_t, void*);
+struct MapEntry {
+    const char* name;
+    int64_t width;
+    MapFwdFn fwd;
+    MapBwdFn bwd;
+};
+// ids as ops.MAP_IDS / PE_MAP_* of include/pe_rotation.h (0 = SVD has its own nodes above)
+const MapEntry* map_entry(int64_t id) {
+    static const MapEntry table[] = {
+        {"svd", 9, nullptr, nullptr},
+        {"pe_ortho6d", 6, pe_ortho6d_fwd, pe_ortho6d_bwd},
+        {"pe_quat", 4, pe_quat_fwd, pe_quat_bwd},
+        {"pe_euler", 3, pe_euler_fwd, pe_euler_bwd},
+        {"pe_ortho5d", 5, pe_ortho5d_fwd, pe_ortho5d_bwd},
+        {"pe_expmap", 3, pe_expmap_fwd, pe_expmap_bwd},
+    };
+    TORCH_CHECK(id >= 1 && id <= 5, "unknown map id ", id);
+    return &table[id];
+}
+
+// x (n, w) -> R (n, 3, 3); eps > 0 selects so3_exp_map's clamp bound for the exponential map (0: the default 1e-4)
+struct MapNode : public torch::autograd::Function<MapNode> {
+    static at::Tensor forward(torch::autograd::AutogradContext* ctx, const at::Tensor& x_in, int64_t id, double eps) {
+        const MapEntry* e = map_entry(id);
+        TORCH_CHECK(eps == 0.0 || id == PE_MAP_EXPMAP, "eps belongs to the exponential map");
+        int64_t stride = e->width;
+        at::Tensor x = records_w(x_in, e->width, &stride);
+        const int64_t n = x.size(0);
+        const c10::cuda::CUDAGuard guard(x.device());
+        ensure_init(x.device().index());
+        at::Tensor r = at::empty({n, 3, 3}, x.options().requires_grad(false));
+        void* st = c10::cuda::getCurrentCUDAStream(x.device().index()).stream();
+        if (eps != 0.0)
+            check_rc(pe_expmap_eps_fwd(x.data_ptr<float>(), stride, (float)eps, r.data_ptr<float>(), n, st), "pe_expmap_eps_fwd");
+        else
+            check_rc(e->fwd(x.data_ptr<float>(), stride, r.data_ptr<float>(), n, st), e->name);
+        ctx->saved_data["id"] = id;
+        ctx->saved_data["eps"] = eps;
+        ctx->saved_data["stride"] = stride;
+        ctx->save_for_backward({x});
+        return r;
+    }
+    static torch::autograd::variable_list backward(torch::autograd::AutogradContext* ctx,
+                                                   torch::autograd::variable_list grads) {
+        auto saved = ctx->get_saved_variables();
+        const at::Tensor& x = saved[0];
+        const int64_t id = ctx->saved_data["id"].toInt();
+        const double eps = ctx->saved_data["eps"].toDouble();
+        const int64_t stride = ctx->saved_data["stride"].toInt();
+        const MapEntry* e = map_entry(id);
+        const int64_t n = x.size(0);
+        const at::Tensor& g = grads[0];
+        if (!g.defined()) return {at::Tensor(), at::Tensor(), at::Tensor()};
+        TORCH_CHECK(g.numel() == 9 * n, "batch mismatch: ", n, " records but ", g.numel() / 9, " upstream gradients");
+        TORCH_CHECK(g.device() == x.device(), "tensors on different devices: ", x.device(), " and ", g.device());
+        const c10::cuda::CUDAGuard guard(x.device());
+        at::Tensor gc = g.scalar_type() == at::kFloat ? g.contiguous() : g.to(at::kFloat).contiguous();
+        at::Tensor dx = at::empty({n, e->width}, x.options().requires_grad(false));
+        void* st = c10::cuda::getCurrentCUDAStream(x.device().index()).stream();
+        if (eps != 0.0)
+            check_rc(pe_expmap_eps_bwd(x.data_ptr<float>(), stride, gc.data_ptr<float>(), (float)eps, dx.data_ptr<float>(), n, st),
+                     "pe_expmap_eps_bwd");
+        else
+            check_rc(e->bwd(x.data_ptr<float>(), stride, gc.data_ptr<float>(), dx.data_ptr<float>(), n, st), e->name);
+        return {dx, at::Tensor(), at::Tensor()};
+    }
+};
+
+at::Tensor map_fwd(const at::Tensor& x, int64_t id, double eps) { return MapNode::apply(x, id, eps); }
+
+// two dense (n, 9) batches of the SAME length on one device (the kernels read n records of both)
+at::Tensor dense9(const at::Tensor& x) {
+    TORCH_CHECK(x.is_cuda(), "pe_b200 ops compute on CUDA tensors; there is no CPU path");
+    TORCH_CHECK(x.scalar_type() == at::kFloat, "pe_b200 ops compute in float32; got ", x.scalar_type());
+    TORCH_CHECK((x.dim() == 3 && x.size(1) == 3 && x.size(2) == 3) || (x.dim() == 2 && x.size(1) == 9),
+                "expected (n, 3, 3) matrices, got ", x.sizes());
+    return x.contiguous();
+}
+void same_batch(const at::Tensor& a, const at::Tensor& b) {
+    TORCH_CHECK(a.size(0) == b.size(0), "batch mismatch: ", a.size(0), " and ", b.size(0), " matrices");
+    TORCH_CHECK(a.device() == b.device(), "tensors on different devices: ", a.device(), " and ", b.device());
+}
+
+// loss_frobenius on two materialised batches (Comparison/main.py:12-16): mean_b |a_b - b_b|_F, 0-d float32
+struct FrobeniusMean : public torch::autograd::Function<FrobeniusMean> {
+    static at::Tensor forward(torch::autograd::AutogradContext* ctx, const at::Tensor& a_in, const at::Tensor& b_in) {
+        at::Tensor a = dense9(a_in), b = dense9(b_in);
+        same_batch(a, b);
+        const int64_t n = a.size(0);
+        const c10::cuda::CUDAGuard guard(a.device());
+        ensure_init(a.device().index());
+        at::Tensor loss = at::empty({}, a.options().requires_grad(false));
+        if (n == 0) {
+            loss.fill_(std::numeric_limits<float>::quiet_NaN());
+        } else {
+            at::Tensor sum = at::empty({1}, a.options().dtype(at::kDouble).requires_grad(false));
+            void* st = c10::cuda::getCurrentCUDAStream(a.device().index()).stream();
+            check_rc(pe_frobenius_mean_fwd(a.data_ptr<float>(), b.data_ptr<float>(), sum.data_ptr<double>(),
+                                           loss.data_ptr<float>(), n, st), "pe_frobenius_mean_fwd");
+        }
+        ctx->save_for_backward({a, b});
+        ctx->saved_data["a_sizes"] = a_in.sizes().vec();
+        ctx->saved_data["b_sizes"] = b_in.sizes().vec();
+        return loss;
+    }
+    static torch::autograd::variable_list backward(torch::autograd::AutogradContext* ctx,
+                                                   torch::autograd::variable_list grads) {
+        auto saved = ctx->get_saved_variables();
+        const at::Tensor &a = saved[0], &b = saved[1];
+        const int64_t n = a.size(0);
+        const bool na = ctx->needs_input_grad(0), nb = ctx->needs_input_grad(1);
+        if (!grads[0].defined() || !(na || nb)) return {at::Tensor(), at::Tensor()};
+        const c10::cuda::CUDAGuard guard(a.device());
+        at::Tensor g = scalar32(grads[0]);
+        at::Tensor da, db;
+        if (na) da = at::empty(ctx->saved_data["a_sizes"].toIntVector(), a.options().requires_grad(false));
+        if (nb) db = at::empty(ctx->saved_data["b_sizes"].toIntVector(), a.options().requires_grad(false));
+        if (n) {
+            void* st = c10::cuda::getCurrentCUDAStream(a.device().index()).stream();
+            check_rc(pe_frobenius_bwd(a.data_ptr<float>(), b.data_ptr<float>(), g.data_ptr<float>(), (float)(1.0 / (double)n),
+                                      na ? da.data_ptr<float>() : nullptr, nb ? db.data_ptr<float>() : nullptr, n, st),
+                     "pe_frobenius_bwd");
+        }
+        return {da, db};
+    }
+};
+
+at::Tensor frobenius_mean(const at::Tensor& a, const at::Tensor& b) { return FrobeniusMean::apply(a, b); }
+
+// geodesic(R1, R2, reduction) of point_cloud/main.py:61-73 and compute_geodesic_distance_from_two_matrices
+// (rotation_representation.py:209-227).  mode 0: per-record theta (n,), 1: mean, 2: sum (0-d float32)
+struct Geodesic : public torch::autograd::Function<Geodesic> {
+    static at::Tensor forward(torch::autograd::AutogradContext* ctx, const at::Tensor& a_in, const at::Tensor& b_in,
+                              double lo, double hi, int64_t mode) {
+        at::Tensor a = dense9(a_in), b = dense9(b_in);
+        same_batch(a, b);
+        TORCH_CHECK(mode >= 0 && mode <= 2, "mode: 0 none, 1 mean, 2 sum");
+        const int64_t n = a.size(0);
+        const c10::cuda::CUDAGuard guard(a.device());
+        ensure_init(a.device().index());
+        void* st = c10::cuda::getCurrentCUDAStream(a.device().index()).stream();
+        at::Tensor out;
+        if (mode == 0) {
+            out = at::empty({n}, a.options().requires_grad(false));
+            if (n) check_rc(pe_geodesic_fwd(a.data_ptr<float>(), b.data_ptr<float>(), (float)lo, (float)hi, out.data_ptr<float>(),
+                                            nullptr, n, st), "pe_geodesic_fwd");
+        } else {
+            out = at::empty({}, a.options().requires_grad(false));
+            if (n == 0) {
+                out.fill_(mode == 1 ? std::numeric_limits<float>::quiet_NaN() : 0.0f);
+            } else {
+                at::Tensor sum = at::empty({1}, a.options().dtype(at::kDouble).requires_grad(false));
+                check_rc(pe_geodesic_reduce_fwd(a.data_ptr<float>(), b.data_ptr<float>(), (float)lo, (float)hi,
+                                                sum.data_ptr<double>(), out.data_ptr<float>(), mode == 1 ? 1.0 / (double)n : 1.0, n, st),
+                         "pe_geodesic_reduce_fwd");
+            }
+        }
+        ctx->save_for_backward({a, b});
+        ctx->saved_data["lo"] = lo;
+        ctx->saved_data["hi"] = hi;
+        ctx->saved_data["mode"] = mode;
+        ctx->saved_data["a_sizes"] = a_in.sizes().vec();
+        ctx->saved_data["b_sizes"] = b_in.sizes().vec();
+        return out;
+    }
+    static torch::autograd::variable_list backward(torch::autograd::AutogradContext* ctx,
+                                                   torch::autograd::variable_list grads) {
+        auto saved = ctx->get_saved_variables();
+        const at::Tensor &a = saved[0], &b = saved[1];
+        const int64_t n = a.size(0);
+        const int64_t mode = ctx->saved_data["mode"].toInt();
+        const bool na = ctx->needs_input_grad(0), nb = ctx->needs_input_grad(1);
+        torch::autograd::variable_list none = {at::Tensor(), at::Tensor(), at::Tensor(), at::Tensor(), at::Tensor()};
+        if (!grads[0].defined() || !(na || nb)) return none;
+        const c10::cuda::CUDAGuard guard(a.device());
+        at::Tensor g;
+        if (mode == 0) {
+            TORCH_CHECK(grads[0].numel() == n, grads[0].numel(), " upstream gradients for ", n, " matrices");
+            g = grads[0].to(at::kFloat).reshape({-1}).contiguous();
+        } else {
+            g = scalar32(grads[0]);
+        }
+        at::Tensor da, db;
+        if (na) da = at::empty(ctx->saved_data["a_sizes"].toIntVector(), a.options().requires_grad(false));
+        if (nb) db = at::empty(ctx->saved_data["b_sizes"].toIntVector(), a.options().requires_grad(false));
+        if (n) {
+            void* st = c10::cuda::getCurrentCUDAStream(a.device().index()).stream();
+            check_rc(pe_geodesic_bwd(a.data_ptr<float>(), b.data_ptr<float>(), (float)ctx->saved_data["lo"].toDouble(),
+                                     (float)ctx->saved_data["hi"].toDouble(), g.data_ptr<float>(), mode == 0 ? 0 : 1,
+                                     mode == 1 ? (float)(1.0 / (double)n) : 1.0f, na ? da.data_ptr<float>() : nullptr,
+                                     nb ? db.data_ptr<float>() : nullptr, n, st), "pe_geodesic_bwd");
+        }
+        none[0] = da;
+        none[1] = db;
+        return none;
+    }
+};
+
+at::Tensor geodesic(const at::Tensor& a, const at::Tensor& b, double lo, double hi, int64_t mode) {
+    return Geodesic::apply(a, b, lo, hi, mode);
+}
+
 std::vector<at::Tensor> fused_step_loss(const at::Tensor& x, const at::Tensor& r_true, bool with_angle) {
     return FusedStep::apply(x, r_true, with_angle);
 }
@@ -311,6 +530,12 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
     m.def("fused_step_loss", &fused_step_loss, "loss (and mean angle error, range flag) of the step; differentiable in x",
           py::arg("x"), py::arg("r_true"), py::arg("with_angle"));
     m.def("svd_orth", &svd_orth, "symmetric_orthogonalization of (n, 9) records as a C++ autograd node", py::arg("x"));
+    m.def("map_fwd", &map_fwd, "representation -> rotation as a C++ autograd node (map id as PE_MAP_*; eps: exp-map clamp, 0 = default)",
+          py::arg("x"), py::arg("map_id"), py::arg("eps") = 0.0);
+    m.def("frobenius_mean", &frobenius_mean, "loss_frobenius on two materialised batches as a C++ autograd node", py::arg("a"),
+          py::arg("b"));
+    m.def("geodesic", &geodesic, "geodesic distance, mode 0 none / 1 mean / 2 sum, as a C++ autograd node", py::arg("a"),
+          py::arg("b"), py::arg("lo"), py::arg("hi"), py::arg("mode"));
     m.def("frobenius_of_svd_output", &frobenius_of_svd_output,
           "loss_frobenius(a, b) through the single-pass step when one argument is an untouched svd_orth output, else None",
           py::arg("a"), py::arg("b"));

@@ -487,11 +487,16 @@ def _(m1, m2, lo, hi):
 @torch.library.custom_op(f"{NS}::geodesic_reduce", mutates_args=(), device_types="cuda")
 def geodesic_reduce(m1: Tensor, m2: Tensor, lo: float, hi: float, mean: bool) -> Tensor:
     """0-d float32 mean or sum of theta, differentiable."""
-    n = _mat(m1).shape[0]
-    s = geodesic_sum(m1, m2, lo, hi)
-    if mean:
-        s = s / n if n else s * float("nan")
-    return s.to(torch.float32).reshape(())
+    m1, m2 = _mat_pair(m1, m2)
+    n = m1.shape[0]
+    if not n:
+        return torch.full((), float("nan") if mean else 0.0, dtype=torch.float32, device=m1.device)
+    s = torch.empty((1,), dtype=torch.float64, device=m1.device)
+    out = torch.empty((), dtype=torch.float32, device=m1.device)
+    with torch.cuda.device(m1.device):            # sum and its float32 mean / sum leave the kernel together: one launch
+        check(lib.pe_geodesic_reduce_fwd(m1.data_ptr(), m2.data_ptr(), lo, hi, s.data_ptr(), out.data_ptr(),
+                                         (1.0 / n) if mean else 1.0, n, _stream()), "pe_geodesic_reduce_fwd")
+    return out
 
 
 @geodesic_reduce.register_fake

@@ -57,26 +57,47 @@ def symmetric_orthogonalization(x):
     return r
 
 
+def _plain_cuda_f32(t) -> bool:
+    return type(t) in (torch.Tensor, torch.nn.Parameter) and t.is_cuda and t.dtype == torch.float32
+
+
+def _cpp_nodes() -> bool:
+    """the C++ autograd nodes of csrc/pe_torch.cpp serve eager calls that will be differentiated; everything else (no
+    gradient, traced graphs, tensor subclasses, argument errors) goes through the registered ops of ops.py"""
+    return _ops._C is not None and torch.is_grad_enabled() and not torch.compiler.is_compiling()
+
+
+def _map(x2d, map_id: int, op, eps: float = 0.0):
+    if x2d.requires_grad and _plain_cuda_f32(x2d) and _cpp_nodes():
+        return _ops._C.map_fwd(x2d, map_id, eps)    # same kernels, no Python frames in forward / backward
+    return op(x2d) if eps == 0.0 else op(x2d, eps)
+
+
+def _pair_for_cpp(a, b) -> bool:
+    return (_plain_cuda_f32(a) and _plain_cuda_f32(b) and (a.requires_grad or b.requires_grad) and a.device == b.device
+            and a.shape == b.shape and (a.shape[1:] == (3, 3) or (a.dim() == 2 and a.shape[1] == 9)) and _cpp_nodes())
+
+
 def compute_rotation_matrix_from_ortho6d(poses):
     """Gram-Schmidt 6D map, columns (x, y, z) (rotation_representation.py:21-36 = 174-189).  [..., 6] -> [..., 3, 3]."""
     assert poses.shape[-1] == 6                   # :28
     lead = poses.shape[:-1]
-    return _ops.ortho6d(poses.reshape(-1, 6)).reshape(*lead, 3, 3)
+    return _map(poses.reshape(-1, 6), 1, _ops.ortho6d).reshape(*lead, 3, 3)
 
 
 def compute_rotation_matrix_from_quaternion(quaternion):
     """(B, 4) quaternions (w, x, y, z), norm floored at 1e-8 -> (B, 3, 3) (rotation_representation.py:139-172)."""
-    return _ops.quat(quaternion.reshape(-1, 4))
+    return _map(quaternion.reshape(-1, 4), 2, _ops.quat)
 
 
 def compute_rotation_matrix_from_euler(euler):
     """(B, 3) -> (B, 3, 3) with the reference's angle order (rotation_representation.py:92-115)."""
-    return _ops.euler(euler.reshape(-1, 3))
+    return _map(euler.reshape(-1, 3), 3, _ops.euler)
 
 
 def compute_rotation_matrix_from_ortho5d(a):
     """(B, 5) -> (B, 3, 3) (rotation_representation.py:120-136)."""
-    return _ops.ortho5d(a.reshape(-1, 5))
+    return _map(a.reshape(-1, 5), 4, _ops.ortho5d)
 
 
 def so3_exp_map(log_rot, eps: float = 0.0001):
@@ -84,8 +105,8 @@ def so3_exp_map(log_rot, eps: float = 0.0001):
     if log_rot.dim() != 2 or log_rot.shape[1] != 3:
         raise ValueError("Input tensor shape has to be Nx3.")           # :255-256
     if eps == 0.0001:
-        return _ops.expmap(log_rot)
-    return _ops.expmap_eps(log_rot, float(eps))
+        return _map(log_rot, 5, _ops.expmap)
+    return _map(log_rot, 5, _ops.expmap_eps, float(eps))
 
 
 def vec_3d_to_SO3(x):
@@ -130,12 +151,16 @@ def hat(v):
 # distances and losses on SO(3)
 def compute_geodesic_distance_from_two_matrices(m1, m2):
     """acos(clamp((tr(m1 m2^T) - 1)/2, -1, 1)), radians, (B,) float32 (rotation_representation.py:209-227)."""
+    if _pair_for_cpp(m1, m2):
+        return _ops._C.geodesic(m1, m2, -1.0, 1.0, 0)
     return _ops.geodesic_theta(m1, m2, -1.0, 1.0)
 
 
 def geodesic(R1, R2, reduction="mean"):
     """point_cloud/main.py:61-73: clamp at +-(1 - 1e-7); ``none`` | ``mean`` | ``sum``."""
     eps = 1e-7
+    if reduction in ("none", "mean", "sum") and _pair_for_cpp(R1, R2):
+        return _ops._C.geodesic(R1, R2, -1 + eps, 1 - eps, ("none", "mean", "sum").index(reduction))
     if reduction == "none":
         return _ops.geodesic_theta(R1, R2, -1 + eps, 1 - eps)
     if reduction == "mean":
@@ -216,6 +241,8 @@ def loss_frobenius(R_pred, R_true):
         fused = _ops.frobenius_of_svd_output(R_pred, R_true)            # outputs of the Python svd_orth node
         if fused is not None:
             return fused
+        if _pair_for_cpp(R_pred, R_true):
+            return _ops._C.frobenius_mean(R_pred, R_true)               # generic pair, C++ node
     return _ops.frobenius_mean(R_pred, R_true)
 
 

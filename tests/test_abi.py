@@ -57,6 +57,8 @@ def test_ctypes_table_matches_header(built):
                 assert ct is ctypes.c_int64, (name, c_decl)
             elif c_decl.startswith("float"):
                 assert ct is ctypes.c_float, (name, c_decl)
+            elif c_decl.startswith("double"):
+                assert ct is ctypes.c_double, (name, c_decl)
             elif c_decl.startswith("int"):
                 assert ct is ctypes.c_int, (name, c_decl)
             else:

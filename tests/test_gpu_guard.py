@@ -117,6 +117,13 @@ def test_record_kernels_stay_inside_their_outputs(abi, n, off):
     _call(abi, "pe_geodesic_fwd", rot.ptr, rot2.ptr, -1.0, 1.0, th.ptr, s.ptr, n, st)
     theta = _inp(th.f32(n).clone(), off)
     done("pe_geodesic_fwd")
+    s2, mean = out(2, f64=True), out(1)
+    _call(abi, "pe_geodesic_reduce_fwd", rot.ptr, rot2.ptr, -1.0, 1.0, s2.ptr, mean.ptr, 1.0 / n, n, st)
+    torch.cuda.synchronize()
+    ref = float(s2.words().view(torch.float64)[0]) / n
+    assert abs(float(mean.f32(1)[0]) - ref) <= 1.2e-7 * abs(ref)
+    assert abs(float(s2.words().view(torch.float64)[0]) - float(s.words().view(torch.float64)[0])) <= 1e-9 * n
+    done("pe_geodesic_reduce_fwd")
     for scalar in (0, 1):
         d1, d2 = out(9 * n), out(9 * n)
         gsrc = one if scalar else theta

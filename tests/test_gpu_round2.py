@@ -321,6 +321,91 @@ def test_cpp_autograd_node_equals_the_python_node(rr, ops):
     assert type(loss.grad_fn).__name__ == "CppFunction" and "FusedStep" in repr(loss)
 
 
+def _graph_names(t):
+    """names of the autograd nodes behind a tensor"""
+    seen, todo, names = set(), [t.grad_fn], set()
+    while todo:
+        fn = todo.pop()
+        if fn is None or fn in seen:
+            continue
+        seen.add(fn)
+        names.add(fn.name())
+        todo.extend(f for f, _ in fn.next_functions)
+    return " ".join(sorted(names))
+
+
+@pytest.mark.parametrize("key,width", [("6D", 6), ("Quat", 4), ("Euler", 3), ("5D", 5), ("3D", 3), ("3D-eps", 3)])
+def test_cpp_map_and_loss_nodes_equal_the_python_route(rr, ops, monkeypatch, key, width):
+    """The maps, loss_frobenius on a generic pair and geodesic() as C++ autograd nodes (csrc/pe_torch.cpp) against the
+    registered Python ops: the same entry points of the C ABI, so values and gradients are bit-identical - for every
+    reduction, a strided input, an upstream gradient other than one, gradients towards either argument, an empty batch."""
+    if ops._C is None:
+        pytest.skip("_pe_torch.so not built")
+    fns = {"6D": rr.compute_rotation_matrix_from_ortho6d, "Quat": rr.compute_rotation_matrix_from_quaternion,
+           "Euler": rr.compute_rotation_matrix_from_euler, "5D": rr.compute_rotation_matrix_from_ortho5d,
+           "3D": rr.so3_exp_map, "3D-eps": lambda v: rr.so3_exp_map(v, 1e-2)}
+    fn = fns[key]
+    g = torch.Generator(device="cuda").manual_seed(width)
+    n = 2049
+    base = torch.randn(n, width + 3, device="cuda", generator=g)
+    rt = rr.symmetric_orthogonalization(torch.randn(n, 9, device="cuda", generator=g))
+    w = torch.randn(n, device="cuda", generator=g)
+
+    def run(strided, loss_kind, cpp):
+        if not cpp:
+            monkeypatch.setattr(ops, "_C", None)
+        leaf = (base if strided else base[:, :width].contiguous()).detach().clone().requires_grad_(True)
+        x = leaf[:, :width] if strided else leaf
+        target = rt.detach().clone().requires_grad_(True)      # gradients towards BOTH arguments
+        r = fn(x)
+        if loss_kind == "frobenius":
+            loss = rr.loss_frobenius(r, target)
+        elif loss_kind == "none":
+            loss = (rr.geodesic(r, target, "none") * w).sum()
+        elif loss_kind == "a6":
+            loss = (rr.compute_geodesic_distance_from_two_matrices(r, target) * w).sum()
+        else:
+            loss = rr.geodesic(r, target, loss_kind)
+        (loss * 1.75).backward()
+        monkeypatch.undo()
+        return r.detach(), loss.detach(), leaf.grad, target.grad, _graph_names(r), _graph_names(loss)
+
+    for strided in (False, True):
+        for kind in ("frobenius", "mean", "sum", "none", "a6"):
+            rc, lc, gc, tc, rep_r, rep_l = run(strided, kind, True)
+            rp, lp, gp, tp, rep_rp, _ = run(strided, kind, False)
+            assert "MapNode" in rep_r and "MapNode" not in rep_rp
+            if kind in ("frobenius", "mean", "sum"):
+                assert ("FrobeniusMean" if kind == "frobenius" else "Geodesic") in rep_l
+                assert lc.dim() == 0 and lc.dtype == torch.float32
+            assert torch.equal(rc, rp) and lc.item() == lp.item()
+            # bitwise (int32 views): the clamp of a6 is +-1 exactly, where acos' has no finite derivative - a record that
+            # lands there gives inf / NaN on both routes, as it does in the reference
+            bits = lambda t: t.contiguous().view(torch.int32)
+            assert torch.equal(bits(gc), bits(gp)) and torch.equal(bits(tc), bits(tp)) and gc.nan_to_num().abs().max().item() > 0
+    # no gradient asked for: the registered op (no node), same numbers
+    with_grad = run(True, "mean", True)[0]
+    with torch.no_grad():
+        assert torch.equal(fn(base[:, :width]), with_grad)
+    assert fn(base[:, :width].contiguous()).grad_fn is None
+    # an empty batch
+    e = torch.zeros(0, width, device="cuda", requires_grad=True)
+    re_ = fn(e)
+    assert re_.shape == (0, 3, 3)
+    t0 = torch.zeros(0, 3, 3, device="cuda")
+    assert torch.isnan(rr.loss_frobenius(re_, t0)) and torch.isnan(rr.geodesic(re_, t0, "mean"))
+    s0 = rr.geodesic(re_, t0, "sum")
+    assert s0.item() == 0.0
+    s0.backward()
+    assert e.grad.shape == (0, width)
+    # argument errors are the Python route's (ValueError / TypeError), whichever nodes are built
+    x = base[:, :width].contiguous().requires_grad_(True)
+    with pytest.raises(ValueError, match="batch mismatch"):
+        rr.loss_frobenius(fn(x), rt[:7])
+    with pytest.raises(TypeError):
+        fn(x.double())
+
+
 # ---------------------------------------------------------------------------------------------------------------------
 # launch slots: streams, graphs
 def test_graph_replay_next_to_eager_launches_on_another_stream(abi, rr):

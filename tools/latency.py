@@ -156,8 +156,32 @@ def main():
                               "kabsch_fwd_cuda_graph_us": round(timed(graph.replay, args.reps), 2),
                               "kabsch_weighted_fwd_us": round(timed(lambda: rr.kabsch(p, q, weights=w), args.reps), 2),
                               "kabsch_fwd_bwd_us": round(timed(fwd_bwd, args.reps), 2)}
+    # the other representations of Comparison/main.py at its batch size: map -> loss_frobenius -> backward
+    maps = {}
+    b = 64
+    rt = rr.symmetric_orthogonalization(torch.randn(b, 9, device=dev)).detach()
+    for key, width, fn in (("6D", 6, rr.compute_rotation_matrix_from_ortho6d), ("Quat", 4, rr.compute_rotation_matrix_from_quaternion),
+                           ("Euler", 3, rr.compute_rotation_matrix_from_euler), ("5D", 5, rr.compute_rotation_matrix_from_ortho5d),
+                           ("3D", 3, rr.so3_exp_map)):
+        xm = torch.randn(b, width, device=dev, requires_grad=True)
+
+        def step(fn=fn, xm=xm):
+            xm.grad = None
+            rr.loss_frobenius(fn(xm), rt).backward()
+
+        def step_geo(fn=fn, xm=xm):
+            xm.grad = None
+            rr.geodesic(fn(xm), rt).backward()
+
+        def fwd_only(fn=fn, xm=xm):
+            with torch.no_grad():
+                fn(xm)
+
+        maps[key] = {"map_frobenius_step_us": round(timed(step, args.reps), 2),
+                     "map_geodesic_step_us": round(timed(step_geo, args.reps), 2),
+                     "map_forward_no_grad_us": round(timed(fwd_only, args.reps), 2)}
     print(json.dumps({"what": "microseconds per call, wall clock, 1 B200", "reps": args.reps, "batch": res,
-                      "kabsch": kab}))
+                      "kabsch": kab, "maps_batch64": maps}))
 
 
 if __name__ == "__main__":
