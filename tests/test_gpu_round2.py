@@ -543,6 +543,10 @@ def test_repeated_launches_are_bitwise_stable(abi, rr):
                                                                         None, None, None, n, st), out),
         "step_metrics_wide": (lambda: lib.pe_svd_orth_frobenius_step_metrics(P(wide), 12, P(rt), 1.0 / n, P(out),
                                                                              P(sums), None, None, None, None, n, st), out),
+        # the split wide ring without an output (in[1] re-armed behind barrier (A)) and with the R output in place
+        "svd_angle_metric_wide": (lambda: lib.pe_map_metric_fwd(0, 2, P(wide), 12, P(rt), -1.0, 1.0, P(sums), P(flag), n, st),
+                                  sums),
+        "svd_frobenius_fwd_wide": (lambda: lib.pe_svd_orth_frobenius_fwd(P(wide), 12, P(rt), P(out), P(sums), n, st), out),
         "ortho6d_fwd": (lambda: lib.pe_ortho6d_fwd(P(x6), 6, P(out), n, st), out),
         "ortho6d_bwd": (lambda: lib.pe_ortho6d_bwd(P(x6), 6, P(up), P(out6), n, st), out6),
         "angle_error": (lambda: lib.pe_angle_error_fwd(P(rt), P(rt2), P(deg), P(sums), P(flag), n, st), deg),
