@@ -6,6 +6,7 @@
 typedef unsigned long long u64;
 #define FMA2(d, a, b, c) asm volatile("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c))
 #define MUL2(d, a, b) asm volatile("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b))
+#define MUFU(d, a) asm volatile("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(d) : "f"(a))
 #define FMA1(d, a, b, c) asm volatile("fma.rn.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c))
 constexpr int NACC = 8, ITERS = 4096;
 
@@ -29,6 +30,11 @@ __global__ void k(u64* out, long long* cyc, u64 seed) {
             if (MODE == 4) FMA1(fa[i], fx[i], fy[i], fa[i]);            // scalar FFMA, 3 distinct
             if (MODE == 5) FMA2(acc[i], x[i], y[(i + 1) % NACC], acc[i]);  // 3 distinct, other pairing
             if (MODE == 6) FMA2(acc[i], x[0], y[i], acc[i]);            // one shared multiplicand (like cos/sin)
+            // do the packed and the scalar instructions share one pipe?  MODE 7: one FFMA2 + one scalar FFMA per slot
+            // (2 instructions), MODE 8: one FFMA2 + two scalar FFMA (3 instructions); cycles are reported per SLOT
+            if (MODE == 7 || MODE == 8) { FMA2(acc[i], x[i], y[i], acc[i]); FMA1(fa[i], fx[i], fy[i], fa[i]); }
+            if (MODE == 8) FMA1(fx[i], fa[i], fy[i], fx[i]);
+            if (MODE == 9) { FMA2(acc[i], x[i], y[i], acc[i]); MUFU(fa[i], fa[i]); }   // packed FMA + MUFU.RSQ per slot
         }
     }
     long long t1 = clock64();
@@ -61,6 +67,9 @@ int main() {
         run<2>("FFMA2 1 distinct", threads);
         run<3>("FMUL2 2 distinct", threads);
         run<4>("FFMA scalar 3 distinct", threads);
+        run<7>("slot = FFMA2 (3 distinct) + 1 scalar FFMA", threads);
+        run<8>("slot = FFMA2 (3 distinct) + 2 scalar FFMA", threads);
+        run<9>("slot = FFMA2 (3 distinct) + 1 MUFU.RSQ", threads);
     }
     return 0;
 }
