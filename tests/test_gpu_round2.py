@@ -406,6 +406,35 @@ def test_cpp_map_and_loss_nodes_equal_the_python_route(rr, ops, monkeypatch, key
         fn(x.double())
 
 
+def test_autograd_routes_do_not_accumulate_memory(rr, route):
+    """300 training steps through every differentiable route (the SVD two-call surface, the fused step, a map with each
+    loss, a loss whose backward never runs): the caching allocator's live bytes return to where they were - the nodes,
+    the parked gradients and the saved inputs are all released."""
+    g = torch.Generator(device="cuda").manual_seed(2)
+    n = 257
+    x9 = torch.randn(n, 12, device="cuda", generator=g, requires_grad=True)
+    x6 = torch.randn(n, 6, device="cuda", generator=g, requires_grad=True)
+    rt = rr.symmetric_orthogonalization(torch.randn(n, 9, device="cuda", generator=g)).detach()
+
+    def steps():
+        for _ in range(300):
+            x9.grad = x6.grad = None
+            rr.loss_frobenius(rr.symmetric_orthogonalization(x9[:, :9]), rt).backward()
+            rr.svd_frobenius_loss(x9[:, :9], rt, with_angle=True, check=False)[0].backward()
+            r6 = rr.compute_rotation_matrix_from_ortho6d(x6)
+            (rr.loss_frobenius(r6, rt) + rr.geodesic(r6, rt, "mean")).backward()
+            rr.loss_frobenius(rr.symmetric_orthogonalization(x9[:, :9]), rt)      # graph dropped without a backward
+            rr.geodesic(rr.compute_rotation_matrix_from_quaternion(x6[:, :4]), rt, "none")
+        x9.grad = x6.grad = None
+
+    steps()                                   # warm the allocator and the per-device state
+    torch.cuda.synchronize()
+    before = torch.cuda.memory_allocated()
+    steps()
+    torch.cuda.synchronize()
+    assert torch.cuda.memory_allocated() == before
+
+
 # ---------------------------------------------------------------------------------------------------------------------
 # launch slots: streams, graphs
 def test_graph_replay_next_to_eager_launches_on_another_stream(abi, rr):
