@@ -406,6 +406,53 @@ def test_cpp_map_and_loss_nodes_equal_the_python_route(rr, ops, monkeypatch, key
         fn(x.double())
 
 
+def test_autograd_routes_on_a_side_stream_and_from_threads(rr, route):
+    """forward on a side stream, backward on the autograd engine's thread (which restores the forward's stream); and four
+    host threads stepping at once, each on its own stream: same loss and gradient as the plain call, bit for bit"""
+    import threading
+    g = torch.Generator(device="cuda").manual_seed(4)
+    n = 70001
+    x = torch.randn(n, 9, device="cuda", generator=g)
+    x6 = torch.randn(n, 6, device="cuda", generator=g)
+    rt = rr.symmetric_orthogonalization(torch.randn(n, 9, device="cuda", generator=g)).detach()
+
+    def step():
+        a, b = x.clone().requires_grad_(True), x6.clone().requires_grad_(True)
+        loss = rr.loss_frobenius(rr.symmetric_orthogonalization(a), rt) + \
+            rr.geodesic(rr.compute_rotation_matrix_from_ortho6d(b), rt, "mean")
+        loss.backward()
+        return loss.detach(), a.grad, b.grad
+
+    want = step()
+    torch.cuda.synchronize()
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        got = step()
+    side.synchronize()
+    assert got[0].item() == want[0].item() and torch.equal(got[1], want[1]) and torch.equal(got[2], want[2])
+    results, errors = [None] * 4, []
+
+    def worker(i):
+        try:
+            s = torch.cuda.Stream()
+            with torch.cuda.stream(s):
+                for _ in range(20):
+                    results[i] = step()
+            s.synchronize()
+        except Exception as e:                                 # noqa: BLE001
+            errors.append(e)
+
+    threads = [threading.Thread(target=worker, args=(i,)) for i in range(4)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not errors, errors
+    for r in results:
+        assert r[0].item() == want[0].item() and torch.equal(r[1], want[1]) and torch.equal(r[2], want[2])
+
+
 def test_autograd_routes_do_not_accumulate_memory(rr, route):
     """300 training steps through every differentiable route (the SVD two-call surface, the fused step, a map with each
     loss, a loss whose backward never runs): the caching allocator's live bytes return to where they were - the nodes,
