@@ -5,6 +5,7 @@ and does not finish these sizes in seconds, so a strided sample goes to it and t
   kernel (checksum of checksums); invariance of the angle under a common left rotation; the maps' own symmetries;
 * config 4 (65 536 clouds x 1024 points): sampler -> rotate_cloud -> kabsch round trip, the Kabsch backward as a
   directional derivative, rotate_cloud against torch.bmm;
+* config 5 at N = 1 (2^30 matrices resident, 116 GB): one launch == its sixteen chunks, means at their expectations;
 * the refiner losses at 4096 meshes x 8192 vertices: ADD-L1 against the reference's own formula evaluated with torch
   ops on the device (Iterative/loss.py:10-69), identical poses -> 0, the pure-translation closed form.
 
@@ -336,3 +337,56 @@ def test_config2_training_step_with_metric_full_size(rr):
     sc = np.abs(want).max(1)
     rel = np.abs(got - want).max(1) / np.maximum(sc, 0.1 * np.median(sc))
     assert rel[cond > 0.1].max() <= 1e-4
+
+
+def test_config5_one_launch_over_2_30_matrices_equals_its_chunks(rr):
+    """BASELINE config 5 at N = 1: 2^30 matrices resident (3 arrays x 38.7 GB; 9.7e9 words per array, beyond 32-bit
+    indexing).  One launch of the step with its metric must equal, chunk by chunk, sixteen launches over 2^26 matrices:
+    gradients bit for bit (same kernel, same 1/n), the three sums to float64 round-off (a checksum of checksums), and
+    the means must sit at their expectations for uniformly random rotation pairs.  Skipped when the device does not
+    have the memory free (the bench's config5 leg makes the same check)."""
+    from poseestimation_b200 import _lib
+    lib, check = _lib.lib, _lib.check
+    n, chunk = 1 << 30, 1 << 26
+    torch.cuda.empty_cache()
+    free_b, _ = torch.cuda.mem_get_info()
+    need = 3 * n * 36 + (12 << 30)
+    if free_b < need:
+        pytest.skip(f"needs {need / 1e9:.0f} GB of device memory, {free_b / 1e9:.0f} GB free")
+    _lib.init_device(torch.cuda.current_device())
+    st = torch.cuda.current_stream().cuda_stream
+    x = torch.empty(n, 9, device="cuda")
+    rt = torch.empty(n, 9, device="cuda")
+    g = torch.Generator(device="cuda").manual_seed(30)
+    for c in range(n // chunk):
+        x[c * chunk:(c + 1) * chunk].normal_(generator=g)
+        q = torch.randn(chunk, 4, device="cuda", generator=g)
+        rt[c * chunk:(c + 1) * chunk] = rr.compute_rotation_matrix_from_quaternion(q).view(chunk, 9)
+        del q
+    dx = torch.empty(n, 9, device="cuda")
+    sums = torch.zeros(3, dtype=torch.float64, device="cuda")
+    check(lib.pe_svd_orth_frobenius_step_metrics(x.data_ptr(), 9, rt.data_ptr(), 1.0 / n, dx.data_ptr(), sums.data_ptr(),
+                                                 None, None, None, None, n, st), "step over 2^30")
+    torch.cuda.synchronize()
+    part = torch.zeros(3, dtype=torch.float64, device="cuda")
+    total = torch.zeros(3, dtype=torch.float64, device="cuda")
+    dxc = torch.empty(chunk, 9, device="cuda")
+    for c in range(n // chunk):
+        lo = c * chunk
+        check(lib.pe_svd_orth_frobenius_step_metrics(x[lo:].data_ptr(), 9, rt[lo:].data_ptr(), 1.0 / n, dxc.data_ptr(),
+                                                     part.data_ptr(), None, None, None, None, chunk, st), "chunk")
+        total += part
+        assert torch.equal(dx[lo:lo + chunk], dxc), f"gradient of chunk {c} differs"
+    assert total[2].item() == 0.0 and sums[2].item() == 0.0                      # no cosine out of range
+    assert abs(total[0].item() - sums[0].item()) <= 1e-11 * sums[0].item()
+    assert abs(total[1].item() - sums[1].item()) <= 1e-11 * sums[1].item()
+    # uniformly random pairs: E[angle] = pi/2 + 2/pi rad; sigma of the mean over 2^30 pairs ~ 0.0011 degrees
+    assert abs(sums[1].item() / n - math.degrees(math.pi / 2 + 2 / math.pi)) <= 0.01
+    # |R - R_t|_F = 2 sqrt(2) sin(theta / 2); its mean over the same distribution (density (1 - cos t) / pi):
+    # (2 sqrt 2 / pi) * int_0^pi sin(t/2)(1 - cos t) dt = (2 sqrt 2 / pi) * 8/3
+    assert abs(sums[0].item() / n - (2 * math.sqrt(2) / math.pi) * (8 / 3)) <= 2e-4
+    # the last matrices of the array (word offsets beyond 2^33) are proper rotations' tangents: finite and non-zero
+    tail = dx[-4096:]
+    assert torch.isfinite(tail).all() and (tail.abs().amax(dim=1) > 0).all()
+    del x, rt, dx, dxc
+    torch.cuda.empty_cache()
