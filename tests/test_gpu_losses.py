@@ -141,3 +141,43 @@ def test_kabsch_full_size_round_trip(rr):
     assert float(t.abs().max()) <= 1e-5
     # float64 acos of a trace built from fp32 entries has a ~0.03 degree floor near zero angle (sqrt(2 * 3e-7) rad)
     assert float(rr.mean_angle_error(r, rot).item()) <= 0.05
+
+
+def test_kabsch_degenerate_clouds_give_finite_proper_rotations(rr):
+    """Clouds that do not determine a rotation - one point, all points equal, collinear points, a planar cloud against its
+    mirror image (the determinant fix decides), zero-size coordinates, huge coordinates: the result must still be a
+    finite proper rotation with a finite translation (the reference's SVD route returns SOME completion there), for
+    the plain and the weighted form, forward and backward."""
+    g = torch.Generator(device="cuda").manual_seed(17)
+    npts = 96
+    line = torch.linspace(-1, 1, npts, device="cuda").view(1, npts, 1) * torch.tensor([[[0.3, -0.5, 0.8]]], device="cuda")
+    plane = torch.randn(1, npts, 3, device="cuda", generator=g) * torch.tensor([[[1.0, 1.0, 0.0]]], device="cuda")
+    mirror = plane * torch.tensor([[[1.0, -1.0, 1.0]]], device="cuda")
+    same = torch.full((1, npts, 3), 0.25, device="cuda")
+    cases = {
+        "one point": (torch.randn(2, 1, 3, device="cuda", generator=g), torch.randn(2, 1, 3, device="cuda", generator=g)),
+        "all equal": (same, same + 1.0),
+        "collinear": (line, line.flip(1) + 2.0),
+        "planar vs mirror": (plane, mirror),
+        "zeros": (torch.zeros(1, npts, 3, device="cuda"), torch.zeros(1, npts, 3, device="cuda")),
+        # the covariance H is a sum of squares of the coordinates and its pullback divides by it: float32 carries that
+        # for coordinates of 1e-12 .. 1e15 (at 1e-20 H is denormal and dH = O(1 / H) overflows - as the 1 / (s_i^2 - s_j^2)
+        # of torch's own svd backward does)
+        "tiny": (1e-12 * torch.randn(1, npts, 3, device="cuda", generator=g), 1e-12 * torch.randn(1, npts, 3, device="cuda", generator=g)),
+        "huge": (1e15 * torch.randn(1, npts, 3, device="cuda", generator=g), 1e15 * torch.randn(1, npts, 3, device="cuda", generator=g)),
+    }
+    eye = torch.eye(3, device="cuda", dtype=torch.float64)
+    for name, (p, q) in cases.items():
+        for weights in (None, torch.rand(p.shape[0], p.shape[1], device="cuda", generator=g) + 0.1):
+            pg, qg = p.clone().requires_grad_(True), q.clone().requires_grad_(True)
+            r, t = rr.kabsch(pg, qg, weights=weights)
+            rd = r.double()
+            assert torch.isfinite(r).all() and torch.isfinite(t).all(), name
+            assert (rd @ rd.transpose(1, 2) - eye).abs().max().item() <= 1e-5, name
+            assert (torch.linalg.det(rd) - 1).abs().max().item() <= 1e-5, name
+            (r.sum() + t.sum()).backward()
+            assert torch.isfinite(pg.grad).all() and torch.isfinite(qg.grad).all(), name
+    # the mirror case has a well-defined answer in the plane: a planar cloud and its reflection across the x axis are
+    # matched exactly by the half turn about x (which also flips z, invisible to a planar cloud)
+    r, t = rr.kabsch(plane, mirror)
+    assert (torch.bmm(plane, r.transpose(1, 2)) + t.view(1, 1, 3) - mirror).abs().max().item() <= 1e-5
